@@ -1,0 +1,172 @@
+/*
+ * m4ri_b200.h — C-ABI of libm4ri_b200.so, the B200-native drop-in for the GF(2)
+ * matrix-multiplication path of thomwiggers/m4ri-rust.
+ *
+ * Every `mzd_*` symbol below has the name, argument order and meaning of the
+ * `extern "C"` prototype that m4ri-sys declares for the M4RI C library; the
+ * reference declaration each one replaces is cited as `file:line` relative to
+ * the reference checkout. All pointers in the `mzd_*` functions are HOST
+ * pointers: host memory is the source of truth on entry and is valid on return
+ * (m4ri-rust writes matrix words through `rows[]` without telling the library,
+ * m4ri-rust/src/friendly/binary_matrix.rs:137-159).
+ *
+ * The `m4ri_b200_*` symbols are additive: device-resident operands, stream
+ * control and algorithm selection for benchmarking and chained products.
+ *
+ * Error model (M4RI-compatible, `m4ri_die`): dimension mismatches and CUDA
+ * failures print to stderr and abort(). There is no CPU fallback for any
+ * multiplication entry point: without a usable sm_100 GPU they die loudly.
+ */
+#ifndef M4RI_B200_H
+#define M4RI_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- scalar types: m4ri-sys/src/misc.rs:5-26 -------------------------------- */
+typedef int rci_t;      /* Rci  = c_int  (misc.rs:5)  */
+typedef int wi_t;       /* Wi   = c_int  (misc.rs:14) */
+typedef int BIT;        /* BIT  = c_int  (misc.rs:8)  */
+typedef uint64_t word;  /* Word = u64    (misc.rs:11) */
+
+#define m4ri_radix 64                          /* misc.rs:18 */
+#define m4ri_one ((word)1)                     /* misc.rs:22 */
+#define m4ri_ffff ((word)0xffffffffffffffffULL) /* misc.rs:26 */
+
+/* ---- matrix descriptor: m4ri-sys/src/mzd.rs:16-79 --------------------------- */
+typedef struct mzd_block_t { /* mzd.rs:16-21 */
+  size_t size;               /* bytes in this block */
+  word *begin;
+  word *end;
+} mzd_block_t;
+
+/* Exactly 64 bytes (asserted by the reference test mzd.rs:385). Bit (r,c) is
+ * (rows[r][c/64] >> (c%64)) & 1  (mzd.rs:263-269). */
+typedef struct mzd_t {
+  rci_t nrows;             /*  0 */
+  rci_t ncols;             /*  4 */
+  wi_t width;              /*  8  ceil(ncols/64) */
+  wi_t rowstride;          /* 12  (width<3 || width even) ? width : width+1   (mzd.rs:35-37) */
+  wi_t offset_vector;      /* 16  rows[0] == blocks[0].begin + offset_vector  (mzd.rs:41-44) */
+  wi_t row_offset;         /* 20 */
+  uint8_t flags;           /* 24  mzd.rs:82-94 */
+  uint8_t blockrows_log;   /* 25 */
+  uint8_t padding[14];     /* 26  mzd.rs:67-71 */
+  word high_bitmask;       /* 40  valid bits of word width-1 */
+  mzd_block_t *blocks;     /* 48 */
+  word **rows;             /* 56 */
+} mzd_t;
+
+#define mzd_flag_nonzero_excess 0x2       /* mzd.rs:82 */
+#define mzd_flag_windowed_zerooffset 0x4  /* mzd.rs:85 */
+#define mzd_flag_windowed_zeroexcess 0x8  /* mzd.rs:88 */
+#define mzd_flag_windowed_ownsblocks 0x10 /* mzd.rs:91 */
+#define mzd_flag_multiple_blocks 0x20     /* mzd.rs:94 */
+
+/* ---- allocator set (one allocator owns every mzd_t the path touches) -------- */
+mzd_t *mzd_init(rci_t r, rci_t c);                       /* mzd.rs:98  */
+void mzd_free(mzd_t *A);                                 /* mzd.rs:102 */
+mzd_t *mzd_init_window(mzd_t *M, rci_t lowr, rci_t lowc, /* mzd.rs:121-127 (lowc % 64 == 0) */
+                       rci_t highr, rci_t highc);
+mzd_t *mzd_copy(mzd_t *DST, const mzd_t *A);             /* mzd.rs:192 */
+int mzd_equal(const mzd_t *A, const mzd_t *B);           /* mzd.rs:187 */
+void mzd_set_ui(mzd_t *A, unsigned int value);           /* mzd.rs:198 */
+void mzd_randomize(mzd_t *A);                            /* mzd.rs:184 */
+mzd_t *mzd_transpose(mzd_t *DST, const mzd_t *A);        /* mzd.rs:148 */
+mzd_t *mzd_add(mzd_t *C, const mzd_t *A, const mzd_t *B);/* mzd.rs:223 (C may alias A) */
+mzd_t *mzd_sub(mzd_t *C, const mzd_t *A, const mzd_t *B);/* mzd.rs:230 (alias of add)  */
+
+/* ---- the hot path: every one of these runs on the GPU ----------------------- */
+/* C = A*B. C == NULL: allocate. cutoff is a hint (the result does not depend on it). */
+mzd_t *mzd_mul(mzd_t *C, const mzd_t *A, const mzd_t *B, int cutoff);      /* strassen.rs:18 */
+/* C ^= A*B. */
+mzd_t *mzd_addmul(mzd_t *C, const mzd_t *A, const mzd_t *B, int cutoff);   /* strassen.rs:31 */
+mzd_t *mzd_mul_m4rm(mzd_t *C, const mzd_t *A, const mzd_t *B, int k);      /* brilliantrussian.rs:216 */
+mzd_t *mzd_addmul_m4rm(mzd_t *C, const mzd_t *A, const mzd_t *B, int k);   /* brilliantrussian.rs:224 */
+/* upstream-M4RI-shaped, named by the north star; not declared by m4ri-sys */
+mzd_t *_mzd_mul_m4rm(mzd_t *C, const mzd_t *A, const mzd_t *B, int k, int clear);
+mzd_t *mzd_mul_naive(mzd_t *C, const mzd_t *A, const mzd_t *B);            /* mzd.rs:152 */
+mzd_t *mzd_addmul_naive(mzd_t *C, const mzd_t *A, const mzd_t *B);         /* mzd.rs:173 */
+/* C (^)= A * Bt^T with B pre-transposed; clear != 0 zeroes C first. */
+mzd_t *_mzd_mul_naive(mzd_t *C, const mzd_t *A, const mzd_t *Bt, int clear); /* mzd.rs:163-168 */
+/* C (^)= v*A, v has few rows (normally 1). */
+mzd_t *_mzd_mul_va(mzd_t *C, const mzd_t *v, const mzd_t *A, int clear);   /* mzd.rs:181 */
+/* y = A*x, x is ncols(A) x 1, y is nrows(A) x 1 (the shape BinMatrix::mul_slice
+ * produces, binary_matrix.rs:426-427). Named by the north star. */
+mzd_t *mzd_mul_v(mzd_t *y, const mzd_t *A, const mzd_t *x);
+
+/* ---- additive API: algorithm choice, device-resident operands --------------- */
+enum m4ri_b200_algo {
+  M4RI_B200_ALGO_AUTO = 0,  /* library picks (shape based)                        */
+  M4RI_B200_ALGO_M4RM = 1,  /* path (a): shared-memory Four-Russians, LOP3 gather  */
+  M4RI_B200_ALGO_MMA = 2,   /* path (b): bits -> int8, tcgen05 MMA, parity of i32  */
+  M4RI_B200_ALGO_SIMPLE = 3 /* AND+popc row.row kernel (what *_naive maps to)      */
+};
+/* Force an algorithm for mzd_mul/mzd_addmul (AUTO restores the default). Also
+ * settable with the environment variable M4RI_B200_ALGO=auto|m4rm|mma|simple. */
+void m4ri_b200_set_algo(int algo);
+int m4ri_b200_get_algo(void);
+/* Strassen-Winograd levels applied above the leaf kernel on device products:
+ * -1 = automatic from `cutoff`/shape, 0 = none. */
+void m4ri_b200_set_strassen_levels(int levels);
+
+/* Number of usable CUDA devices (0 when there is none; never aborts). */
+int m4ri_b200_device_count(void);
+/* Name/SM count of the device the calling thread's context uses. */
+int m4ri_b200_device_info(char *name, int name_len, int *sm_count, int *cc_major, int *cc_minor);
+/* Use `stream` (a cudaStream_t) for all device-API work issued by this thread;
+ * NULL selects the library's own stream. */
+void m4ri_b200_set_stream(void *stream);
+void m4ri_b200_synchronize(void);
+/* Count of kernels the library launched since process start (bench: gpu_launches). */
+unsigned long long m4ri_b200_launch_count(void);
+const char *m4ri_b200_version(void);
+
+/* A device-resident matrix: same 64-bit-word row-major LSB-first packing as
+ * mzd_t, rowstride in words (>= width, even), excess bits always zero. */
+typedef struct m4ri_b200_dmat m4ri_b200_dmat_t;
+m4ri_b200_dmat_t *m4ri_b200_dmat_init(rci_t nrows, rci_t ncols);
+/* Wrap caller-owned device memory (e.g. a torch tensor): not freed by dmat_free. */
+m4ri_b200_dmat_t *m4ri_b200_dmat_wrap(void *dptr, rci_t nrows, rci_t ncols, wi_t rowstride);
+void m4ri_b200_dmat_free(m4ri_b200_dmat_t *M);
+rci_t m4ri_b200_dmat_nrows(const m4ri_b200_dmat_t *M);
+rci_t m4ri_b200_dmat_ncols(const m4ri_b200_dmat_t *M);
+wi_t m4ri_b200_dmat_rowstride(const m4ri_b200_dmat_t *M);
+void *m4ri_b200_dmat_ptr(const m4ri_b200_dmat_t *M);
+/* Async on the current stream; host memory should be pinned (mzd_init's is). */
+void m4ri_b200_upload(m4ri_b200_dmat_t *D, const mzd_t *H);
+void m4ri_b200_download(mzd_t *H, const m4ri_b200_dmat_t *D);
+/* C (^)= A*B on device, async on the current stream. algo as enum above. */
+void m4ri_b200_dmul(m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *A, const m4ri_b200_dmat_t *B,
+                    int clear, int algo);
+/* C (^)= A*Bt^T on device (both operands k-contiguous). */
+void m4ri_b200_dmul_abt(m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *A,
+                        const m4ri_b200_dmat_t *Bt, int clear, int algo);
+/* y (^)= A*x, x packed as a 1 x ncols(A) row, y packed as a 1 x nrows(A) row
+ * (packed words in, packed words out: SURVEY 8f.2). */
+void m4ri_b200_dmul_v(m4ri_b200_dmat_t *y, const m4ri_b200_dmat_t *A, const m4ri_b200_dmat_t *x,
+                      int clear);
+/* C (^)= v*A, v is r x nrows(A) with small r. */
+void m4ri_b200_dmul_va(m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *v, const m4ri_b200_dmat_t *A,
+                       int clear);
+void m4ri_b200_dtranspose(m4ri_b200_dmat_t *DST, const m4ri_b200_dmat_t *A);
+void m4ri_b200_dadd(m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *A, const m4ri_b200_dmat_t *B);
+void m4ri_b200_dcopy(m4ri_b200_dmat_t *DST, const m4ri_b200_dmat_t *A);
+/* Fill with splitmix64(seed) words, row by row, excess bits masked: the same
+ * stream of words the oracle's generator produces (oracle/gf2_oracle.c). */
+void m4ri_b200_dfill_random(m4ri_b200_dmat_t *M, uint64_t seed);
+/* 64-bit XOR-fold checksum of all words (position-mixed), computed on device. */
+uint64_t m4ri_b200_dchecksum(const m4ri_b200_dmat_t *M);
+/* Freivalds over GF(2) with 64 packed random vectors: returns 1 iff
+ * A*(B*X) == C*X for X = random(ncols(B) x 64, seed). False accept 2^-64. */
+int m4ri_b200_dfreivalds(const m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *A,
+                         const m4ri_b200_dmat_t *B, uint64_t seed);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* M4RI_B200_H */

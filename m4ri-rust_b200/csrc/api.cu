@@ -1,0 +1,433 @@
+// api.cu — context, device-resident matrices and the multiplication entry
+// points of the C-ABI (include/m4ri_b200.h). Each mzd_* product does what the
+// reference's FFI call does (allocate C when NULL, validate shapes, die on
+// mismatch — SURVEY 8b) with the arithmetic on the GPU:
+//   host mzd_t --H2D--> device mirrors --kernels--> device C --D2H--> host mzd_t
+// synchronously, because m4ri-rust reads the result words right after the call
+// returns (m4ri-rust/src/friendly/binary_matrix.rs:459-472).
+#include <stdarg.h>
+#include <string.h>
+
+#include <mutex>
+
+#include "common.cuh"
+
+namespace m4b {
+
+std::atomic<unsigned long long> g_launches{0};
+
+void die(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vfprintf(stderr, fmt, ap);
+  va_end(ap);
+  fflush(stderr);
+  abort();
+}
+
+// ---- context -------------------------------------------------------------------
+static std::once_flag g_once;
+static int g_ndev = 0, g_sms = 0, g_cc_major = 0, g_cc_minor = 0;
+static char g_name[256] = "";
+static std::atomic<int> g_algo{-1};
+static std::atomic<int> g_strassen{-1};
+
+static void probe() {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    (void)cudaGetLastError();
+    n = 0;
+  }
+  g_ndev = n;
+  if (n > 0) {
+    int dev = 0;
+    cudaDeviceProp p;
+    if (cudaGetDevice(&dev) == cudaSuccess && cudaGetDeviceProperties(&p, dev) == cudaSuccess) {
+      g_sms = p.multiProcessorCount;
+      g_cc_major = p.major;
+      g_cc_minor = p.minor;
+      snprintf(g_name, sizeof(g_name), "%s", p.name);
+    } else {
+      (void)cudaGetLastError();
+      g_ndev = 0;
+    }
+  }
+  const char *e = getenv("M4RI_B200_ALGO");
+  int a = M4RI_B200_ALGO_AUTO;
+  if (e) {
+    if (!strcmp(e, "m4rm")) a = M4RI_B200_ALGO_M4RM;
+    else if (!strcmp(e, "mma")) a = M4RI_B200_ALGO_MMA;
+    else if (!strcmp(e, "simple")) a = M4RI_B200_ALGO_SIMPLE;
+  }
+  g_algo.store(a);
+}
+
+void require_device() {
+  std::call_once(g_once, probe);
+  if (g_ndev <= 0)
+    die("m4ri_b200: no CUDA device is available; this library has no CPU fallback for the "
+        "GF(2) multiplication path\n");
+  if (g_cc_major < 10)
+    die("m4ri_b200: device '%s' is sm_%d%d; the kernels are built for sm_100a (B200) only\n",
+        g_name, g_cc_major, g_cc_minor);
+}
+
+int sm_count() {
+  require_device();
+  return g_sms;
+}
+bool has_tcgen05() {
+  require_device();
+  return g_cc_major == 10;
+}
+
+static thread_local cudaStream_t t_user_stream = nullptr;
+static thread_local bool t_use_user_stream = false;
+static thread_local cudaStream_t t_own_stream = nullptr;
+
+cudaStream_t current_stream() {
+  require_device();
+  if (t_use_user_stream) return t_user_stream;
+  if (!t_own_stream) M4B_CUDA(cudaStreamCreateWithFlags(&t_own_stream, cudaStreamNonBlocking));
+  return t_own_stream;
+}
+
+// ---- device matrices -------------------------------------------------------------
+static DMat *dmat_new(rci_t nrows, rci_t ncols, cudaStream_t s) {
+  if (nrows < 0 || ncols < 0) die("m4ri_b200: negative matrix dimension\n");
+  DMat *M = (DMat *)calloc(1, sizeof(DMat));
+  if (!M) die("m4ri_b200: out of memory\n");
+  M->nrows = nrows;
+  M->ncols = ncols;
+  M->width = width_of(ncols);
+  M->rowstride = dev_rowstride(ncols);
+  size_t bytes = (size_t)(nrows > 0 ? nrows : 1) * M->rowstride * 8;
+  M4B_CUDA(cudaMallocAsync(&M->base, bytes, s));
+  M4B_CUDA(cudaMemsetAsync(M->base, 0, bytes, s));
+  M->d = (word *)M->base;
+  return M;
+}
+
+static void dmat_delete(DMat *M, cudaStream_t s) {
+  if (!M) return;
+  if (M->base) M4B_CUDA(cudaFreeAsync(M->base, s));
+  free(M);
+}
+
+static void upload(DMat *D, const mzd_t *H, cudaStream_t s) {
+  if (D->nrows != H->nrows || D->ncols != H->ncols)
+    die("m4ri_b200: upload: shape mismatch (%d x %d vs %d x %d)\n", D->nrows, D->ncols, H->nrows,
+        H->ncols);
+  if (H->nrows == 0 || H->width == 0) return;
+  // rows[] is the only thing the reference guarantees ("multi-block");
+  // copy maximal runs of evenly strided rows with one 2-D copy each.
+  rci_t i = 0;
+  while (i < H->nrows) {
+    rci_t j = i + 1;
+    while (j < H->nrows && H->rows[j] == H->rows[i] + (size_t)(j - i) * H->rowstride) j++;
+    M4B_CUDA(cudaMemcpy2DAsync(D->d + (size_t)i * D->rowstride, (size_t)D->rowstride * 8,
+                               H->rows[i], (size_t)H->rowstride * 8, (size_t)H->width * 8, j - i,
+                               cudaMemcpyHostToDevice, s));
+    i = j;
+  }
+  k_mask_excess(D, s);  // never trust excess bits of a caller's matrix
+}
+
+static void download(mzd_t *H, const DMat *D, cudaStream_t s) {
+  if (D->nrows != H->nrows || D->ncols != H->ncols)
+    die("m4ri_b200: download: shape mismatch\n");
+  if (H->nrows == 0 || H->width == 0) return;
+  rci_t i = 0;
+  while (i < H->nrows) {
+    rci_t j = i + 1;
+    while (j < H->nrows && H->rows[j] == H->rows[i] + (size_t)(j - i) * H->rowstride) j++;
+    M4B_CUDA(cudaMemcpy2DAsync(H->rows[i], (size_t)H->rowstride * 8,
+                               D->d + (size_t)i * D->rowstride, (size_t)D->rowstride * 8,
+                               (size_t)H->width * 8, j - i, cudaMemcpyDeviceToHost, s));
+    i = j;
+  }
+}
+
+// ---- algorithm choice ---------------------------------------------------------------
+static int resolve_algo(int algo, int m, int k, int n) {
+  std::call_once(g_once, probe);
+  if (algo == M4RI_B200_ALGO_AUTO) algo = g_algo.load();
+  if (algo == M4RI_B200_ALGO_AUTO) {
+    // Tiny products are launch-latency bound: the AND+popc kernel has the smallest
+    // fixed cost. Otherwise the shared-memory Four-Russians kernel.
+    long long work = (long long)m * n;
+    algo = (work <= 64LL * 64 || k <= 64) ? M4RI_B200_ALGO_SIMPLE : M4RI_B200_ALGO_M4RM;
+  }
+  return algo;
+}
+
+// C (^)= A*B on device
+static void dmul(DMat *C, const DMat *A, const DMat *B, int clear, int algo, cudaStream_t s) {
+  if (A->ncols != B->nrows || C->nrows != A->nrows || C->ncols != B->ncols)
+    die("m4ri_b200: mul: shapes (%d x %d) * (%d x %d) -> (%d x %d) do not match\n", A->nrows,
+        A->ncols, B->nrows, B->ncols, C->nrows, C->ncols);
+  algo = resolve_algo(algo, C->nrows, A->ncols, C->ncols);
+  if (algo == M4RI_B200_ALGO_M4RM) {
+    k_mul_m4rm(C, A, B, clear, s);
+    return;
+  }
+  DMat *Bt = dmat_new(B->ncols, B->nrows, s);
+  k_transpose(Bt, B, s);
+  if (algo == M4RI_B200_ALGO_MMA) k_mul_abt_mma(C, A, Bt, clear, s);
+  else k_mul_abt_simple(C, A, Bt, clear, s);
+  dmat_delete(Bt, s);
+}
+
+// C (^)= A*Bt^T on device
+static void dmul_abt(DMat *C, const DMat *A, const DMat *Bt, int clear, int algo, cudaStream_t s) {
+  if (A->ncols != Bt->ncols || C->nrows != A->nrows || C->ncols != Bt->nrows)
+    die("m4ri_b200: mul (pre-transposed): shapes (%d x %d) * (%d x %d)^T -> (%d x %d) do not match\n",
+        A->nrows, A->ncols, Bt->nrows, Bt->ncols, C->nrows, C->ncols);
+  algo = resolve_algo(algo, C->nrows, A->ncols, C->ncols);
+  if (algo == M4RI_B200_ALGO_MMA) {
+    k_mul_abt_mma(C, A, Bt, clear, s);
+  } else if (algo == M4RI_B200_ALGO_M4RM) {
+    DMat *B = dmat_new(Bt->ncols, Bt->nrows, s);
+    k_transpose(B, Bt, s);
+    k_mul_m4rm(C, A, B, clear, s);
+    dmat_delete(B, s);
+  } else {
+    k_mul_abt_simple(C, A, Bt, clear, s);
+  }
+}
+
+// Shared body of the host-ABI products. form: 0 = A*B, 1 = A*Bt^T, 2 = v*A.
+static mzd_t *host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int clear, int algo, int form,
+                           const char *who) {
+  rci_t m = A->nrows, k = A->ncols;
+  rci_t n = form == 1 ? B->nrows : B->ncols;
+  rci_t kb = form == 1 ? B->ncols : B->nrows;
+  if (k != kb) die("m4ri_b200: %s: A ncols (%d) need to match B nrows (%d)\n", who, k, kb);
+  if (!C) {
+    if (!clear) die("m4ri_b200: %s: C must not be NULL when accumulating\n", who);
+    C = mzd_init(m, n);
+  } else if (C->nrows != m || C->ncols != n) {
+    die("m4ri_b200: %s: C (%d x %d) has wrong dimensions, expected (%d x %d)\n", who, C->nrows,
+        C->ncols, m, n);
+  }
+  if (C == A || C == B) die("m4ri_b200: %s: C must not alias an input\n", who);
+  cudaStream_t s = current_stream();
+  DMat *dA = dmat_new(A->nrows, A->ncols, s), *dB = dmat_new(B->nrows, B->ncols, s),
+       *dC = dmat_new(m, n, s);
+  upload(dA, A, s);
+  upload(dB, B, s);
+  if (!clear) upload(dC, C, s);
+  if (form == 0) dmul(dC, dA, dB, clear, algo, s);
+  else if (form == 1) dmul_abt(dC, dA, dB, clear, algo, s);
+  else k_mul_va(dC, dA, dB, clear, s);
+  download(C, dC, s);
+  dmat_delete(dA, s);
+  dmat_delete(dB, s);
+  dmat_delete(dC, s);
+  M4B_CUDA(cudaStreamSynchronize(s));
+  return C;
+}
+
+}  // namespace m4b
+
+using namespace m4b;
+
+extern "C" {
+
+// ---- hot-path entry points (reference declarations cited in include/m4ri_b200.h) ----
+mzd_t *mzd_mul(mzd_t *C, const mzd_t *A, const mzd_t *B, int cutoff) {
+  (void)cutoff;  // a tuning hint in M4RI; the product does not depend on it
+  return host_product(C, A, B, 1, M4RI_B200_ALGO_AUTO, 0, "mzd_mul");
+}
+mzd_t *mzd_addmul(mzd_t *C, const mzd_t *A, const mzd_t *B, int cutoff) {
+  (void)cutoff;
+  return host_product(C, A, B, 0, M4RI_B200_ALGO_AUTO, 0, "mzd_addmul");
+}
+mzd_t *mzd_mul_m4rm(mzd_t *C, const mzd_t *A, const mzd_t *B, int k) {
+  (void)k;  // table width is fixed by the shared-memory budget
+  return host_product(C, A, B, 1, M4RI_B200_ALGO_M4RM, 0, "mzd_mul_m4rm");
+}
+mzd_t *mzd_addmul_m4rm(mzd_t *C, const mzd_t *A, const mzd_t *B, int k) {
+  (void)k;
+  return host_product(C, A, B, 0, M4RI_B200_ALGO_M4RM, 0, "mzd_addmul_m4rm");
+}
+mzd_t *_mzd_mul_m4rm(mzd_t *C, const mzd_t *A, const mzd_t *B, int k, int clear) {
+  (void)k;
+  return host_product(C, A, B, clear != 0, M4RI_B200_ALGO_M4RM, 0, "_mzd_mul_m4rm");
+}
+mzd_t *mzd_mul_naive(mzd_t *C, const mzd_t *A, const mzd_t *B) {
+  return host_product(C, A, B, 1, M4RI_B200_ALGO_SIMPLE, 0, "mzd_mul_naive");
+}
+mzd_t *mzd_addmul_naive(mzd_t *C, const mzd_t *A, const mzd_t *B) {
+  return host_product(C, A, B, 0, M4RI_B200_ALGO_SIMPLE, 0, "mzd_addmul_naive");
+}
+mzd_t *_mzd_mul_naive(mzd_t *C, const mzd_t *A, const mzd_t *Bt, int clear) {
+  return host_product(C, A, Bt, clear != 0, M4RI_B200_ALGO_SIMPLE, 1, "_mzd_mul_naive");
+}
+mzd_t *_mzd_mul_va(mzd_t *C, const mzd_t *v, const mzd_t *A, int clear) {
+  return host_product(C, v, A, clear != 0, M4RI_B200_ALGO_AUTO, 2, "_mzd_mul_va");
+}
+
+// y = A*x with x (n x 1) and y (m x 1) column matrices, one word per row
+// (the shape BinMatrix::mul_slice builds, binary_matrix.rs:416-431). The column
+// <-> packed-row marshalling is O(m+n) on the host; A never leaves packed form.
+mzd_t *mzd_mul_v(mzd_t *y, const mzd_t *A, const mzd_t *x) {
+  rci_t m = A->nrows, n = A->ncols;
+  if (x->nrows != n || x->ncols != 1)
+    die("m4ri_b200: mzd_mul_v: x must be %d x 1 (got %d x %d)\n", n, x->nrows, x->ncols);
+  if (!y) y = mzd_init(m, 1);
+  else if (y->nrows != m || y->ncols != 1)
+    die("m4ri_b200: mzd_mul_v: y must be %d x 1\n", m);
+  cudaStream_t s = current_stream();
+  DMat *dA = dmat_new(m, n, s), *dx = dmat_new(1, n, s), *dy = dmat_new(1, m, s);
+  upload(dA, A, s);
+  int xw = width_of(n), yw = width_of(m);
+  word *hx = (word *)calloc((size_t)(xw > 0 ? xw : 1), 8), *hy = (word *)calloc((size_t)(yw > 0 ? yw : 1), 8);
+  for (rci_t j = 0; j < n; j++) hx[j / 64] |= (x->rows[j][0] & 1) << (j % 64);
+  if (xw) M4B_CUDA(cudaMemcpyAsync(dx->d, hx, (size_t)xw * 8, cudaMemcpyHostToDevice, s));
+  k_mul_v(dy, dA, dx, 1, s);
+  if (yw) M4B_CUDA(cudaMemcpyAsync(hy, dy->d, (size_t)yw * 8, cudaMemcpyDeviceToHost, s));
+  dmat_delete(dA, s);
+  dmat_delete(dx, s);
+  dmat_delete(dy, s);
+  M4B_CUDA(cudaStreamSynchronize(s));
+  for (rci_t i = 0; i < m; i++) y->rows[i][0] = (hy[i / 64] >> (i % 64)) & 1;
+  free(hx);
+  free(hy);
+  return y;
+}
+
+// ---- additive API -------------------------------------------------------------------
+void m4ri_b200_set_algo(int algo) {
+  std::call_once(g_once, probe);
+  if (algo < 0 || algo > 3) die("m4ri_b200: unknown algorithm %d\n", algo);
+  g_algo.store(algo);
+}
+int m4ri_b200_get_algo(void) {
+  std::call_once(g_once, probe);
+  return g_algo.load();
+}
+void m4ri_b200_set_strassen_levels(int levels) { g_strassen.store(levels); }
+
+int m4ri_b200_device_count(void) {
+  std::call_once(g_once, probe);
+  return g_ndev;
+}
+int m4ri_b200_device_info(char *name, int name_len, int *sms, int *cc_major, int *cc_minor) {
+  std::call_once(g_once, probe);
+  if (g_ndev <= 0) return 0;
+  if (name && name_len > 0) {
+    strncpy(name, g_name, (size_t)name_len - 1);
+    name[name_len - 1] = 0;
+  }
+  if (sms) *sms = g_sms;
+  if (cc_major) *cc_major = g_cc_major;
+  if (cc_minor) *cc_minor = g_cc_minor;
+  return 1;
+}
+void m4ri_b200_set_stream(void *stream) {
+  t_user_stream = (cudaStream_t)stream;
+  t_use_user_stream = true;
+}
+void m4ri_b200_synchronize(void) { M4B_CUDA(cudaStreamSynchronize(current_stream())); }
+unsigned long long m4ri_b200_launch_count(void) { return g_launches.load(); }
+const char *m4ri_b200_version(void) { return "m4ri_b200 0.1 (sm_100a)"; }
+
+m4ri_b200_dmat_t *m4ri_b200_dmat_init(rci_t nrows, rci_t ncols) {
+  return dmat_new(nrows, ncols, current_stream());
+}
+m4ri_b200_dmat_t *m4ri_b200_dmat_wrap(void *dptr, rci_t nrows, rci_t ncols, wi_t rowstride) {
+  if (rowstride < width_of(ncols) || (rowstride & 1) || ((uintptr_t)dptr & 15))
+    die("m4ri_b200: dmat_wrap: rowstride must be even and >= width, pointer 16-byte aligned\n");
+  DMat *M = (DMat *)calloc(1, sizeof(DMat));
+  if (!M) die("m4ri_b200: out of memory\n");
+  M->d = (word *)dptr;
+  M->nrows = nrows;
+  M->ncols = ncols;
+  M->width = width_of(ncols);
+  M->rowstride = rowstride;
+  M->base = nullptr;
+  return M;
+}
+void m4ri_b200_dmat_free(m4ri_b200_dmat_t *M) {
+  if (M) dmat_delete(M, M->base ? current_stream() : nullptr);
+}
+rci_t m4ri_b200_dmat_nrows(const m4ri_b200_dmat_t *M) { return M->nrows; }
+rci_t m4ri_b200_dmat_ncols(const m4ri_b200_dmat_t *M) { return M->ncols; }
+wi_t m4ri_b200_dmat_rowstride(const m4ri_b200_dmat_t *M) { return M->rowstride; }
+void *m4ri_b200_dmat_ptr(const m4ri_b200_dmat_t *M) { return M->d; }
+
+void m4ri_b200_upload(m4ri_b200_dmat_t *D, const mzd_t *H) { upload(D, H, current_stream()); }
+void m4ri_b200_download(mzd_t *H, const m4ri_b200_dmat_t *D) { download(H, D, current_stream()); }
+
+void m4ri_b200_dmul(m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *A, const m4ri_b200_dmat_t *B,
+                    int clear, int algo) {
+  dmul(C, A, B, clear, algo, current_stream());
+}
+void m4ri_b200_dmul_abt(m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *A,
+                        const m4ri_b200_dmat_t *Bt, int clear, int algo) {
+  dmul_abt(C, A, Bt, clear, algo, current_stream());
+}
+void m4ri_b200_dmul_v(m4ri_b200_dmat_t *y, const m4ri_b200_dmat_t *A, const m4ri_b200_dmat_t *x,
+                      int clear) {
+  if (x->nrows != 1 || x->ncols != A->ncols || y->nrows != 1 || y->ncols != A->nrows)
+    die("m4ri_b200: dmul_v: x must be 1 x %d and y 1 x %d\n", A->ncols, A->nrows);
+  k_mul_v(y, A, x, clear, current_stream());
+}
+void m4ri_b200_dmul_va(m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *v, const m4ri_b200_dmat_t *A,
+                       int clear) {
+  if (v->ncols != A->nrows || C->nrows != v->nrows || C->ncols != A->ncols)
+    die("m4ri_b200: dmul_va: shapes do not match\n");
+  k_mul_va(C, v, A, clear, current_stream());
+}
+void m4ri_b200_dtranspose(m4ri_b200_dmat_t *DST, const m4ri_b200_dmat_t *A) {
+  if (DST->nrows != A->ncols || DST->ncols != A->nrows)
+    die("m4ri_b200: dtranspose: wrong size for return matrix\n");
+  k_transpose(DST, A, current_stream());
+}
+void m4ri_b200_dadd(m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *A, const m4ri_b200_dmat_t *B) {
+  if (A->nrows != B->nrows || A->ncols != B->ncols || C->nrows != A->nrows || C->ncols != A->ncols)
+    die("m4ri_b200: dadd: rows and columns must match\n");
+  k_add(C, A, B, current_stream());
+}
+void m4ri_b200_dcopy(m4ri_b200_dmat_t *DST, const m4ri_b200_dmat_t *A) {
+  if (DST->nrows != A->nrows || DST->ncols != A->ncols) die("m4ri_b200: dcopy: shape mismatch\n");
+  k_copy(DST, A, current_stream());
+}
+void m4ri_b200_dfill_random(m4ri_b200_dmat_t *M, uint64_t seed) {
+  k_fill_random(M, seed, current_stream());
+}
+uint64_t m4ri_b200_dchecksum(const m4ri_b200_dmat_t *M) { return k_checksum(M, current_stream()); }
+
+// Freivalds with 64 packed vectors; the three thin products use the AND+popc
+// kernel so the check shares no code with the M4RM / MMA kernels it verifies.
+int m4ri_b200_dfreivalds(const m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *A,
+                         const m4ri_b200_dmat_t *B, uint64_t seed) {
+  cudaStream_t s = current_stream();
+  rci_t m = A->nrows, k = A->ncols, n = B->ncols;
+  if (B->nrows != k || C->nrows != m || C->ncols != n) die("m4ri_b200: dfreivalds: shape mismatch\n");
+  // X^T is 64 x n with row j of X = splitmix64 word j: generate X (n x 64) then transpose.
+  DMat *X = dmat_new(n, 64, s), *Xt = dmat_new(64, n, s);
+  k_fill_random(X, seed, s);
+  k_transpose(Xt, X, s);
+  DMat *BX = dmat_new(k, 64, s), *BXt = dmat_new(64, k, s), *ABX = dmat_new(m, 64, s),
+       *CX = dmat_new(m, 64, s);
+  k_mul_abt_simple(BX, B, Xt, 1, s);
+  k_transpose(BXt, BX, s);
+  k_mul_abt_simple(ABX, A, BXt, 1, s);
+  k_mul_abt_simple(CX, C, Xt, 1, s);
+  k_add(CX, CX, ABX, s);
+  uint64_t chk_zero;
+  {
+    DMat *Z = dmat_new(m, 64, s);
+    uint64_t a = k_checksum(CX, s), z = k_checksum(Z, s);
+    chk_zero = (a == z);
+    dmat_delete(Z, s);
+  }
+  dmat_delete(X, s); dmat_delete(Xt, s); dmat_delete(BX, s); dmat_delete(BXt, s);
+  dmat_delete(ABX, s); dmat_delete(CX, s);
+  M4B_CUDA(cudaStreamSynchronize(s));
+  return (int)chk_zero;
+}
+
+}  // extern "C"

@@ -1,0 +1,90 @@
+// common.cuh — shared declarations of libm4ri_b200 (internal, not installed).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+
+#include <atomic>
+
+#include "../../include/m4ri_b200.h"
+
+namespace m4b {
+
+// M4RI's error model (m4ri_die): print and abort. SURVEY 8b "Errors".
+[[noreturn]] void die(const char *fmt, ...);
+
+#define M4B_CUDA(expr)                                                                   \
+  do {                                                                                   \
+    cudaError_t _e = (expr);                                                             \
+    if (_e != cudaSuccess)                                                               \
+      ::m4b::die("m4ri_b200: CUDA error %s (%d) at %s:%d: %s\n", cudaGetErrorName(_e),  \
+                 (int)_e, __FILE__, __LINE__, cudaGetErrorString(_e));                   \
+  } while (0)
+
+// Called after every kernel launch: counts it and surfaces launch errors.
+extern std::atomic<unsigned long long> g_launches;
+#define M4B_LAUNCHED()                 \
+  do {                                 \
+    ::m4b::g_launches.fetch_add(1);    \
+    M4B_CUDA(cudaGetLastError());      \
+  } while (0)
+
+// Makes sure a usable device exists (dies loudly otherwise) and returns the
+// stream the calling thread issues work on.
+cudaStream_t current_stream();
+void require_device();
+int sm_count();
+bool has_tcgen05();  // compute capability 10.x
+
+static inline int width_of(int ncols) { return (ncols + 63) / 64; }
+static inline word high_mask(int ncols) {
+  int r = ncols % 64;
+  return r ? (((word)1 << r) - 1) : ~(word)0;
+}
+// Device row stride (64-bit words): even and >= 2 so every row is 16-byte aligned.
+static inline int dev_rowstride(int ncols) {
+  int w = width_of(ncols);
+  w = (w + 1) & ~1;
+  return w < 2 ? 2 : w;
+}
+
+}  // namespace m4b
+
+// Device-resident matrix (opaque at the ABI).
+struct m4ri_b200_dmat {
+  word *d;        // first word of row 0
+  rci_t nrows, ncols;
+  wi_t width;     // ceil(ncols/64)
+  wi_t rowstride; // words between rows (even)
+  void *base;     // allocation to free (NULL when wrapped / window)
+};
+
+namespace m4b {
+typedef m4ri_b200_dmat DMat;
+
+// ---- kernels_aux.cu ----------------------------------------------------------
+void k_zero(DMat *M, cudaStream_t s);
+void k_mask_excess(DMat *M, cudaStream_t s);
+void k_add(DMat *C, const DMat *A, const DMat *B, cudaStream_t s);
+void k_copy(DMat *D, const DMat *A, cudaStream_t s);
+void k_transpose(DMat *D, const DMat *A, cudaStream_t s);
+void k_fill_random(DMat *M, uint64_t seed, cudaStream_t s);
+uint64_t k_checksum(const DMat *M, cudaStream_t s);
+// y (^)= A*x ; x, y packed rows
+void k_mul_v(DMat *y, const DMat *A, const DMat *x, int clear, cudaStream_t s);
+// C (^)= v*A
+void k_mul_va(DMat *C, const DMat *v, const DMat *A, int clear, cudaStream_t s);
+// C (^)= A*Bt^T by AND + popcount parity
+void k_mul_abt_simple(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream_t s);
+
+// ---- kernels_m4rm.cu ---------------------------------------------------------
+// C (^)= A*B, Four-Russians tables in shared memory
+void k_mul_m4rm(DMat *C, const DMat *A, const DMat *B, int clear, cudaStream_t s);
+
+// ---- kernels_mma.cu ----------------------------------------------------------
+// C (^)= A*Bt^T, bits -> int8 in shared memory / TMEM, tcgen05 MMA, parity
+void k_mul_abt_mma(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream_t s);
+bool mma_shape_ok(const DMat *C, const DMat *A, const DMat *Bt);
+
+}  // namespace m4b

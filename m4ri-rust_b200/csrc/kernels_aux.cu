@@ -1,0 +1,330 @@
+// kernels_aux.cu — the HBM-bound kernels around the product: XOR-add (the
+// Strassen / addmul "add", reference mzd_add m4ri-sys/src/mzd.rs:223), bit-matrix
+// transpose (mzd_transpose, mzd.rs:148), mat-vec (mul_slice path,
+// m4ri-rust/src/friendly/binary_matrix.rs:416-431), vec-mat (_mzd_mul_va,
+// mzd.rs:181), the AND+popcount product behind the *_naive entry points
+// (mzd.rs:152-173), plus input generation and checksums for the harness.
+#include "common.cuh"
+
+namespace m4b {
+
+static inline unsigned cdiv(long long a, long long b) { return (unsigned)((a + b - 1) / b); }
+
+// ---------------------------------------------------------------------------
+// zero / mask / copy / add
+// ---------------------------------------------------------------------------
+void k_zero(DMat *M, cudaStream_t s) {
+  if (M->nrows == 0 || M->width == 0) return;
+  M4B_CUDA(cudaMemset2DAsync(M->d, (size_t)M->rowstride * 8, 0, (size_t)M->width * 8, M->nrows, s));
+}
+
+__global__ void mask_excess_kernel(word *d, int nrows, int width, int rs, word hm) {
+  int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < nrows) d[(size_t)r * rs + width - 1] &= hm;
+}
+
+void k_mask_excess(DMat *M, cudaStream_t s) {
+  if (M->ncols % 64 == 0 || M->nrows == 0) return;
+  mask_excess_kernel<<<cdiv(M->nrows, 256), 256, 0, s>>>(M->d, M->nrows, M->width, M->rowstride,
+                                                          high_mask(M->ncols));
+  M4B_LAUNCHED();
+}
+
+void k_copy(DMat *D, const DMat *A, cudaStream_t s) {
+  if (A->nrows == 0 || A->width == 0) return;
+  M4B_CUDA(cudaMemcpy2DAsync(D->d, (size_t)D->rowstride * 8, A->d, (size_t)A->rowstride * 8,
+                             (size_t)A->width * 8, A->nrows, cudaMemcpyDeviceToDevice, s));
+}
+
+// C = A ^ B over nrows x width words. 16-byte vectors: 3 x 16 B of traffic per
+// thread-iteration, pure HBM streaming (algorithmic bytes = 3 * nrows * width * 8).
+template <typename V>
+__global__ void add_kernel(V *C, const V *A, const V *B, int nrows, int wv, int cs,
+                           int as, int bs) {
+  long long total = (long long)nrows * wv;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    int r = (int)(i / wv), w = (int)(i % wv);
+    V a = A[(size_t)r * as + w], b = B[(size_t)r * bs + w], c;
+    if constexpr (sizeof(V) == 16) {
+      c.x = a.x ^ b.x; c.y = a.y ^ b.y;
+    } else {
+      c = a ^ b;
+    }
+    C[(size_t)r * cs + w] = c;
+  }
+}
+
+void k_add(DMat *C, const DMat *A, const DMat *B, cudaStream_t s) {
+  if (C->nrows == 0 || C->width == 0) return;
+  bool vec = (C->width % 2 == 0) && (C->rowstride % 2 == 0) && (A->rowstride % 2 == 0) &&
+             (B->rowstride % 2 == 0) && (((uintptr_t)C->d | (uintptr_t)A->d | (uintptr_t)B->d) % 16 == 0);
+  long long total = (long long)C->nrows * (vec ? C->width / 2 : C->width);
+  unsigned grid = (unsigned)min((long long)cdiv(total, 256), (long long)sm_count() * 16);
+  if (vec)
+    add_kernel<ulonglong2><<<grid, 256, 0, s>>>((ulonglong2 *)C->d, (const ulonglong2 *)A->d,
+                                                (const ulonglong2 *)B->d, C->nrows, C->width / 2,
+                                                C->rowstride / 2, A->rowstride / 2, B->rowstride / 2);
+  else
+    add_kernel<word><<<grid, 256, 0, s>>>(C->d, A->d, B->d, C->nrows, C->width, C->rowstride,
+                                          A->rowstride, B->rowstride);
+  M4B_LAUNCHED();
+}
+
+// ---------------------------------------------------------------------------
+// transpose: 32 x 1024-bit input tiles, 32x32 bit blocks turned with ballots
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024)
+transpose_kernel(uint32_t *__restrict__ D, const uint32_t *__restrict__ S, int nrows, int ncols,
+                 int sw32, int ss32, int ds32) {
+  __shared__ uint32_t tile[32][33];
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  const int r0 = blockIdx.y * 32, cw0 = blockIdx.x * 32;
+  uint32_t v = 0;
+  if (r0 + w < nrows && cw0 + l < sw32) v = S[(size_t)(r0 + w) * ss32 + cw0 + l];
+  tile[w][l] = v;
+  __syncthreads();
+  uint32_t x = tile[l][w];  // input row r0+l, input column word cw0+w
+  uint32_t out = 0;
+#pragma unroll
+  for (int j = 0; j < 32; j++) {
+    uint32_t b = __ballot_sync(0xffffffffu, (x >> j) & 1u);
+    if (l == j) out = b;
+  }
+  int orow = (cw0 + w) * 32 + l;  // = input column
+  if (orow < ncols) D[(size_t)orow * ds32 + (r0 >> 5)] = out;
+}
+
+void k_transpose(DMat *D, const DMat *A, cudaStream_t s) {
+  if (A->nrows == 0 || A->ncols == 0) return;
+  int sw32 = A->width * 2;
+  dim3 grid(cdiv(sw32, 32), cdiv(A->nrows, 32));
+  transpose_kernel<<<grid, 1024, 0, s>>>((uint32_t *)D->d, (const uint32_t *)A->d, A->nrows,
+                                         A->ncols, sw32, A->rowstride * 2, D->rowstride * 2);
+  M4B_LAUNCHED();
+}
+
+// ---------------------------------------------------------------------------
+// input generation and checksum (harness support)
+// ---------------------------------------------------------------------------
+__host__ __device__ static inline uint64_t mix64(uint64_t z) {
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+  return z ^ (z >> 31);
+}
+
+__global__ void fill_random_kernel(word *d, int nrows, int width, int rs, uint64_t seed, word hm) {
+  long long total = (long long)nrows * width;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    int r = (int)(i / width), w = (int)(i % width);
+    word z = mix64(seed + (uint64_t)(i + 1) * 0x9E3779B97F4A7C15ULL);
+    if (w == width - 1) z &= hm;
+    d[(size_t)r * rs + w] = z;
+  }
+}
+
+void k_fill_random(DMat *M, uint64_t seed, cudaStream_t s) {
+  if (M->nrows == 0 || M->width == 0) return;
+  long long total = (long long)M->nrows * M->width;
+  unsigned grid = (unsigned)min((long long)cdiv(total, 256), (long long)sm_count() * 16);
+  fill_random_kernel<<<grid, 256, 0, s>>>(M->d, M->nrows, M->width, M->rowstride, seed,
+                                          high_mask(M->ncols));
+  M4B_LAUNCHED();
+}
+
+__global__ void checksum_kernel(const word *d, int nrows, int width, int rs,
+                                unsigned long long *out) {
+  long long total = (long long)nrows * width;
+  uint64_t acc = 0;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    int r = (int)(i / width), w = (int)(i % width);
+    acc ^= mix64(d[(size_t)r * rs + w] + (uint64_t)(i + 1) * 0x9E3779B97F4A7C15ULL);
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) acc ^= __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0 && acc) atomicXor(out, (unsigned long long)acc);
+}
+
+uint64_t k_checksum(const DMat *M, cudaStream_t s) {
+  unsigned long long *dout, h = 0;
+  M4B_CUDA(cudaMallocAsync(&dout, 8, s));
+  M4B_CUDA(cudaMemsetAsync(dout, 0, 8, s));
+  long long total = (long long)M->nrows * M->width;
+  if (total) {
+    unsigned grid = (unsigned)min((long long)cdiv(total, 256), (long long)sm_count() * 16);
+    checksum_kernel<<<grid, 256, 0, s>>>(M->d, M->nrows, M->width, M->rowstride, dout);
+    M4B_LAUNCHED();
+  }
+  M4B_CUDA(cudaMemcpyAsync(&h, dout, 8, cudaMemcpyDeviceToHost, s));
+  M4B_CUDA(cudaFreeAsync(dout, s));
+  M4B_CUDA(cudaStreamSynchronize(s));
+  return h;
+}
+
+// ---------------------------------------------------------------------------
+// mat-vec: y (^)= A*x, packed vector in, packed vector out. G lanes share a row
+// (G = 32 for long rows, fewer for short ones so every lane still moves 16 B).
+// HBM-bound: algorithmic bytes = 8 * (m*width + width) + ceil(m/64)*8.
+// ---------------------------------------------------------------------------
+template <int G>
+__global__ void __launch_bounds__(256)
+mul_v_kernel(uint32_t *__restrict__ y, const ulonglong2 *__restrict__ A,
+             const ulonglong2 *__restrict__ x, int m, int wv /*16B vectors per row*/,
+             int as /*row stride in 16B vectors*/) {
+  const int lane = threadIdx.x & 31;
+  const int g = lane / G, gl = lane % G;
+  constexpr int RPW = 32 / G;  // rows per warp
+  long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  long long row = warp * RPW + g;
+  uint64_t acc = 0;
+  if (row < m) {
+    const ulonglong2 *arow = A + (size_t)row * as;
+#pragma unroll 4
+    for (int w = gl; w < wv; w += G) {
+      ulonglong2 a = arow[w];
+      ulonglong2 b = __ldg(&x[w]);
+      acc ^= (a.x & b.x) ^ (a.y & b.y);
+    }
+  }
+#pragma unroll
+  for (int o = G / 2; o; o >>= 1) acc ^= __shfl_xor_sync(0xffffffffu, acc, o);
+  unsigned bit = (row < m) && gl == 0 && (__popcll(acc) & 1);
+  unsigned ball = __ballot_sync(0xffffffffu, bit);
+  if (lane == 0) {
+    // compress the leader bits (lanes 0, G, 2G, ...) into RPW consecutive bits
+    unsigned bits = 0;
+#pragma unroll
+    for (int i = 0; i < RPW; i++) bits |= ((ball >> (i * G)) & 1u) << i;
+    long long r0 = warp * RPW;
+    if (bits) atomicXor(&y[r0 >> 5], bits << (r0 & 31));
+  }
+}
+
+void k_mul_v(DMat *y, const DMat *A, const DMat *x, int clear, cudaStream_t s) {
+  if (clear) k_zero(y, s);
+  if (A->nrows == 0 || A->ncols == 0) return;
+  if (A->rowstride % 2 || ((uintptr_t)A->d % 16) || ((uintptr_t)x->d % 16))
+    die("m4ri_b200: mul_v needs 16-byte aligned rows\n");
+  // x is read in 16-byte vectors up to ceil(width/2): its row is padded to an even stride.
+  int wv = (A->width + 1) / 2, as = A->rowstride / 2;
+  int G = wv >= 32 ? 32 : wv >= 16 ? 16 : wv >= 8 ? 8 : wv >= 4 ? 4 : wv >= 2 ? 2 : 1;
+  long long warps = cdiv(A->nrows, 32 / G);
+  unsigned grid = cdiv(warps * 32, 256);
+  uint32_t *yy = (uint32_t *)y->d;
+  const ulonglong2 *AA = (const ulonglong2 *)A->d, *xx = (const ulonglong2 *)x->d;
+  switch (G) {
+    case 32: mul_v_kernel<32><<<grid, 256, 0, s>>>(yy, AA, xx, A->nrows, wv, as); break;
+    case 16: mul_v_kernel<16><<<grid, 256, 0, s>>>(yy, AA, xx, A->nrows, wv, as); break;
+    case 8: mul_v_kernel<8><<<grid, 256, 0, s>>>(yy, AA, xx, A->nrows, wv, as); break;
+    case 4: mul_v_kernel<4><<<grid, 256, 0, s>>>(yy, AA, xx, A->nrows, wv, as); break;
+    case 2: mul_v_kernel<2><<<grid, 256, 0, s>>>(yy, AA, xx, A->nrows, wv, as); break;
+    default: mul_v_kernel<1><<<grid, 256, 0, s>>>(yy, AA, xx, A->nrows, wv, as); break;
+  }
+  M4B_LAUNCHED();
+}
+
+// ---------------------------------------------------------------------------
+// vec-mat: C (^)= v*A = XOR of the rows of A selected by the bits of v.
+// grid = (column chunks, k chunks, rows of v); partial XORs merge with atomicXor.
+// ---------------------------------------------------------------------------
+constexpr int VA_ROWS = 256;
+__global__ void __launch_bounds__(256)
+mul_va_kernel(word *__restrict__ C, const word *__restrict__ v, const word *__restrict__ A, int k,
+              int width, int cs, int vs, int as) {
+  int w = blockIdx.x * blockDim.x + threadIdx.x;
+  int l0 = blockIdx.y * VA_ROWS, l1 = min(k, l0 + VA_ROWS);
+  int i = blockIdx.z;
+  if (w >= width) return;
+  word acc = 0;
+  for (int lw = l0; lw < l1; lw += 64) {
+    word bits = v[(size_t)i * vs + lw / 64];
+    int cnt = min(64, l1 - lw);
+    if (cnt < 64) bits &= (((word)1 << cnt) - 1);
+    while (bits) {
+      int b = __ffsll((long long)bits) - 1;
+      bits &= bits - 1;
+      acc ^= A[(size_t)(lw + b) * as + w];
+    }
+  }
+  if (acc) atomicXor((unsigned long long *)&C[(size_t)i * cs + w], (unsigned long long)acc);
+}
+
+void k_mul_va(DMat *C, const DMat *v, const DMat *A, int clear, cudaStream_t s) {
+  if (clear) k_zero(C, s);
+  if (v->nrows == 0 || A->nrows == 0 || A->ncols == 0) return;
+  dim3 grid(cdiv(A->width, 256), cdiv(A->nrows, VA_ROWS), v->nrows);
+  mul_va_kernel<<<grid, 256, 0, s>>>(C->d, v->d, A->d, A->nrows, A->width, C->rowstride,
+                                     v->rowstride, A->rowstride);
+  M4B_LAUNCHED();
+}
+
+// ---------------------------------------------------------------------------
+// C (^)= A * Bt^T by AND + popcount parity: 64x64 output tile per CTA, 4x4
+// outputs per thread, k staged through shared memory 16 words at a time.
+// ---------------------------------------------------------------------------
+constexpr int SK = 16;
+__global__ void __launch_bounds__(256)
+mul_abt_simple_kernel(word *__restrict__ C, const word *__restrict__ A, const word *__restrict__ Bt,
+                      int m, int n, int kw, int cs, int as, int bs, int clear) {
+  __shared__ word As[64][SK + 1];
+  __shared__ word Bs[64][SK + 1];
+  __shared__ unsigned long long Cs[64];
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  const int i0 = blockIdx.y * 64, j0 = blockIdx.x * 64;
+  word acc[4][4];
+#pragma unroll
+  for (int a = 0; a < 4; a++)
+#pragma unroll
+    for (int b = 0; b < 4; b++) acc[a][b] = 0;
+  if (threadIdx.x < 64) Cs[threadIdx.x] = 0;
+  for (int k0 = 0; k0 < kw; k0 += SK) {
+    for (int idx = threadIdx.x; idx < 64 * SK; idx += 256) {
+      int r = idx / SK, c = idx % SK;
+      As[r][c] = (i0 + r < m && k0 + c < kw) ? A[(size_t)(i0 + r) * as + k0 + c] : 0;
+      Bs[r][c] = (j0 + r < n && k0 + c < kw) ? Bt[(size_t)(j0 + r) * bs + k0 + c] : 0;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < SK; kk++) {
+      word av[4], bv[4];
+#pragma unroll
+      for (int a = 0; a < 4; a++) av[a] = As[ty + 16 * a][kk];
+#pragma unroll
+      for (int b = 0; b < 4; b++) bv[b] = Bs[tx + 16 * b][kk];
+#pragma unroll
+      for (int a = 0; a < 4; a++)
+#pragma unroll
+        for (int b = 0; b < 4; b++) acc[a][b] ^= av[a] & bv[b];
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int a = 0; a < 4; a++) {
+    unsigned long long bits = 0;
+#pragma unroll
+    for (int b = 0; b < 4; b++)
+      bits |= (unsigned long long)(__popcll(acc[a][b]) & 1) << (tx + 16 * b);
+    if (bits) atomicOr(&Cs[ty + 16 * a], bits);
+  }
+  __syncthreads();
+  if (threadIdx.x < 64 && i0 + threadIdx.x < m) {
+    word *dst = &C[(size_t)(i0 + threadIdx.x) * cs + (j0 >> 6)];
+    *dst = clear ? Cs[threadIdx.x] : (*dst ^ Cs[threadIdx.x]);
+  }
+}
+
+void k_mul_abt_simple(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream_t s) {
+  if (C->nrows == 0 || C->ncols == 0) return;
+  if (A->ncols == 0) {
+    if (clear) k_zero(C, s);
+    return;
+  }
+  dim3 grid(cdiv(C->ncols, 64), cdiv(C->nrows, 64));
+  mul_abt_simple_kernel<<<grid, 256, 0, s>>>(C->d, A->d, Bt->d, C->nrows, C->ncols, A->width,
+                                             C->rowstride, A->rowstride, Bt->rowstride, clear);
+  M4B_LAUNCHED();
+}
+
+}  // namespace m4b

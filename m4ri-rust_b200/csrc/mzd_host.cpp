@@ -1,0 +1,228 @@
+// mzd_host.cpp — the allocator set of the C-ABI: host-side mzd_t management.
+//
+// These are the O(size) host-memory utilities m4ri-rust's BinMatrix needs around
+// the multiplication path (SURVEY 8b "must also export — because one allocator
+// must own every mzd_t the path touches"): construction, copy, compare, XOR-add
+// and transpose of HOST matrices. They move no data to the GPU because their
+// operands live in host memory and a PCIe round trip costs more than the work.
+// Every multiplication entry point is in api.cu and runs on the GPU.
+//
+// Layout contract (m4ri-sys/src/mzd.rs:24-79, checked by the reference tests at
+// mzd.rs:381-422): 64-byte descriptor, rows[i] == blocks[0].begin + offset_vector
+// + i*rowstride, rowstride = (width < 3 || width even) ? width : width + 1,
+// excess bits and padding words are zero.
+#include <string.h>
+
+#include <atomic>
+#include <mutex>
+
+#include "common.cuh"
+
+static_assert(sizeof(mzd_t) == 64, "mzd_t must be 64 bytes (m4ri-sys/src/mzd.rs:385)");
+static_assert(offsetof(mzd_t, high_bitmask) == 40 && offsetof(mzd_t, blocks) == 48 &&
+                  offsetof(mzd_t, rows) == 56 && offsetof(mzd_t, flags) == 24,
+              "mzd_t field offsets (m4ri-sys/src/mzd.rs:24-79)");
+
+namespace m4b {
+// how a matrix's words were allocated, kept in mzd_t::padding[0]
+enum : uint8_t { ALLOC_NONE = 0, ALLOC_MALLOC = 0xA1, ALLOC_PINNED = 0xA2 };
+// Matrices at least this large get page-locked memory so the H2D/D2H copies of a
+// product run at full PCIe rate; small ones (the reference's tests create
+// thousands of 10x10 matrices) stay in ordinary memory.
+constexpr size_t PINNED_MIN_BYTES = 256 * 1024;
+}  // namespace m4b
+
+using namespace m4b;
+
+extern "C" {
+
+mzd_t *mzd_init(rci_t r, rci_t c) {
+  if (r < 0 || c < 0) die("m4ri_b200: mzd_init(%d, %d): negative dimension\n", r, c);
+  mzd_t *A = (mzd_t *)calloc(1, sizeof(mzd_t));
+  if (!A) die("m4ri_b200: out of memory\n");
+  A->nrows = r;
+  A->ncols = c;
+  A->width = width_of(c);
+  A->rowstride = (A->width < 3 || (A->width & 1) == 0) ? A->width : A->width + 1;  // mzd.rs:35-37
+  A->high_bitmask = high_mask(c);
+  A->flags = (c % 64) ? mzd_flag_nonzero_excess : 0;
+  A->offset_vector = 0;
+  A->row_offset = 0;
+  int lg = 0;  // single block: blockrows = next power of two >= nrows
+  while (((rci_t)1 << lg) < (r > 0 ? r : 1)) lg++;
+  A->blockrows_log = (uint8_t)lg;
+
+  size_t words = (size_t)r * (size_t)A->rowstride;
+  size_t bytes = words * sizeof(word);
+  A->blocks = (mzd_block_t *)calloc(2, sizeof(mzd_block_t));  // [1] is the {0,NULL,NULL} terminator
+  A->rows = (word **)calloc((size_t)(r > 0 ? r : 1), sizeof(word *));
+  if (!A->blocks || !A->rows) die("m4ri_b200: out of memory\n");
+  word *data = nullptr;
+  uint8_t kind = ALLOC_MALLOC;
+  if (bytes >= PINNED_MIN_BYTES && m4ri_b200_device_count() > 0) {
+    if (cudaHostAlloc((void **)&data, bytes, cudaHostAllocPortable) == cudaSuccess) {
+      kind = ALLOC_PINNED;
+      memset(data, 0, bytes);
+    } else {
+      (void)cudaGetLastError();
+      data = nullptr;
+    }
+  }
+  if (!data) {
+    size_t alloc = bytes ? ((bytes + 63) & ~(size_t)63) : 64;
+    data = (word *)aligned_alloc(64, alloc);
+    if (!data) die("m4ri_b200: out of memory (%zu bytes)\n", bytes);
+    memset(data, 0, alloc);
+  }
+  A->padding[0] = kind;
+  A->blocks[0].size = bytes;
+  A->blocks[0].begin = data;
+  A->blocks[0].end = data + words;
+  for (rci_t i = 0; i < r; i++) A->rows[i] = data + (size_t)i * A->rowstride;
+  return A;
+}
+
+void mzd_free(mzd_t *A) {
+  if (!A) return;
+  if (A->blocks && A->padding[0] != ALLOC_NONE) {
+    if (A->padding[0] == ALLOC_PINNED) cudaFreeHost(A->blocks[0].begin);
+    else free(A->blocks[0].begin);
+    free(A->blocks);
+  }
+  free(A->rows);
+  free(A);
+}
+
+// Window = view sharing the parent's words (mzd.rs:121-127); lowc % 64 == 0.
+mzd_t *mzd_init_window(mzd_t *M, rci_t lowr, rci_t lowc, rci_t highr, rci_t highc) {
+  if (lowc % 64) die("m4ri_b200: mzd_init_window: lowc must be a multiple of 64\n");
+  if (lowr < 0 || highr > M->nrows || lowr > highr || lowc < 0 || highc > M->ncols || lowc > highc)
+    die("m4ri_b200: mzd_init_window: window out of range\n");
+  mzd_t *W = (mzd_t *)calloc(1, sizeof(mzd_t));
+  if (!W) die("m4ri_b200: out of memory\n");
+  W->nrows = highr - lowr;
+  W->ncols = highc - lowc;
+  W->width = width_of(W->ncols);
+  W->rowstride = M->rowstride;
+  W->high_bitmask = high_mask(W->ncols);
+  W->flags = mzd_flag_windowed_zerooffset |
+             ((W->ncols % 64) ? mzd_flag_nonzero_excess : mzd_flag_windowed_zeroexcess);
+  W->blockrows_log = M->blockrows_log;
+  W->row_offset = M->row_offset + lowr;
+  W->offset_vector = M->offset_vector + lowr * M->rowstride + lowc / 64;
+  W->blocks = M->blocks;  // shared, not owned
+  W->padding[0] = ALLOC_NONE;
+  W->rows = (word **)calloc((size_t)(W->nrows > 0 ? W->nrows : 1), sizeof(word *));
+  if (!W->rows) die("m4ri_b200: out of memory\n");
+  for (rci_t i = 0; i < W->nrows; i++) W->rows[i] = M->rows[lowr + i] + lowc / 64;
+  return W;
+}
+
+mzd_t *mzd_copy(mzd_t *N, const mzd_t *P) {
+  if (N == P) return N;
+  if (!N) N = mzd_init(P->nrows, P->ncols);
+  else if (N->nrows < P->nrows || N->ncols < P->ncols)
+    die("m4ri_b200: mzd_copy: target matrix is too small\n");
+  if (P->width == 0) return N;
+  word hm = P->high_bitmask;
+  for (rci_t i = 0; i < P->nrows; i++) {
+    const word *src = P->rows[i];
+    word *dst = N->rows[i];
+    memcpy(dst, src, sizeof(word) * (size_t)(P->width - 1));
+    // keep the target's bits beyond P's last column (it may be wider)
+    dst[P->width - 1] = (dst[P->width - 1] & ~hm) | (src[P->width - 1] & hm);
+  }
+  return N;
+}
+
+int mzd_equal(const mzd_t *A, const mzd_t *B) {
+  if (A->nrows != B->nrows || A->ncols != B->ncols) return 0;
+  if (A == B || A->width == 0) return 1;
+  word hm = A->high_bitmask;
+  for (rci_t i = 0; i < A->nrows; i++) {
+    const word *a = A->rows[i], *b = B->rows[i];
+    if (memcmp(a, b, sizeof(word) * (size_t)(A->width - 1)) != 0) return 0;
+    if ((a[A->width - 1] ^ b[A->width - 1]) & hm) return 0;
+  }
+  return 1;
+}
+
+// value odd: identity on the main diagonal; value even: zero matrix (mzd.rs:198).
+void mzd_set_ui(mzd_t *A, unsigned int value) {
+  for (rci_t i = 0; i < A->nrows; i++) memset(A->rows[i], 0, sizeof(word) * (size_t)A->width);
+  if (value & 1) {
+    rci_t d = A->nrows < A->ncols ? A->nrows : A->ncols;
+    for (rci_t i = 0; i < d; i++) A->rows[i][i / 64] |= m4ri_one << (i % 64);
+  }
+}
+
+// Uniform bits, NOT stream-compatible with M4RI's generator (which the reference
+// never relies on: SURVEY 8c). splitmix64 over a process-wide counter.
+static std::atomic<uint64_t> g_rand_state{0x4D345249B200ULL};
+void mzd_randomize(mzd_t *A) {
+  if (A->width == 0) return;
+  uint64_t words = (uint64_t)A->nrows * (uint64_t)A->width;
+  uint64_t base = g_rand_state.fetch_add(words * 0x9E3779B97F4A7C15ULL);
+  for (rci_t i = 0; i < A->nrows; i++) {
+    word *row = A->rows[i];
+    for (wi_t w = 0; w < A->width; w++) {
+      uint64_t z = (base += 0x9E3779B97F4A7C15ULL);
+      z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+      z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+      row[w] = z ^ (z >> 31);
+    }
+    row[A->width - 1] &= A->high_bitmask;
+  }
+}
+
+// 64x64 bit-block transpose (recursive swap network).
+static inline void transpose64(word x[64]) {
+  word m = 0x00000000FFFFFFFFULL;
+  for (int j = 32; j; j >>= 1, m ^= m << j)
+    for (int k = 0; k < 64; k = (k + j + 1) & ~j) {
+      word t = ((x[k] >> j) ^ x[k + j]) & m;
+      x[k] ^= t << j;
+      x[k + j] ^= t;
+    }
+}
+
+mzd_t *mzd_transpose(mzd_t *DST, const mzd_t *A) {
+  if (!DST) DST = mzd_init(A->ncols, A->nrows);
+  else if (DST->nrows != A->ncols || DST->ncols != A->nrows)
+    die("m4ri_b200: mzd_transpose: wrong size for return matrix\n");
+  if (DST == A) die("m4ri_b200: mzd_transpose: in-place transpose is not supported\n");
+  word blk[64];
+  for (rci_t r0 = 0; r0 < A->nrows; r0 += 64) {
+    int nr = A->nrows - r0 < 64 ? A->nrows - r0 : 64;
+    for (wi_t w = 0; w < A->width; w++) {
+      for (int i = 0; i < nr; i++) blk[i] = A->rows[r0 + i][w];
+      for (int i = nr; i < 64; i++) blk[i] = 0;
+      if (w == A->width - 1)
+        for (int i = 0; i < nr; i++) blk[i] &= A->high_bitmask;
+      transpose64(blk);
+      int nc = A->ncols - w * 64 < 64 ? A->ncols - w * 64 : 64;
+      for (int j = 0; j < nc; j++) DST->rows[w * 64 + j][r0 / 64] = blk[j];
+    }
+  }
+  return DST;
+}
+
+mzd_t *mzd_add(mzd_t *C, const mzd_t *A, const mzd_t *B) {
+  if (A->nrows != B->nrows || A->ncols != B->ncols)
+    die("m4ri_b200: mzd_add: rows and columns must match\n");
+  if (!C) C = mzd_init(A->nrows, A->ncols);
+  else if (C->nrows != A->nrows || C->ncols != A->ncols)
+    die("m4ri_b200: mzd_add: rows and columns of returned matrix must match\n");
+  if (A->width == 0) return C;
+  for (rci_t i = 0; i < A->nrows; i++) {
+    const word *a = A->rows[i], *b = B->rows[i];
+    word *c = C->rows[i];  // may alias a (binary_matrix.rs:497-523)
+    for (wi_t w = 0; w < A->width; w++) c[w] = a[w] ^ b[w];
+    c[A->width - 1] &= A->high_bitmask;
+  }
+  return C;
+}
+
+mzd_t *mzd_sub(mzd_t *C, const mzd_t *A, const mzd_t *B) { return mzd_add(C, A, B); }
+
+}  // extern "C"

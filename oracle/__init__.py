@@ -1,0 +1,163 @@
+"""ctypes loader for the CPU oracle (oracle/gf2_oracle.c).
+
+TEST INFRASTRUCTURE ONLY. May be imported by tests/, __graft_entry__.smoke() and
+bench.py's cpu_baseline / --impl reference legs, never by the product package.
+Matrices are numpy uint64 arrays of shape [nrows, stride] (64-bit words,
+LSB-first, row-major: m4ri-sys/src/mzd.rs:263-269 in the reference).
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "_build", "libgf2_oracle.so")
+_lib = None
+
+
+def build(force=False):
+    src = os.path.join(_HERE, "gf2_oracle.c")
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-s", "all"] + (["-B"] if force else []))
+    return _SO
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO):
+            build()
+        _lib = ctypes.CDLL(_SO)
+        u64p, i, u64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_uint64
+        sig = {
+            "oracle_fill_random": (None, [u64p, i, i, i, u64]),
+            "oracle_checksum": (u64, [u64p, i, i, i]),
+            "oracle_mul_naive": (None, [u64p, i, u64p, i, u64p, i, i, i, i, i]),
+            "oracle_mul_m4rm": (None, [u64p, i, u64p, i, u64p, i, i, i, i, i, i]),
+            "oracle_mul_abt": (None, [u64p, i, u64p, i, u64p, i, i, i, i, i]),
+            "oracle_mul_va": (None, [u64p, i, u64p, i, u64p, i, i, i, i, i]),
+            "oracle_mul_v": (None, [u64p, u64p, i, u64p, i, i, i]),
+            "oracle_transpose": (None, [u64p, i, u64p, i, i, i]),
+            "oracle_add": (None, [u64p, i, u64p, i, u64p, i, i, i]),
+            "oracle_freivalds": (i, [u64p, i, u64p, i, u64p, i, i, i, i, u64]),
+            "oracle_max_threads": (i, []),
+        }
+        for name, (res, args) in sig.items():
+            f = getattr(_lib, name)
+            f.restype, f.argtypes = res, args
+    return _lib
+
+
+def width(ncols):
+    return (ncols + 63) // 64
+
+
+def m4ri_rowstride(ncols):
+    """rowstride rule of the reference: m4ri-sys/src/mzd.rs:35-37 (paddingwidth 3)."""
+    w = width(ncols)
+    return w if (w < 3 or w % 2 == 0) else w + 1
+
+
+def zeros(nrows, ncols, stride=None):
+    return np.zeros((nrows, stride or m4ri_rowstride(ncols)), dtype=np.uint64)
+
+
+def _p(a):
+    assert a.dtype == np.uint64 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data
+
+
+def random(nrows, ncols, seed, stride=None):
+    m = zeros(nrows, ncols, stride)
+    lib().oracle_fill_random(_p(m), nrows, ncols, m.shape[1], seed)
+    return m
+
+
+def checksum(M, ncols):
+    return int(lib().oracle_checksum(_p(M), M.shape[0], ncols, M.shape[1]))
+
+
+def mul_naive(A, B, k, n, C=None):
+    m = A.shape[0]
+    clear = C is None
+    C = zeros(m, n) if C is None else C
+    lib().oracle_mul_naive(_p(C), C.shape[1], _p(A), A.shape[1], _p(B), B.shape[1], m, k, n, int(clear))
+    return C
+
+
+def mul_m4rm(A, B, k, n, C=None, threads=1):
+    m = A.shape[0]
+    clear = C is None
+    C = zeros(m, n) if C is None else C
+    lib().oracle_mul_m4rm(_p(C), C.shape[1], _p(A), A.shape[1], _p(B), B.shape[1], m, k, n, int(clear), threads)
+    return C
+
+
+def mul_abt(A, Bt, k, C=None):
+    m, n = A.shape[0], Bt.shape[0]
+    clear = C is None
+    C = zeros(m, n) if C is None else C
+    lib().oracle_mul_abt(_p(C), C.shape[1], _p(A), A.shape[1], _p(Bt), Bt.shape[1], m, k, n, int(clear))
+    return C
+
+
+def mul_va(v, A, k, n, C=None):
+    r = v.shape[0]
+    clear = C is None
+    C = zeros(r, n) if C is None else C
+    lib().oracle_mul_va(_p(C), C.shape[1], _p(v), v.shape[1], _p(A), A.shape[1], r, k, n, int(clear))
+    return C
+
+
+def mul_v(A, x, n, y=None):
+    """y = A*x with x, y packed rows (1-D uint64 arrays)."""
+    m = A.shape[0]
+    clear = y is None
+    y = np.zeros(width(m), dtype=np.uint64) if y is None else y
+    lib().oracle_mul_v(_p(y), _p(A), A.shape[1], _p(np.ascontiguousarray(x)), m, n, int(clear))
+    return y
+
+
+def transpose(S, ncols):
+    nrows = S.shape[0]
+    D = zeros(ncols, nrows)
+    lib().oracle_transpose(_p(D), D.shape[1], _p(S), S.shape[1], nrows, ncols)
+    return D
+
+
+def add(A, B, ncols):
+    C = zeros(A.shape[0], ncols)
+    lib().oracle_add(_p(C), C.shape[1], _p(A), A.shape[1], _p(B), B.shape[1], A.shape[0], ncols)
+    return C
+
+
+def freivalds(C, A, B, k, n, seed=0xF5E1):
+    return bool(lib().oracle_freivalds(_p(C), C.shape[1], _p(A), A.shape[1], _p(B), B.shape[1], A.shape[0], k, n, seed))
+
+
+def max_threads():
+    return int(lib().oracle_max_threads())
+
+
+def get_bit(M, r, c):
+    return int((int(M[r, c // 64]) >> (c % 64)) & 1)
+
+
+def from_bits(bits):
+    """bits: 2-D array-like of 0/1 -> packed matrix with the reference's rowstride."""
+    bits = np.asarray(bits, dtype=np.uint8)
+    nrows, ncols = bits.shape
+    M = zeros(nrows, ncols)
+    for r in range(nrows):
+        for c in np.flatnonzero(bits[r]):
+            M[r, c // 64] |= np.uint64(1) << np.uint64(c % 64)
+    return M
+
+
+def to_bits(M, ncols):
+    nrows = M.shape[0]
+    out = np.zeros((nrows, ncols), dtype=np.uint8)
+    for c in range(ncols):
+        out[:, c] = (M[:, c // 64] >> np.uint64(c % 64)) & np.uint64(1)
+    return out

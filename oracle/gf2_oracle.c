@@ -1,0 +1,279 @@
+/*
+ * gf2_oracle.c — CPU restatement of the GF(2) multiplication path of M4RI as
+ * m4ri-rust uses it. TEST INFRASTRUCTURE ONLY: it may be imported, linked or
+ * executed only by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+ * `--impl reference` legs, and only as the checker or the timed CPU baseline.
+ * The product (libm4ri_b200.so) never links or calls anything in this file.
+ *
+ * PARITY STATUS: "parity unpinned" for non-identity products. The arithmetic the
+ * reference runs lives in a third-party C library that is absent from
+ * /root/reference: M4RI, fork bitbucket.org/thomwiggers/m4ri pinned at commit
+ * 5cd604d29068651c23265e94ccd785a821c3dfe6 (.gitmodules:1-3; the vendor directory
+ * m4ri-sys/vendor/m4ri is empty), and the reference's own tests hold only
+ * identity products (m4ri-rust/src/friendly/binary_matrix.rs:661-686), which
+ * tests/test_oracle.py replays against this file. What makes parity well defined
+ * anyway: a product over GF(2) is a unique mathematical object (no rounding, no
+ * order dependence, independent of M4RI's `cutoff`/`k`), so this file restates
+ * the published semantics twice — from the definition (oracle_mul_naive) and as
+ * the published Method of the Four Russians (oracle_mul_m4rm: Gray-code tables
+ * of 2^8 row combinations per 8-row slab of B, one table lookup + XOR per row of
+ * A; mechanism documented at m4ri-sys/src/brilliantrussian.rs:17-193) — and the
+ * tests prove the two agree.
+ *
+ * Semantics followed (all file:line relative to /root/reference):
+ *   bit order  (r,c) = (row[c/64] >> (c%64)) & 1      m4ri-sys/src/mzd.rs:263-269
+ *   width / rowstride / high_bitmask                    m4ri-sys/src/mzd.rs:26-39,73-74
+ *   C = A*B, C ^= A*B                                   m4ri-sys/src/strassen.rs:18,31
+ *                                                       m4ri-sys/src/brilliantrussian.rs:216,224
+ *   C (^)= A*Bt^T with `clear`                          m4ri-sys/src/mzd.rs:154-168
+ *   C (^)= v*A with `clear`                             m4ri-sys/src/mzd.rs:175-181
+ *   transpose, add                                      m4ri-sys/src/mzd.rs:148,223
+ *
+ * Matrices are plain arrays of 64-bit words, row-major, `stride` words per row,
+ * `ncols` valid bits per row; bits beyond ncols are kept zero on output.
+ */
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+typedef uint64_t word;
+
+static inline int width_of(int ncols) { return (ncols + 63) / 64; }
+static inline word high_mask(int ncols) {
+  int r = ncols % 64;
+  return r ? (((word)1 << r) - 1) : ~(word)0;
+}
+
+/* ---- deterministic input generator ---------- */
+static inline word splitmix64_at(uint64_t seed, uint64_t index) {
+  /* the index-th output (0-based) of splitmix64 started at `seed` */
+  word z = seed + (index + 1) * 0x9E3779B97F4A7C15ULL;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+  return z ^ (z >> 31);
+}
+
+/* word (r,w) of the matrix = splitmix64 output number r*width + w; last word masked */
+void oracle_fill_random(word *M, int nrows, int ncols, int stride, uint64_t seed) {
+  int width = width_of(ncols);
+  word hm = high_mask(ncols);
+  for (int r = 0; r < nrows; r++) {
+    word *row = M + (size_t)r * stride;
+    for (int w = 0; w < width; w++) row[w] = splitmix64_at(seed, (uint64_t)r * width + w);
+    if (width) row[width - 1] &= hm;
+    for (int w = width; w < stride; w++) row[w] = 0;
+  }
+}
+
+/* position-mixed XOR fold over the valid words; padding words are ignored */
+uint64_t oracle_checksum(const word *M, int nrows, int ncols, int stride) {
+  int width = width_of(ncols);
+  uint64_t acc = 0;
+  for (int r = 0; r < nrows; r++)
+    for (int w = 0; w < width; w++) {
+      word z = M[(size_t)r * stride + w] + ((uint64_t)r * width + w + 1) * 0x9E3779B97F4A7C15ULL;
+      z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+      z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+      acc ^= z ^ (z >> 31);
+    }
+  return acc;
+}
+
+static inline int get_bit(const word *M, int stride, int r, int c) {
+  return (int)((M[(size_t)r * stride + c / 64] >> (c % 64)) & 1);
+}
+
+static void clear_or_mask(word *C, int cs, int m, int n, int clear) {
+  int width = width_of(n);
+  word hm = high_mask(n);
+  for (int i = 0; i < m; i++) {
+    word *row = C + (size_t)i * cs;
+    if (clear) memset(row, 0, sizeof(word) * (size_t)width);
+    else if (width) row[width - 1] &= hm;
+  }
+}
+
+/* ---- from the definition: C[i,j] (^)= XOR_l A[i,l] & B[l,j] ------------------ */
+void oracle_mul_naive(word *C, int cs, const word *A, int as, const word *B, int bs, int m, int k,
+                      int n, int clear) {
+  clear_or_mask(C, cs, m, n, clear);
+  for (int i = 0; i < m; i++)
+    for (int j = 0; j < n; j++) {
+      int acc = 0;
+      for (int l = 0; l < k; l++) acc ^= get_bit(A, as, i, l) & get_bit(B, bs, l, j);
+      if (acc) C[(size_t)i * cs + j / 64] ^= (word)1 << (j % 64);
+    }
+}
+
+/* ---- Method of the Four Russians, t = 8, four tables (32 bits of k) per pass --
+ * Column blocks of C are independent, so threads split the columns: every
+ * thread builds the tables of its own block and nothing is computed twice.   */
+#define ORACLE_CB 16 /* words per column block: 1024 columns */
+void oracle_mul_m4rm(word *C, int cs, const word *A, int as, const word *B, int bs, int m, int k,
+                     int n, int clear, int nthreads) {
+  clear_or_mask(C, cs, m, n, clear);
+  int width = width_of(n);
+  int nblocks = (width + ORACLE_CB - 1) / ORACLE_CB;
+  word hm = high_mask(n);
+#ifdef _OPENMP
+  if (nthreads <= 0) nthreads = omp_get_max_threads();
+#else
+  nthreads = 1;
+#endif
+#pragma omp parallel num_threads(nthreads)
+  {
+    word(*T)[256][ORACLE_CB] = aligned_alloc(64, sizeof(word) * 4 * 256 * ORACLE_CB);
+#pragma omp for schedule(dynamic, 1)
+    for (int cb = 0; cb < nblocks; cb++) {
+      int w0 = cb * ORACLE_CB;
+      int wn = width - w0 < ORACLE_CB ? width - w0 : ORACLE_CB;
+      for (int k0 = 0; k0 < k; k0 += 32) {
+        int kb = k - k0 < 32 ? k - k0 : 32;
+        int ntab = (kb + 7) / 8;
+        for (int t = 0; t < ntab; t++) {
+          /* entry e = XOR of the rows k0+8t+b of B for the set bits b of e, built
+           * from the entry with the lowest set bit removed (one XOR per entry) */
+          memset(T[t][0], 0, sizeof(word) * ORACLE_CB);
+          for (int e = 1; e < 256; e++) {
+            int b = __builtin_ctz(e);
+            int row = k0 + 8 * t + b;
+            const word *prev = T[t][e & (e - 1)];
+            if (row < k) {
+              const word *brow = B + (size_t)row * bs + w0;
+              for (int w = 0; w < wn; w++) T[t][e][w] = prev[w] ^ brow[w];
+            } else {
+              for (int w = 0; w < wn; w++) T[t][e][w] = prev[w];
+            }
+          }
+        }
+        word kmask = kb == 32 ? 0xffffffffULL : (((word)1 << kb) - 1);
+        for (int i = 0; i < m; i++) {
+          word a = (A[(size_t)i * as + k0 / 64] >> (k0 % 64)) & kmask;
+          if (!a) continue;
+          word *crow = C + (size_t)i * cs + w0;
+          const word *t0 = T[0][a & 255];
+          if (ntab == 4) {
+            const word *t1 = T[1][(a >> 8) & 255], *t2 = T[2][(a >> 16) & 255],
+                       *t3 = T[3][(a >> 24) & 255];
+            for (int w = 0; w < wn; w++) crow[w] ^= t0[w] ^ t1[w] ^ t2[w] ^ t3[w];
+          } else {
+            for (int w = 0; w < wn; w++) crow[w] ^= t0[w];
+            for (int t = 1; t < ntab; t++) {
+              const word *tt = T[t][(a >> (8 * t)) & 255];
+              for (int w = 0; w < wn; w++) crow[w] ^= tt[w];
+            }
+          }
+        }
+      }
+      if (w0 + wn == width)
+        for (int i = 0; i < m; i++) C[(size_t)i * cs + width - 1] &= hm;
+    }
+    free(T);
+  }
+}
+
+/* ---- C (^)= A * Bt^T, both operands k-contiguous (mzd.rs:154-168) ------------ */
+void oracle_mul_abt(word *C, int cs, const word *A, int as, const word *Bt, int bts, int m, int k,
+                    int n, int clear) {
+  clear_or_mask(C, cs, m, n, clear);
+  int kw = width_of(k);
+  word km = high_mask(k);
+  for (int i = 0; i < m; i++)
+    for (int j = 0; j < n; j++) {
+      word acc = 0;
+      for (int w = 0; w < kw; w++) {
+        word x = A[(size_t)i * as + w] & Bt[(size_t)j * bts + w];
+        if (w == kw - 1) x &= km;
+        acc ^= x;
+      }
+      if (__builtin_parityll(acc)) C[(size_t)i * cs + j / 64] ^= (word)1 << (j % 64);
+    }
+}
+
+/* ---- C (^)= v * A, v is r x k with few rows (mzd.rs:175-181) ----------------- */
+void oracle_mul_va(word *C, int cs, const word *v, int vs, const word *A, int as, int r, int k,
+                   int n, int clear) {
+  clear_or_mask(C, cs, r, n, clear);
+  int width = width_of(n);
+  word hm = high_mask(n);
+  for (int i = 0; i < r; i++) {
+    word *crow = C + (size_t)i * cs;
+    for (int l = 0; l < k; l++)
+      if (get_bit(v, vs, i, l)) {
+        const word *arow = A + (size_t)l * as;
+        for (int w = 0; w < width; w++) crow[w] ^= arow[w];
+      }
+    if (width) crow[width - 1] &= hm;
+  }
+}
+
+/* ---- y (^)= A * x, x and y packed rows (x: n bits, y: m bits) ---------------- */
+void oracle_mul_v(word *y, const word *A, int as, const word *x, int m, int n, int clear) {
+  int nw = width_of(n), mw = width_of(m);
+  word nm = high_mask(n);
+  if (clear) memset(y, 0, sizeof(word) * (size_t)mw);
+  for (int i = 0; i < m; i++) {
+    word acc = 0;
+    for (int w = 0; w < nw; w++) {
+      word t = A[(size_t)i * as + w] & x[w];
+      if (w == nw - 1) t &= nm;
+      acc ^= t;
+    }
+    if (__builtin_parityll(acc)) y[i / 64] ^= (word)1 << (i % 64);
+  }
+}
+
+/* ---- D = S^T (mzd.rs:148) and C = A ^ B (mzd.rs:223) ------------------------- */
+void oracle_transpose(word *D, int ds, const word *S, int ss, int nrows, int ncols) {
+  for (int j = 0; j < ncols; j++) memset(D + (size_t)j * ds, 0, sizeof(word) * (size_t)width_of(nrows));
+  for (int i = 0; i < nrows; i++)
+    for (int j = 0; j < ncols; j++)
+      if (get_bit(S, ss, i, j)) D[(size_t)j * ds + i / 64] |= (word)1 << (i % 64);
+}
+
+void oracle_add(word *C, int cs, const word *A, int as, const word *B, int bs, int nrows,
+                int ncols) {
+  int width = width_of(ncols);
+  word hm = high_mask(ncols);
+  for (int i = 0; i < nrows; i++) {
+    for (int w = 0; w < width; w++)
+      C[(size_t)i * cs + w] = A[(size_t)i * as + w] ^ B[(size_t)i * bs + w];
+    if (width) C[(size_t)i * cs + width - 1] &= hm;
+  }
+}
+
+/* ---- Freivalds over GF(2): A*(B*X) == C*X for 64 random vectors packed in X ---
+ * X is n x 64 (one word per row of X). Returns 1 when equal. O(mk + kn + mn). */
+static void mat_times_x(word *out, const word *M, int ms, int rows, int cols, const word *X) {
+  for (int i = 0; i < rows; i++) {
+    word acc = 0;
+    const word *row = M + (size_t)i * ms;
+    for (int j = 0; j < cols; j++)
+      if ((row[j / 64] >> (j % 64)) & 1) acc ^= X[j];
+    out[i] = acc;
+  }
+}
+
+int oracle_freivalds(const word *C, int cs, const word *A, int as, const word *B, int bs, int m,
+                     int k, int n, uint64_t seed) {
+  word *X = malloc(sizeof(word) * (size_t)n), *BX = malloc(sizeof(word) * (size_t)k),
+       *ABX = malloc(sizeof(word) * (size_t)m), *CX = malloc(sizeof(word) * (size_t)m);
+  for (int j = 0; j < n; j++) X[j] = splitmix64_at(seed, (uint64_t)j);
+  mat_times_x(BX, B, bs, k, n, X);
+  mat_times_x(ABX, A, as, m, k, BX);
+  mat_times_x(CX, C, cs, m, n, X);
+  int ok = memcmp(ABX, CX, sizeof(word) * (size_t)m) == 0;
+  free(X); free(BX); free(ABX); free(CX);
+  return ok;
+}
+
+int oracle_max_threads(void) {
+#ifdef _OPENMP
+  return omp_get_max_threads();
+#else
+  return 1;
+#endif
+}
