@@ -1,0 +1,310 @@
+#!/usr/bin/env python
+"""bench.py — GF(2) mzd_mul throughput on B200 (BASELINE.json's metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                    [--n SIZE] [--algo auto|m4rm|mma]
+
+A step is one product C = A*B over GF(2) on synthetic uniform random bits.
+  N = 1 : square n = 32768 (BASELINE configs[2], the size the metric is quoted on).
+  N > 1 : square n = 65536 (configs[3]): C/A row-blocks sharded over the ranks, B
+          broadcast from rank 0 by NCCL inside every timed step (the path's one
+          exchange step), one process per GPU under torchrun.
+`value` = effective bit-ops 2*m*k*n of the whole job / device time (operands
+resident in HBM); `e2e` = the same through the reference-facing C-ABI call
+mzd_mul(NULL, A, B, 0) on HOST mzd_t operands (H2D + kernels + D2H inside the
+timed region). Prints ONE JSON line on rank 0.
+
+--impl reference times the CPU arm: M4RI itself is an absent submodule of the
+reference (DESIGN.md "Oracle"), so the arm is the repo's C restatement of the
+Method of the Four Russians (oracle/, kind "port") on all host threads, on a
+bounded row sample of the same workload.
+"""
+import argparse
+import ctypes
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SEED_A, SEED_B = 0x4D345249 ^ (2 << 32) ^ 1, 0x4D345249 ^ (2 << 32) ^ 2
+METRIC = "GF(2) mzd_mul effective Tbit-op/s"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"],
+                "bf16_tflops_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "src": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "src": "fallback"}
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz, self._stop = index, [], set(), None, threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if not self.nv:
+            return
+        nv = self.nv
+        names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                 nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def stop(self):
+        self._stop.set()
+        self.join(timeout=2)
+        return {"sm_mhz": statistics.median(self.samples) if self.samples else None,
+                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def cpu_arm(n, m_total, steps, warmup, target_s=12.0):
+    """Times oracle_mul_m4rm (all host threads) on a bounded row sample of the
+    workload: the first `rows` rows of A against the full k x n B."""
+    import oracle
+    threads = oracle.max_threads()
+    B = oracle.random(n, n, SEED_B)
+    probe_rows = 256
+    A = oracle.random(probe_rows, n, SEED_A)
+    t0 = time.perf_counter()
+    oracle.mul_m4rm(A, B, n, n, threads=0)
+    t_probe = time.perf_counter() - t0
+    per_step = target_s / max(1, steps + warmup)
+    rows = int(min(m_total, max(256, probe_rows * per_step / max(t_probe, 1e-6))))
+    rows = max(256, (rows // 256) * 256)
+    A = oracle.random(rows, n, SEED_A)
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        oracle.mul_m4rm(A, B, n, n, threads=0)
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    t = sum(times) / len(times)
+    val = 2.0 * rows * n * n / t / 1e12
+    return {"value": val, "unit": "Tbit-op/s", "cores": threads, "kind": "port",
+            "sample": f"first {rows} of {m_total} rows of A times the full {n}x{n} B, per step; "
+                      f"CPU restatement of M4RM (oracle/gf2_oracle.c, OpenMP), not M4RI (absent submodule)",
+            "ms_per_step": t * 1e3, "rows": rows}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=0)
+    ap.add_argument("--algo", default="auto", choices=["auto", "m4rm", "mma", "simple"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    n = args.n or (32768 if world == 1 else 65536)
+    workload = f"square mzd_mul n={n} random" + (
+        "" if world == 1 else f", C/A row-blocks sharded over {world} ranks, NCCL broadcast of B per step")
+    config = {"workload": workload, "m": n, "k": n, "n": n, "algo": args.algo,
+              "l2": "operands (3 x n*n/8 bytes) exceed the 126 MB L2; no explicit flush" if n >= 32768
+              else "L2 flushed between steps by writing a 256 MiB buffer"}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        steps, warmup = args.steps, args.warmup
+        r = cpu_arm(n, n, steps, warmup, target_s=60.0)
+        line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": "Tbit-op/s",
+                "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": r["ms_per_step"],
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u64",
+                "data": "synthetic", "config": config,
+                "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+                "e2e": {"value": r["value"], "unit": "Tbit-op/s", "h2d_bytes_per_step": 0,
+                        "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line))
+        return
+
+    import torch
+    import m4ri_rust_b200 as m4
+    L = m4.lib()
+    if m4.device_count() <= 0:
+        raise SystemExit("bench.py: no CUDA device; libm4ri_b200 has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist = dist_mod
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    stream = torch.cuda.current_stream()
+    L.m4ri_b200_set_stream(ctypes.c_void_p(stream.cuda_stream))
+    algo = m4.ALGO_NAMES[args.algo]
+
+    # row-block of this rank
+    rows = n // world
+    r0 = rank * rows
+    ws = n // 64  # words per row (n % 128 == 0 so device stride == width)
+    tA = torch.empty((rows, ws), dtype=torch.int64, device="cuda")
+    tB = torch.empty((n, ws), dtype=torch.int64, device="cuda")
+    tC = torch.empty((rows, ws), dtype=torch.int64, device="cuda")
+    dA = m4.DMat.wrap(tA.data_ptr(), rows, n, ws, keepalive=tA)
+    dB = m4.DMat.wrap(tB.data_ptr(), n, n, ws, keepalive=tB)
+    dC = m4.DMat.wrap(tC.data_ptr(), rows, n, ws, keepalive=tC)
+    # word (r,w) of A = splitmix64 stream index r*width+w: generate the full-matrix
+    # stream positions of this rank's rows
+    L.m4ri_b200_dfill_random_at(dA.h, SEED_A, r0 * ws)
+    if rank == 0:
+        dB.fill_random(SEED_B)
+    else:
+        tB.zero_()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda") if n < 32768 else None
+
+    def step():
+        if dist is not None:
+            dist.broadcast(tB, src=0)
+        m4.dmul(dC, dA, dB, clear=True, algo=algo)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    L.m4ri_b200_timing_reset()
+    l0 = m4.launch_count()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    e_all0, e_all1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e_all0.record(stream)
+    for a, b in evs:
+        if flush is not None:
+            flush.fill_(1)
+        a.record(stream)
+        step()
+        b.record(stream)
+    e_all1.record(stream)
+    barrier()
+    clocks = sampler.stop()
+    launches = m4.launch_count() - l0
+    step_ms = [a.elapsed_time(b) for a, b in evs]
+    ms = sum(step_ms) / len(step_ms)
+    kern_ms = L.m4ri_b200_timing_ms() / max(1, L.m4ri_b200_timing_count())
+    kern_name = L.m4ri_b200_timing_name().decode()
+
+    # parity inside the run: Freivalds on this rank's block (false accept 2^-64)
+    ok = L.m4ri_b200_dfreivalds(dC.h, dA.h, dB.h, 0xF5E1)
+    if ok != 1:
+        raise SystemExit(f"bench.py: rank {rank}: product failed the Freivalds check")
+    chk = dC.checksum()
+
+    # ---- e2e: the reference-facing call, host operands ---------------------------
+    e2e_ms = None
+    if not args.no_e2e:
+        hA, hB = L.mzd_init(rows, n), L.mzd_init(n, n)
+        L.m4ri_b200_download(hA, dA.h)
+        L.m4ri_b200_download(hB, dB.h)
+        L.m4ri_b200_synchronize()
+        L.m4ri_b200_set_algo(algo)
+        hC = L.mzd_init(rows, n)
+        e2e_steps = max(3, min(args.steps, 5))
+        for i in range(2):
+            L.mzd_mul(hC, hA, hB, 0)
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(e2e_steps):
+            L.mzd_mul(hC, hA, hB, 0)  # synchronous: result words valid on return
+        torch.cuda.synchronize()
+        e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
+        L.m4ri_b200_set_algo(0)
+        host_chk_ok = bool((m4.mzd_words(hC)[:4] == dC.to_words()[:4]).all())
+        if not host_chk_ok:
+            raise SystemExit("bench.py: host-ABI result differs from the device-resident result")
+        for p in (hA, hB, hC):
+            L.mzd_free(p)
+
+    # ---- reduce over ranks: max time ------------------------------------------------
+    t = torch.tensor([ms, e2e_ms or 0.0, kern_ms], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_max, kern_ms = (float(x) for x in t.cpu())
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    total_ops = 2.0 * n * n * n
+    value = total_ops / (ms * 1e-3) / 1e12
+    pk = peaks()
+    per_launch_ops = 2.0 * rows * n * n
+    achieved = per_launch_ops / (kern_ms * 1e-3) / 1e12 if kern_ms > 0 else None
+    if "mma" in kern_name:
+        # tensor roofline: int8 dense rate = 2 x the measured bf16 rate of this pool
+        peak = 2.0 * pk["bf16_tflops_sustained"]
+        roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TOP/s (int8, 2mnk)",
+                "frac": achieved / peak if achieved else None, "traffic": None,
+                "peak_source": f"2 x bf16_tflops_sustained of MEASURED_PEAKS.json ({pk['src']})"}
+    else:
+        # Four-Russians gather: bound by shared-memory load bandwidth, measured by
+        # m4ri-rust_b200/lib/microbench (profiles/); expressed in the metric's unit
+        smem = json.load(open(os.path.join(ROOT, "profiles", "peaks_measured.json"))) \
+            if os.path.exists(os.path.join(ROOT, "profiles", "peaks_measured.json")) else {}
+        lds = smem.get("lds128_bytes_per_s", 128.0 * 148 * 1.965e9)
+        peak = lds / 4 * 64 * 8 / 1e12  # one 32-bit table word = 32 columns x 8 k-bits x 2 ops
+        roof = {"bound": "smem", "achieved": achieved, "peak": peak, "unit": "Tbit-op/s",
+                "frac": achieved / peak if achieved else None, "traffic": None,
+                "peak_source": "measured shared-memory load bandwidth x 512 bit-ops per 32-bit table word (t=8)"}
+    roof["kernel"] = kern_name
+    roof["kernel_ms"] = kern_ms
+    line = {"metric": METRIC, "value": value, "unit": "Tbit-op/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": config,
+            "clocks": clocks, "gpu_launches": int(launches), "roofline": roof,
+            "parity": {"freivalds_2^-64": True, "checksum_rank0": f"{chk:016x}"}}
+    if e2e_ms is not None:
+        bytes_in = (rows * ws + n * ws) * 8
+        line["e2e"] = {"value": total_ops / (e2e_max * 1e-3) / 1e12, "unit": "Tbit-op/s",
+                       "ms_per_step": e2e_max, "h2d_bytes_per_step": bytes_in,
+                       "d2h_bytes_per_step": rows * ws * 8,
+                       "api": "mzd_mul(C, A, B, 0) on host mzd_t operands (pinned), per rank on its row-block"}
+    if world == 1 and not args.no_cpu_baseline:
+        r = cpu_arm(n, n, 2, 1, target_s=12.0)
+        line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

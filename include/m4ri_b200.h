@@ -159,8 +159,25 @@ void m4ri_b200_dcopy(m4ri_b200_dmat_t *DST, const m4ri_b200_dmat_t *A);
 /* Fill with splitmix64(seed) words, row by row, excess bits masked: the same
  * stream of words the oracle's generator produces (oracle/gf2_oracle.c). */
 void m4ri_b200_dfill_random(m4ri_b200_dmat_t *M, uint64_t seed);
+/* Same, starting at output number `first_index` of the stream (row-block shards
+ * of one big matrix generate exactly their own rows). */
+void m4ri_b200_dfill_random_at(m4ri_b200_dmat_t *M, uint64_t seed, uint64_t first_index);
+/* Per-kernel device timing of the dominant product kernel (CUDA events on the
+ * launching stream). reset() enables recording and clears it; ms() synchronises and
+ * returns the summed duration of the recorded launches; count() their number;
+ * name() the kernel they belong to. */
+void m4ri_b200_timing_reset(void);
+double m4ri_b200_timing_ms(void);
+int m4ri_b200_timing_count(void);
+const char *m4ri_b200_timing_name(void);
 /* 64-bit XOR-fold checksum of all words (position-mixed), computed on device. */
 uint64_t m4ri_b200_dchecksum(const m4ri_b200_dmat_t *M);
+/* 1 iff every valid word is zero (OR-reduction on device). */
+int m4ri_b200_dis_zero(const m4ri_b200_dmat_t *M);
+/* Flip bit (r,c) on device (fault injection for the harness). */
+void m4ri_b200_dflip_bit(m4ri_b200_dmat_t *M, rci_t r, rci_t c);
+/* 1 when `algo` (enum above) is built into this library for the current device. */
+int m4ri_b200_algo_available(int algo);
 /* Freivalds over GF(2) with 64 packed random vectors: returns 1 iff
  * A*(B*X) == C*X for X = random(ncols(B) x 64, seed). False accept 2^-64. */
 int m4ri_b200_dfreivalds(const m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *A,

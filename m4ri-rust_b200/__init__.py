@@ -93,6 +93,11 @@ def lib():
         "m4ri_b200_dfill_random": (None, [vp, u64]),
         "m4ri_b200_dchecksum": (u64, [vp]),
         "m4ri_b200_dfreivalds": (i, [vp, vp, vp, u64]),
+        "m4ri_b200_dis_zero": (i, [vp]), "m4ri_b200_dflip_bit": (None, [vp, i, i]),
+        "m4ri_b200_algo_available": (i, [i]),
+        "m4ri_b200_dfill_random_at": (None, [vp, u64, u64]),
+        "m4ri_b200_timing_reset": (None, []), "m4ri_b200_timing_ms": (ctypes.c_double, []),
+        "m4ri_b200_timing_count": (i, []), "m4ri_b200_timing_name": (ctypes.c_char_p, []),
     }
     for name, (res, args) in sig.items():
         f = getattr(L, name)  # AttributeError = symbol missing: loud

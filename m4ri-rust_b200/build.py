@@ -27,7 +27,7 @@ def _stale():
     if not os.path.exists(LIB):
         return True
     t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)]
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f != "microbench.cu"]
     deps.append(os.path.join(HERE, "..", "include", "m4ri_b200.h"))
     deps.append(os.path.abspath(__file__))
     return any(os.path.getmtime(d) > t for d in deps)
@@ -60,5 +60,20 @@ def build(force=False, verbose=False):
     return LIB
 
 
+MICROBENCH = os.path.join(LIBDIR, "microbench")
+
+
+def build_microbench(force=False):
+    """Standalone peak microbenchmarks (LOP3, shared-memory loads, IMMA, HBM copy)."""
+    src = os.path.join(CSRC, "microbench.cu")
+    if not force and os.path.exists(MICROBENCH) and os.path.getmtime(MICROBENCH) >= os.path.getmtime(src):
+        return MICROBENCH
+    os.makedirs(LIBDIR, exist_ok=True)
+    subprocess.check_call(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3",
+                           "-std=c++17", "-o", MICROBENCH, src])
+    return MICROBENCH
+
+
 if __name__ == "__main__":
+    build_microbench(force="--force" in sys.argv)
     print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))

@@ -9,6 +9,8 @@
 #include <string.h>
 
 #include <mutex>
+#include <utility>
+#include <vector>
 
 #include "common.cuh"
 
@@ -23,6 +25,29 @@ void die(const char *fmt, ...) {
   va_end(ap);
   fflush(stderr);
   abort();
+}
+
+// ---- per-kernel timing (bench.py roofline) ------------------------------------------
+static std::mutex g_tmu;
+static std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_tev;
+static bool g_timing_on = false;
+static const char *g_tname = "";
+void timing_begin(const char *kernel_name, cudaStream_t s) {
+  if (!g_timing_on) return;
+  std::lock_guard<std::mutex> g(g_tmu);
+  if (g_tev.size() >= 4096) return;
+  cudaEvent_t a, b;
+  M4B_CUDA(cudaEventCreate(&a));
+  M4B_CUDA(cudaEventCreate(&b));
+  M4B_CUDA(cudaEventRecord(a, s));
+  g_tev.push_back({a, b});
+  g_tname = kernel_name;
+}
+void timing_end(cudaStream_t s) {
+  if (!g_timing_on) return;
+  std::lock_guard<std::mutex> g(g_tmu);
+  if (g_tev.empty()) return;
+  M4B_CUDA(cudaEventRecord(g_tev.back().second, s));
 }
 
 // ---- context -------------------------------------------------------------------
@@ -297,6 +322,47 @@ mzd_t *mzd_mul_v(mzd_t *y, const mzd_t *A, const mzd_t *x) {
   return y;
 }
 
+// C = A ^ B on the GPU (the Strassen / addmul "add"; reference mzd_add mzd.rs:223).
+// C may be NULL (allocate) or alias A or B (binary_matrix.rs:497-523).
+mzd_t *mzd_add(mzd_t *C, const mzd_t *A, const mzd_t *B) {
+  if (A->nrows != B->nrows || A->ncols != B->ncols)
+    die("m4ri_b200: mzd_add: rows and columns must match\n");
+  if (!C) C = mzd_init(A->nrows, A->ncols);
+  else if (C->nrows != A->nrows || C->ncols != A->ncols)
+    die("m4ri_b200: mzd_add: rows and columns of returned matrix must match\n");
+  if (A->nrows == 0 || A->width == 0) return C;
+  cudaStream_t s = current_stream();
+  DMat *dA = dmat_new(A->nrows, A->ncols, s), *dB = (B == A) ? dA : dmat_new(B->nrows, B->ncols, s);
+  upload(dA, A, s);
+  if (dB != dA) upload(dB, B, s);
+  k_add(dA, dA, dB, s);
+  download(C, dA, s);
+  if (dB != dA) dmat_delete(dB, s);
+  dmat_delete(dA, s);
+  M4B_CUDA(cudaStreamSynchronize(s));
+  return C;
+}
+mzd_t *mzd_sub(mzd_t *C, const mzd_t *A, const mzd_t *B) { return mzd_add(C, A, B); }
+
+// DST = A^T on the GPU (reference mzd_transpose mzd.rs:148; on the mat-vec path
+// twice per call, binary_matrix.rs:272-279,335,426).
+mzd_t *mzd_transpose(mzd_t *DST, const mzd_t *A) {
+  if (!DST) DST = mzd_init(A->ncols, A->nrows);
+  else if (DST->nrows != A->ncols || DST->ncols != A->nrows)
+    die("m4ri_b200: mzd_transpose: wrong size for return matrix\n");
+  if (DST == A) die("m4ri_b200: mzd_transpose: in-place transpose is not supported\n");
+  if (A->nrows == 0 || A->ncols == 0) return DST;
+  cudaStream_t s = current_stream();
+  DMat *dA = dmat_new(A->nrows, A->ncols, s), *dT = dmat_new(A->ncols, A->nrows, s);
+  upload(dA, A, s);
+  k_transpose(dT, dA, s);
+  download(DST, dT, s);
+  dmat_delete(dA, s);
+  dmat_delete(dT, s);
+  M4B_CUDA(cudaStreamSynchronize(s));
+  return DST;
+}
+
 // ---- additive API -------------------------------------------------------------------
 void m4ri_b200_set_algo(int algo) {
   std::call_once(g_once, probe);
@@ -395,9 +461,43 @@ void m4ri_b200_dcopy(m4ri_b200_dmat_t *DST, const m4ri_b200_dmat_t *A) {
   k_copy(DST, A, current_stream());
 }
 void m4ri_b200_dfill_random(m4ri_b200_dmat_t *M, uint64_t seed) {
-  k_fill_random(M, seed, current_stream());
+  k_fill_random(M, seed, 0, current_stream());
 }
+void m4ri_b200_dfill_random_at(m4ri_b200_dmat_t *M, uint64_t seed, uint64_t first_index) {
+  k_fill_random(M, seed, first_index, current_stream());
+}
+void m4ri_b200_timing_reset(void) {
+  std::lock_guard<std::mutex> g(g_tmu);
+  for (auto &p : g_tev) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
+  g_tev.clear();
+  g_timing_on = true;
+}
+double m4ri_b200_timing_ms(void) {
+  std::lock_guard<std::mutex> g(g_tmu);
+  double tot = 0;
+  for (auto &p : g_tev) {
+    M4B_CUDA(cudaEventSynchronize(p.second));
+    float ms = 0;
+    M4B_CUDA(cudaEventElapsedTime(&ms, p.first, p.second));
+    tot += ms;
+  }
+  return tot;
+}
+int m4ri_b200_timing_count(void) {
+  std::lock_guard<std::mutex> g(g_tmu);
+  return (int)g_tev.size();
+}
+const char *m4ri_b200_timing_name(void) { return g_tname; }
 uint64_t m4ri_b200_dchecksum(const m4ri_b200_dmat_t *M) { return k_checksum(M, current_stream()); }
+
+int m4ri_b200_dis_zero(const m4ri_b200_dmat_t *M) { return k_is_zero(M, current_stream()) ? 1 : 0; }
+void m4ri_b200_dflip_bit(m4ri_b200_dmat_t *M, rci_t r, rci_t c) { k_flip_bit(M, r, c, current_stream()); }
+int m4ri_b200_algo_available(int algo) {
+  std::call_once(g_once, probe);
+  if (g_ndev <= 0 || g_cc_major < 10) return 0;
+  if (algo == M4RI_B200_ALGO_MMA) return mma_available() ? 1 : 0;
+  return algo >= 0 && algo <= 3;
+}
 
 // Freivalds with 64 packed vectors; the three thin products use the AND+popc
 // kernel so the check shares no code with the M4RM / MMA kernels it verifies.
@@ -408,7 +508,7 @@ int m4ri_b200_dfreivalds(const m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *A,
   if (B->nrows != k || C->nrows != m || C->ncols != n) die("m4ri_b200: dfreivalds: shape mismatch\n");
   // X^T is 64 x n with row j of X = splitmix64 word j: generate X (n x 64) then transpose.
   DMat *X = dmat_new(n, 64, s), *Xt = dmat_new(64, n, s);
-  k_fill_random(X, seed, s);
+  k_fill_random(X, seed, 0, s);
   k_transpose(Xt, X, s);
   DMat *BX = dmat_new(k, 64, s), *BXt = dmat_new(64, k, s), *ABX = dmat_new(m, 64, s),
        *CX = dmat_new(m, 64, s);
@@ -417,13 +517,7 @@ int m4ri_b200_dfreivalds(const m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *A,
   k_mul_abt_simple(ABX, A, BXt, 1, s);
   k_mul_abt_simple(CX, C, Xt, 1, s);
   k_add(CX, CX, ABX, s);
-  uint64_t chk_zero;
-  {
-    DMat *Z = dmat_new(m, 64, s);
-    uint64_t a = k_checksum(CX, s), z = k_checksum(Z, s);
-    chk_zero = (a == z);
-    dmat_delete(Z, s);
-  }
+  bool chk_zero = k_is_zero(CX, s);
   dmat_delete(X, s); dmat_delete(Xt, s); dmat_delete(BX, s); dmat_delete(BXt, s);
   dmat_delete(ABX, s); dmat_delete(CX, s);
   M4B_CUDA(cudaStreamSynchronize(s));

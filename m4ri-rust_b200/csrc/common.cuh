@@ -37,6 +37,10 @@ void require_device();
 int sm_count();
 bool has_tcgen05();  // compute capability 10.x
 
+// Event pair around the dominant product kernel (api.cu; no-ops until enabled).
+void timing_begin(const char *kernel_name, cudaStream_t s);
+void timing_end(cudaStream_t s);
+
 static inline int width_of(int ncols) { return (ncols + 63) / 64; }
 static inline word high_mask(int ncols) {
   int r = ncols % 64;
@@ -69,8 +73,10 @@ void k_mask_excess(DMat *M, cudaStream_t s);
 void k_add(DMat *C, const DMat *A, const DMat *B, cudaStream_t s);
 void k_copy(DMat *D, const DMat *A, cudaStream_t s);
 void k_transpose(DMat *D, const DMat *A, cudaStream_t s);
-void k_fill_random(DMat *M, uint64_t seed, cudaStream_t s);
+void k_fill_random(DMat *M, uint64_t seed, uint64_t first_index, cudaStream_t s);
 uint64_t k_checksum(const DMat *M, cudaStream_t s);
+bool k_is_zero(const DMat *M, cudaStream_t s);
+void k_flip_bit(DMat *M, int r, int c, cudaStream_t s);
 // y (^)= A*x ; x, y packed rows
 void k_mul_v(DMat *y, const DMat *A, const DMat *x, int clear, cudaStream_t s);
 // C (^)= v*A
@@ -86,5 +92,6 @@ void k_mul_m4rm(DMat *C, const DMat *A, const DMat *B, int clear, cudaStream_t s
 // C (^)= A*Bt^T, bits -> int8 in shared memory / TMEM, tcgen05 MMA, parity
 void k_mul_abt_mma(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream_t s);
 bool mma_shape_ok(const DMat *C, const DMat *A, const DMat *Bt);
+bool mma_available();
 
 }  // namespace m4b

@@ -98,7 +98,9 @@ transpose_kernel(uint32_t *__restrict__ D, const uint32_t *__restrict__ S, int n
 void k_transpose(DMat *D, const DMat *A, cudaStream_t s) {
   if (A->nrows == 0 || A->ncols == 0) return;
   int sw32 = A->width * 2;
-  dim3 grid(cdiv(sw32, 32), cdiv(A->nrows, 32));
+  // row blocks cover every 32-bit half of D's words, so stale bits of a reused
+  // destination are overwritten with zeros (rows >= nrows read as zero)
+  dim3 grid(cdiv(sw32, 32), D->width * 2);
   transpose_kernel<<<grid, 1024, 0, s>>>((uint32_t *)D->d, (const uint32_t *)A->d, A->nrows,
                                          A->ncols, sw32, A->rowstride * 2, D->rowstride * 2);
   M4B_LAUNCHED();
@@ -113,23 +115,24 @@ __host__ __device__ static inline uint64_t mix64(uint64_t z) {
   return z ^ (z >> 31);
 }
 
-__global__ void fill_random_kernel(word *d, int nrows, int width, int rs, uint64_t seed, word hm) {
+__global__ void fill_random_kernel(word *d, int nrows, int width, int rs, uint64_t seed, word hm,
+                                   uint64_t first) {
   long long total = (long long)nrows * width;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     int r = (int)(i / width), w = (int)(i % width);
-    word z = mix64(seed + (uint64_t)(i + 1) * 0x9E3779B97F4A7C15ULL);
+    word z = mix64(seed + (first + (uint64_t)i + 1) * 0x9E3779B97F4A7C15ULL);
     if (w == width - 1) z &= hm;
     d[(size_t)r * rs + w] = z;
   }
 }
 
-void k_fill_random(DMat *M, uint64_t seed, cudaStream_t s) {
+void k_fill_random(DMat *M, uint64_t seed, uint64_t first_index, cudaStream_t s) {
   if (M->nrows == 0 || M->width == 0) return;
   long long total = (long long)M->nrows * M->width;
   unsigned grid = (unsigned)min((long long)cdiv(total, 256), (long long)sm_count() * 16);
   fill_random_kernel<<<grid, 256, 0, s>>>(M->d, M->nrows, M->width, M->rowstride, seed,
-                                          high_mask(M->ncols));
+                                          high_mask(M->ncols), first_index);
   M4B_LAUNCHED();
 }
 
@@ -161,6 +164,37 @@ uint64_t k_checksum(const DMat *M, cudaStream_t s) {
   M4B_CUDA(cudaFreeAsync(dout, s));
   M4B_CUDA(cudaStreamSynchronize(s));
   return h;
+}
+
+__global__ void is_zero_kernel(const word *d, int nrows, int width, int rs, int *nonzero) {
+  long long total = (long long)nrows * width;
+  word acc = 0;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x)
+    acc |= d[(size_t)(i / width) * rs + (i % width)];
+  if (__any_sync(0xffffffffu, acc != 0) && (threadIdx.x & 31) == 0) atomicOr(nonzero, 1);
+}
+
+bool k_is_zero(const DMat *M, cudaStream_t s) {
+  long long total = (long long)M->nrows * M->width;
+  if (!total) return true;
+  int *dflag, h = 0;
+  M4B_CUDA(cudaMallocAsync(&dflag, 4, s));
+  M4B_CUDA(cudaMemsetAsync(dflag, 0, 4, s));
+  unsigned grid = (unsigned)min((long long)cdiv(total, 256), (long long)sm_count() * 16);
+  is_zero_kernel<<<grid, 256, 0, s>>>(M->d, M->nrows, M->width, M->rowstride, dflag);
+  M4B_LAUNCHED();
+  M4B_CUDA(cudaMemcpyAsync(&h, dflag, 4, cudaMemcpyDeviceToHost, s));
+  M4B_CUDA(cudaFreeAsync(dflag, s));
+  M4B_CUDA(cudaStreamSynchronize(s));
+  return h == 0;
+}
+
+__global__ void flip_bit_kernel(word *d, size_t idx, int bit) { d[idx] ^= (word)1 << bit; }
+void k_flip_bit(DMat *M, int r, int c, cudaStream_t s) {
+  if (r < 0 || r >= M->nrows || c < 0 || c >= M->ncols) die("m4ri_b200: flip_bit out of range\n");
+  flip_bit_kernel<<<1, 1, 0, s>>>(M->d, (size_t)r * M->rowstride + c / 64, c % 64);
+  M4B_LAUNCHED();
 }
 
 // ---------------------------------------------------------------------------

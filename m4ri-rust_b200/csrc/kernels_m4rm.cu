@@ -107,12 +107,14 @@ void k_mul_m4rm(DMat *C, const DMat *A, const DMat *B, int clear, cudaStream_t s
     attr_set = true;
   }
   dim3 grid((C->width * 2 + TNW - 1) / TNW, (C->nrows + TM - 1) / TM);
+  timing_begin("m4rm_kernel", s);
   m4rm_kernel<<<grid, 1024, M4RM_SMEM, s>>>((uint32_t *)C->d, (const uint32_t *)A->d,
                                             (const uint32_t *)B->d, C->nrows, A->ncols,
                                             A->width * 2, B->width * 2, C->width * 2,
                                             A->rowstride * 2, B->rowstride * 2, C->rowstride * 2,
                                             clear);
   M4B_LAUNCHED();
+  timing_end(s);
 }
 
 }  // namespace m4b

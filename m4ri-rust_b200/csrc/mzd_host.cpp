@@ -2,10 +2,10 @@
 //
 // These are the O(size) host-memory utilities m4ri-rust's BinMatrix needs around
 // the multiplication path (SURVEY 8b "must also export — because one allocator
-// must own every mzd_t the path touches"): construction, copy, compare, XOR-add
-// and transpose of HOST matrices. They move no data to the GPU because their
-// operands live in host memory and a PCIe round trip costs more than the work.
-// Every multiplication entry point is in api.cu and runs on the GPU.
+// must own every mzd_t the path touches"): construction, windows, copy, compare,
+// identity and random fill of HOST matrices — descriptor and memcpy work, no GF(2)
+// arithmetic. Everything that computes (the products, mzd_add, mzd_transpose:
+// SURVEY 8a) is in api.cu and runs on the GPU.
 //
 // Layout contract (m4ri-sys/src/mzd.rs:24-79, checked by the reference tests at
 // mzd.rs:381-422): 64-byte descriptor, rows[i] == blocks[0].begin + offset_vector
@@ -174,55 +174,5 @@ void mzd_randomize(mzd_t *A) {
     row[A->width - 1] &= A->high_bitmask;
   }
 }
-
-// 64x64 bit-block transpose (recursive swap network).
-static inline void transpose64(word x[64]) {
-  word m = 0x00000000FFFFFFFFULL;
-  for (int j = 32; j; j >>= 1, m ^= m << j)
-    for (int k = 0; k < 64; k = (k + j + 1) & ~j) {
-      word t = ((x[k] >> j) ^ x[k + j]) & m;
-      x[k] ^= t << j;
-      x[k + j] ^= t;
-    }
-}
-
-mzd_t *mzd_transpose(mzd_t *DST, const mzd_t *A) {
-  if (!DST) DST = mzd_init(A->ncols, A->nrows);
-  else if (DST->nrows != A->ncols || DST->ncols != A->nrows)
-    die("m4ri_b200: mzd_transpose: wrong size for return matrix\n");
-  if (DST == A) die("m4ri_b200: mzd_transpose: in-place transpose is not supported\n");
-  word blk[64];
-  for (rci_t r0 = 0; r0 < A->nrows; r0 += 64) {
-    int nr = A->nrows - r0 < 64 ? A->nrows - r0 : 64;
-    for (wi_t w = 0; w < A->width; w++) {
-      for (int i = 0; i < nr; i++) blk[i] = A->rows[r0 + i][w];
-      for (int i = nr; i < 64; i++) blk[i] = 0;
-      if (w == A->width - 1)
-        for (int i = 0; i < nr; i++) blk[i] &= A->high_bitmask;
-      transpose64(blk);
-      int nc = A->ncols - w * 64 < 64 ? A->ncols - w * 64 : 64;
-      for (int j = 0; j < nc; j++) DST->rows[w * 64 + j][r0 / 64] = blk[j];
-    }
-  }
-  return DST;
-}
-
-mzd_t *mzd_add(mzd_t *C, const mzd_t *A, const mzd_t *B) {
-  if (A->nrows != B->nrows || A->ncols != B->ncols)
-    die("m4ri_b200: mzd_add: rows and columns must match\n");
-  if (!C) C = mzd_init(A->nrows, A->ncols);
-  else if (C->nrows != A->nrows || C->ncols != A->ncols)
-    die("m4ri_b200: mzd_add: rows and columns of returned matrix must match\n");
-  if (A->width == 0) return C;
-  for (rci_t i = 0; i < A->nrows; i++) {
-    const word *a = A->rows[i], *b = B->rows[i];
-    word *c = C->rows[i];  // may alias a (binary_matrix.rs:497-523)
-    for (wi_t w = 0; w < A->width; w++) c[w] = a[w] ^ b[w];
-    c[A->width - 1] &= A->high_bitmask;
-  }
-  return C;
-}
-
-mzd_t *mzd_sub(mzd_t *C, const mzd_t *A, const mzd_t *B) { return mzd_add(C, A, B); }
 
 }  // extern "C"

@@ -1,0 +1,128 @@
+"""CPU tests of the C-ABI boundary: the library loads without a GPU, exports
+every symbol include/m4ri_b200.h declares, and its host-side mzd_t allocator set
+honours the layout contract the reference's own tests pin
+(m4ri-sys/src/mzd.rs:381-456). No product is computed here (no GPU)."""
+import ctypes
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    src = open(os.path.join(ROOT, "include", "m4ri_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    names = re.findall(r"\b(_?mzd_[a-z0-9_]+|m4ri_b200_[a-z0-9_]+)\s*\(", src)
+    return sorted(set(n for n in names if n not in ("m4ri_b200_dmat",)))
+
+
+def test_every_declared_symbol_is_exported(m4):
+    L = m4.lib()
+    names = declared_symbols()
+    assert len(names) >= 40, names
+    for must in ["mzd_mul", "mzd_addmul", "mzd_mul_m4rm", "mzd_addmul_m4rm", "_mzd_mul_m4rm",
+                 "mzd_mul_naive", "mzd_addmul_naive", "_mzd_mul_naive", "_mzd_mul_va", "mzd_mul_v",
+                 "mzd_init", "mzd_free", "mzd_transpose", "mzd_copy", "mzd_equal", "mzd_add",
+                 "mzd_randomize", "mzd_set_ui"]:
+        assert must in names
+    for n in names:
+        assert hasattr(L, n), f"{n} declared in include/m4ri_b200.h but not exported"
+    # and through the dynamic symbol table, not only ctypes' lazy lookup
+    out = subprocess.run(["nm", "-D", "--defined-only", m4.LIB_PATH], capture_output=True, text=True).stdout
+    exported = set(line.split()[-1] for line in out.splitlines() if line.strip())
+    assert set(names) <= exported
+
+
+def test_no_torch_or_oracle_dependency(m4):
+    out = subprocess.run(["ldd", m4.LIB_PATH], capture_output=True, text=True).stdout
+    assert "torch" not in out and "oracle" not in out and "m4ri.so" not in out
+
+
+def test_sizeof_mzd_is_64(m4):  # m4ri-sys/src/mzd.rs:385
+    assert ctypes.sizeof(m4.Mzd) == 64
+    assert m4.Mzd.high_bitmask.offset == 40 and m4.Mzd.blocks.offset == 48 and m4.Mzd.rows.offset == 56
+
+
+def test_init_layout(m4):  # mzd.rs:381-422
+    L = m4.lib()
+    for (r, c) in [(10, 10), (1000, 1000), (3, 129), (7, 193), (5, 64), (64, 321)]:
+        p = L.mzd_init(r, c)
+        m = p.contents
+        w = (c + 63) // 64
+        assert (m.nrows, m.ncols, m.width) == (r, c, w)
+        assert m.rowstride == (w if (w < 3 or w % 2 == 0) else w + 1)  # mzd.rs:35-37
+        assert bool(m.blocks) and bool(m.rows)  # mzd.rs:387-388
+        assert m.high_bitmask == ((1 << (c % 64)) - 1 if c % 64 else (1 << 64) - 1)
+        base = ctypes.addressof(m.blocks[0].begin.contents)
+        for i in range(r):  # mzd_row / mzd_first_row address rule, mzd.rs:277-313
+            assert ctypes.addressof(m.rows[i].contents) == base + 8 * (m.offset_vector + i * m.rowstride)
+        assert not m4.mzd_words(p).any()
+        assert L.mzd_equal(p, p) == 1
+        L.mzd_free(p)
+
+
+def test_set_ui_write_read_bit(m4):  # mzd.rs:425-456
+    L = m4.lib()
+    p = L.mzd_init(1000, 1000)
+    L.mzd_set_ui(p, 1)
+    M = m4.BinMatrix(p)
+    for i in range(0, 1000, 7):
+        for j in (0, i, 999 - i, 63, 64):
+            assert M.bit(i, j) == (i == j)
+    # identity(3) words: rows [1],[2],[4] (binary_matrix.rs:693-699)
+    I3 = m4.BinMatrix.identity(3)
+    assert [int(I3.words()[r, 0]) for r in range(3)] == [1, 2, 4]
+
+
+def test_randomize_copy_equal(m4):  # mzd.rs:389-394
+    L = m4.lib()
+    a = L.mzd_init(100, 131)
+    L.mzd_randomize(a)
+    w = m4.mzd_words(a)
+    assert w.any()
+    assert not (w[:, 2] >> np.uint64(131 - 128)).any()  # excess bits masked
+    assert not w[:, 3:].any()                          # padding word zero
+    b = L.mzd_copy(None, a)
+    assert L.mzd_equal(a, b) == 1
+    L.mzd_randomize(b)
+    assert L.mzd_equal(a, b) == 0
+    L.mzd_free(a)
+    L.mzd_free(b)
+
+
+def test_window_shares_words(m4):  # mzd.rs:121-127
+    L = m4.lib()
+    a = L.mzd_init(20, 300)
+    L.mzd_randomize(a)
+    w = L.mzd_init_window(a, 5, 64, 15, 200)
+    assert (w.contents.nrows, w.contents.ncols) == (10, 136)
+    for i in range(10):
+        assert ctypes.addressof(w.contents.rows[i].contents) == ctypes.addressof(a.contents.rows[5 + i].contents) + 8
+    L.mzd_free(w)
+    L.mzd_free(a)
+
+
+def test_binvector_mirror(m4):  # binary_vector.rs:217-288
+    v = m4.BinVector.from_bytes(bytes([0b10000000]))
+    assert [int(b) for b in v.bits] == [1, 0, 0, 0, 0, 0, 0, 0]
+    a = m4.BinVector.from_function(70, lambda i: i % 3 == 0)
+    assert a.count_ones() == 24 and len(a) == 70
+    st = a.get_storage()
+    assert m4.BinVector.from_storage(st, 70) == a
+    assert (a + a).count_ones() == 0
+    assert (a * a) == (24 % 2 == 1)
+
+
+def test_product_without_gpu_dies_loudly(m4):
+    """No CPU fallback: on a box without a GPU the product aborts the process."""
+    if m4.device_count() > 0:
+        return
+    code = ("import sys; sys.path.insert(0, %r); import m4ri_rust_b200 as m; "
+            "a = m.BinMatrix.identity(8); a * a" % ROOT)
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True)
+    assert r.returncode != 0
+    assert "no CPU fallback" in r.stderr

@@ -1,0 +1,304 @@
+"""GPU parity tests: the CUDA path, called through the C-ABI of libm4ri_b200.so
+(the m4ri-sys-shaped mzd_* entry points and the BinMatrix/BinVector mirrors),
+against the CPU oracle on identical seeded inputs — bit-exact, including excess
+bits and padding words. Reads neither /root/reference nor anything else outside
+the repo."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLD = os.path.join(HERE, "golden")
+
+ALGOS = ["m4rm", "mma", "simple"]
+
+
+def need(m4, algo):
+    if not m4.lib().m4ri_b200_algo_available(m4.ALGO_NAMES[algo]):
+        pytest.fail(f"algorithm {algo} is not built into libm4ri_b200.so")
+
+
+def host(m4, words, ncols):
+    return m4.mzd_from_words(words, ncols)
+
+
+def result_words(m4, p, free=True):
+    """[nrows, width] valid words + assert padding is zero."""
+    w = m4.mzd_words(p).copy()
+    width = p.contents.width
+    assert not w[:, width:].any(), "padding words must be zero"
+    if p.contents.ncols % 64 and width:
+        assert not (w[:, width - 1] & ~np.uint64(p.contents.high_bitmask)).any(), "excess bits must be zero"
+    if free:
+        m4.lib().mzd_free(p)
+    return w[:, :width]
+
+
+def entry_points(m4):
+    L = m4.lib()
+    return {
+        "mzd_mul": lambda a, b: L.mzd_mul(None, a, b, 0),
+        "mzd_mul_m4rm": lambda a, b: L.mzd_mul_m4rm(None, a, b, 0),
+        "_mzd_mul_m4rm": lambda a, b: L._mzd_mul_m4rm(None, a, b, 0, 1),
+        "mzd_mul_naive": lambda a, b: L.mzd_mul_naive(None, a, b),
+    }
+
+
+# ---- the reference's own pinned answers, replayed through the mirrors -----------
+def test_reference_known_answers(gpu, m4):
+    cases = json.load(open(os.path.join(GOLD, "reference_known_answers.json")))["cases"]
+    for strategy in ("strassen_mul", "m4rm_mul", "naive_mul"):  # mul_impl!, binary_matrix.rs:53-95
+        m4.BinMatrix.mul_strategy = strategy
+        for c in cases:
+            if c["op"] == "mul":  # binary_matrix.rs:661-670
+                m1, m2 = m4.BinMatrix.identity(8), m4.BinMatrix.identity(8)
+                prod = m1 * m2
+                assert prod == m4.BinMatrix.identity(8)
+            elif c["op"] == "matvec":  # binary_matrix.rs:677-678
+                result = m4.BinMatrix.identity(10) * m4.BinVector.from_elem(10, True)
+                assert result == m4.BinVector.from_elem(10, True)
+            elif c["op"] == "vecmat":  # binary_matrix.rs:680-681
+                result = m4.BinVector.from_elem(10, True) * m4.BinMatrix.identity(10)
+                assert result == m4.BinVector.from_elem(10, True)
+            elif c["op"] == "vecmat_shape":  # binary_matrix.rs:683-685
+                result = m4.BinVector.from_elem(10, True) * m4.BinMatrix.random(10, 3)
+                assert len(result) == 3
+    m4.BinMatrix.mul_strategy = "strassen_mul"
+
+
+def test_as_vector_and_transposed(gpu, m4):  # binary_matrix.rs:701-719, binary_vector.rs:262-278
+    v = m4.BinVector.from_function(10, lambda i: i % 2 == 1)
+    assert v.as_matrix().as_vector() == v
+    col = v.as_column_matrix()
+    assert (col.nrows(), col.ncols()) == (10, 1)
+    assert col.as_vector() == v
+    a = m4.BinMatrix.random(70, 200)
+    assert a.transposed().transposed() == a
+    b = a.clone()
+    b += a
+    assert b == m4.BinMatrix.zero(70, 200)
+    assert (a + a) == m4.BinMatrix.zero(70, 200)
+
+
+# ---- golden products (committed fixtures) ---------------------------------------
+def test_golden_products_all_entry_points(gpu, m4, orc):
+    g = np.load(os.path.join(GOLD, "oracle_products.npz"))
+    L = m4.lib()
+    n_cases = sum(1 for k in g.files if k.startswith("shape_"))
+    for idx in range(n_cases):
+        m, k, n = (int(x) for x in g[f"shape_{idx}"])
+        A = orc.random(m, k, 0x4D345249 ^ (idx << 32) ^ 1)
+        B = orc.random(k, n, 0x4D345249 ^ (idx << 32) ^ 2)
+        C = g[f"C_{idx}"][:, : orc.width(n)]
+        a, b = host(m4, A, k), host(m4, B, n)
+        for name, f in entry_points(m4).items():
+            got = result_words(m4, f(a, b))
+            assert (got == C).all(), f"{name} differs on golden case {idx} ({m}x{k}x{n})"
+        bt = L.mzd_transpose(None, b)
+        assert (result_words(m4, L._mzd_mul_naive(None, a, bt, 1)) == C).all()
+        if m <= 4:
+            assert (result_words(m4, L._mzd_mul_va(None, a, b, 1)) == C).all()
+        if n == 1:
+            assert (result_words(m4, L.mzd_mul_v(None, a, b)) == C).all()
+        for p in (a, b, bt):
+            L.mzd_free(p)
+
+
+# ---- shape sweep, every algorithm, device API -----------------------------------
+SWEEP = [(1, 1, 1), (1, 64, 1), (2, 63, 65), (7, 129, 3), (65, 64, 64), (64, 65, 64), (64, 64, 65),
+         (33, 31, 200), (191, 193, 129), (200, 257, 321), (5, 700, 1100), (1030, 40, 1030),
+         (1024, 1024, 1024), (257, 2050, 1500), (128, 128, 256), (256, 4096, 128), (1500, 96, 70)]
+
+
+@pytest.mark.parametrize("algo", ALGOS)
+def test_shape_sweep(gpu, m4, orc, algo):
+    need(m4, algo)
+    L = m4.lib()
+    for (m, k, n) in SWEEP:
+        A, B = orc.random(m, k, 77 + m), orc.random(k, n, 99 + n)
+        want = orc.mul_m4rm(A, B, k, n, threads=4)[:, : orc.width(n)]
+        a, b = host(m4, A, k), host(m4, B, n)
+        dA, dB = m4.DMat.from_host(a), m4.DMat.from_host(b)
+        dC = m4.DMat.init(m, n)
+        m4.dmul(dC, dA, dB, clear=True, algo=m4.ALGO_NAMES[algo])
+        got = dC.to_words()
+        assert not got[:, orc.width(n):].any()
+        assert (got[:, : orc.width(n)] == want).all(), f"{algo} differs at {m}x{k}x{n}"
+        # accumulate: C ^= A*B twice restores a random C
+        C0 = orc.random(m, n, 5)
+        c0 = host(m4, C0, n)
+        dC2 = m4.DMat.from_host(c0)
+        m4.dmul(dC2, dA, dB, clear=False, algo=m4.ALGO_NAMES[algo])
+        once = dC2.to_words()[:, : orc.width(n)]
+        assert (once == (C0[:, : orc.width(n)] ^ want)).all(), f"{algo} addmul differs at {m}x{k}x{n}"
+        m4.dmul(dC2, dA, dB, clear=False, algo=m4.ALGO_NAMES[algo])
+        assert (dC2.to_words()[:, : orc.width(n)] == C0[:, : orc.width(n)]).all()
+        for p in (a, b, c0):
+            L.mzd_free(p)
+
+
+def test_addmul_entry_points(gpu, m4, orc):
+    L = m4.lib()
+    m, k, n = 300, 500, 700
+    A, B, C0 = orc.random(m, k, 1), orc.random(k, n, 2), orc.random(m, n, 3)
+    want = (C0 ^ orc.mul_m4rm(A, B, k, n))[:, : orc.width(n)]
+    a, b = host(m4, A, k), host(m4, B, n)
+    bt = L.mzd_transpose(None, b)
+    calls = {
+        "mzd_addmul": lambda c: L.mzd_addmul(c, a, b, 0),
+        "mzd_addmul_m4rm": lambda c: L.mzd_addmul_m4rm(c, a, b, 0),
+        "_mzd_mul_m4rm(clear=0)": lambda c: L._mzd_mul_m4rm(c, a, b, 0, 0),
+        "mzd_addmul_naive": lambda c: L.mzd_addmul_naive(c, a, b),
+        "_mzd_mul_naive(clear=0)": lambda c: L._mzd_mul_naive(c, a, bt, 0),
+    }
+    for name, f in calls.items():
+        c = host(m4, C0, n)
+        r = f(c)
+        assert r and (m4.mzd_words(r)[:, : orc.width(n)] == want).all(), name
+        L.mzd_free(c)
+    # _mzd_mul_va accumulate, 3-row v
+    v = orc.random(3, k, 9)
+    hv = host(m4, v, k)
+    c = host(m4, C0[:3].copy(), n)
+    L._mzd_mul_va(c, hv, b, 0)
+    assert (m4.mzd_words(c)[:, : orc.width(n)] == (C0[:3] ^ orc.mul_va(v, B, k, n))[:, : orc.width(n)]).all()
+    for p in (a, b, bt, hv, c):
+        L.mzd_free(p)
+
+
+def test_window_operands(gpu, m4, orc):
+    """Inputs that are windows (rows[] not one contiguous slab) are read through rows[]."""
+    L = m4.lib()
+    P = orc.random(300, 640, 4)
+    p = host(m4, P, 640)
+    w = L.mzd_init_window(p, 10, 128, 210, 448)  # 200 x 320
+    A = np.ascontiguousarray(P[10:210, 2:7])
+    B = orc.random(320, 100, 5)
+    b = host(m4, B, 100)
+    want = orc.mul_m4rm(A, B, 320, 100)[:, :2]
+    assert (result_words(m4, L.mzd_mul(None, w, b, 0)) == want).all()
+    for q in (w, p, b):
+        L.mzd_free(q)
+
+
+def test_transpose_add_device_and_host(gpu, m4, orc):
+    L = m4.lib()
+    for (r, c) in [(1, 1), (10, 1), (1, 10), (65, 129), (300, 1000), (1000, 64), (1030, 2050)]:
+        S, S2 = orc.random(r, c, 1), orc.random(r, c, 2)
+        s, s2 = host(m4, S, c), host(m4, S2, c)
+        assert (result_words(m4, L.mzd_transpose(None, s)) == orc.transpose(S, c)[:, : orc.width(r)]).all()
+        assert (result_words(m4, L.mzd_add(None, s, s2)) == orc.add(S, S2, c)[:, : orc.width(c)]).all()
+        L.mzd_add(s, s, s2)  # C aliases A (binary_matrix.rs:497-523)
+        assert (result_words(m4, s, free=False) == orc.add(S, S2, c)[:, : orc.width(c)]).all()
+        L.mzd_free(s)
+        L.mzd_free(s2)
+
+
+def test_matvec_shapes(gpu, m4, orc):
+    L = m4.lib()
+    for (m, n) in [(34, 128), (10, 10), (64, 1000), (1000, 64), (1, 1), (4097, 777), (300, 8192)]:
+        A = orc.random(m, n, 3)
+        x = orc.random(1, n, 4)
+        a = host(m4, A, n)
+        want = orc.mul_v(A, x[0], n)
+        # mul_slice path (binary_matrix.rs:416-431): m x 1 matrix, one word per row
+        M = m4.BinMatrix(a)
+        col = M.mul_slice(x[0][: orc.width(n)])
+        assert (col.nrows(), col.ncols()) == (m, 1)
+        bits = m4.mzd_words(col.mzd)[:, 0]
+        assert [int(b) for b in bits] == [int(want[i // 64] >> np.uint64(i % 64)) & 1 for i in range(m)]
+        # packed in / packed out device API
+        dA = m4.DMat.from_host(a)
+        hx = host(m4, x, n)
+        dx = m4.DMat.from_host(hx)
+        dy = m4.DMat.init(1, m)
+        L.m4ri_b200_dmul_v(dy.h, dA.h, dx.h, 1)
+        assert (dy.to_words()[0, : orc.width(m)] == want).all()
+        L.mzd_free(hx)
+
+
+def test_device_generator_and_checksum_match_oracle(gpu, m4, orc):
+    for (r, c) in [(5, 70), (100, 64), (257, 1000)]:
+        d = m4.DMat.init(r, c).fill_random(0xABCD + r)
+        want = orc.random(r, c, 0xABCD + r)
+        assert (d.to_words()[:, : orc.width(c)] == want[:, : orc.width(c)]).all()
+        assert d.checksum() == orc.checksum(want, c)
+
+
+# ---- BASELINE.json sizes ---------------------------------------------------------
+@pytest.mark.parametrize("algo", ["m4rm", "mma"])
+def test_n8192_bit_exact(gpu, m4, orc, algo):
+    """configs[1]: square n=8192, full compare against the oracle."""
+    need(m4, algo)
+    n = 8192
+    A, B = orc.random(n, n, 0x4D345249 ^ (1 << 32) ^ 1), orc.random(n, n, 0x4D345249 ^ (1 << 32) ^ 2)
+    want = orc.mul_m4rm(A, B, n, n, threads=0)
+    dA = m4.DMat.init(n, n).fill_random(0x4D345249 ^ (1 << 32) ^ 1)
+    dB = m4.DMat.init(n, n).fill_random(0x4D345249 ^ (1 << 32) ^ 2)
+    dC = m4.DMat.init(n, n)
+    m4.dmul(dC, dA, dB, clear=True, algo=m4.ALGO_NAMES[algo])
+    assert dC.checksum() == orc.checksum(want, n)
+    assert (dC.to_words() == want).all()
+    # and through the host ABI
+    L = m4.lib()
+    a, b = host(m4, A, n), host(m4, B, n)
+    m4.lib().m4ri_b200_set_algo(m4.ALGO_NAMES[algo])
+    try:
+        c = L.mzd_mul(None, a, b, 0)
+    finally:
+        m4.lib().m4ri_b200_set_algo(0)
+    assert (m4.mzd_words(c) == want).all()
+    for p in (a, b, c):
+        L.mzd_free(p)
+
+
+def test_n32768_properties(gpu, m4):
+    """configs[2]: n=32768 on one B200 — size-independent properties: Freivalds
+    (false accept 2^-64), the two independent kernels agree bit for bit,
+    A*(B^B2) == A*B ^ A*B2, addmul twice restores C."""
+    n = 32768
+    L = m4.lib()
+    dA = m4.DMat.init(n, n).fill_random(11)
+    dB = m4.DMat.init(n, n).fill_random(12)
+    dC = m4.DMat.init(n, n)
+    m4.dmul(dC, dA, dB, algo=m4.ALGO_M4RM)
+    assert L.m4ri_b200_dfreivalds(dC.h, dA.h, dB.h, 0xF5E1) == 1
+    chk = dC.checksum()
+    dC2 = m4.DMat.init(n, n)
+    m4.dmul(dC2, dA, dB, algo=m4.ALGO_MMA)
+    assert dC2.checksum() == chk
+    L.m4ri_b200_dadd(dC2.h, dC2.h, dC.h)
+    assert L.m4ri_b200_dis_zero(dC2.h) == 1
+    # a corrupted product is rejected
+    m4.dmul(dC2, dA, dB, algo=m4.ALGO_MMA)
+    L.m4ri_b200_dflip_bit(dC2.h, 12345, 23456)
+    assert L.m4ri_b200_dfreivalds(dC2.h, dA.h, dB.h, 0xF5E1) == 0
+    L.m4ri_b200_dflip_bit(dC2.h, 12345, 23456)
+    # linearity
+    dB2 = m4.DMat.init(n, n).fill_random(13)
+    m4.dmul(dC2, dA, dB2, clear=False, algo=m4.ALGO_AUTO)  # C2 = A*B ^ A*B2
+    L.m4ri_b200_dadd(dB2.h, dB2.h, dB.h)
+    m4.dmul(dC, dA, dB2, algo=m4.ALGO_AUTO)               # C = A*(B^B2)
+    assert dC.checksum() == dC2.checksum()
+
+
+def test_lpn_shape(gpu, m4, orc):
+    """configs[4]: tall 2^20 x 512 times 512 x 512, full compare on a 2^16-row
+    slice per algorithm and Freivalds on the whole product."""
+    m, k, n = 1 << 20, 512, 512
+    L = m4.lib()
+    dA = m4.DMat.init(m, k).fill_random(21)
+    dB = m4.DMat.init(k, n).fill_random(22)
+    dC = m4.DMat.init(m, n)
+    rows = 1 << 16
+    A = orc.random(rows, k, 21)  # word (r,w) = stream index r*width+w: a row prefix is a prefix
+    B = orc.random(k, n, 22)
+    want = orc.mul_m4rm(A, B, k, n, threads=0)
+    for algo in (m4.ALGO_M4RM, m4.ALGO_MMA, m4.ALGO_AUTO):
+        m4.dmul(dC, dA, dB, algo=algo)
+        assert L.m4ri_b200_dfreivalds(dC.h, dA.h, dB.h, 7) == 1
+        head = m4.DMat.wrap(dC.ptr, rows, n, dC.rowstride, keepalive=dC)
+        assert (head.to_words() == want).all()
