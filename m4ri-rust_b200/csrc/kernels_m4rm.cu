@@ -3,93 +3,186 @@
 // Replaces what M4RI does behind mzd_mul_m4rm / mzd_addmul_m4rm
 // (m4ri-sys/src/brilliantrussian.rs:216,224; mechanism documented at
 // brilliantrussian.rs:17-193: mzd_make_table builds the 2^k XOR-combinations of k
-// rows of B, mzd_process_rows* look k bits of A up and XOR the table row into C).
+// rows of B in Gray-code order, mzd_process_rows* look k bits of A up and XOR
+// the table row into C).
 //
 // B200 design (not M4RI's): one CTA owns a 1024 x 1024-bit tile of C, held
-// entirely in registers (1024 threads x 32 accumulators: thread (warp w, lane l)
-// owns the 32-bit column word l of the tile rows 32w..32w+31). Per pass the CTA
-// consumes 32 rows of B: it builds four 256-entry tables (8 rows of B each,
-// 4 x 256 x 128 B = 128 KiB of shared memory), then every warp walks its 32
-// rows: one A word per row (read once per lane, broadcast with a shuffle) gives
-// four byte indices, each a conflict-free 128-byte table-row read (lane l reads
-// bank l) that is XORed into the accumulators with LOP3.
+// entirely in registers (512 threads x 64 accumulator words; the other ~60
+// registers keep eight LDS.128 in flight per warp). k is consumed in
+// phases of 16 bits: two 256-entry tables (8 rows of B each) of 128-byte rows,
+// double buffered (2 x 64 KiB of shared memory) so every phase both gathers from
+// the current tables and builds the next ones — the LSU never idles on a
+// build-only or gather-only stretch.
 //
-// Roofline: shared-memory wavefronts. Per (row, pass) the warp
-// issues 4 table reads + 1 shuffle = 5 crossbar wavefronts for 32 x 1024 bit-MACs;
-// the table build adds 1024 store wavefronts per pass per CTA (25 % at 1024 rows).
+// Gather: a quarter-warp (8 lanes x 16 B) reads one 128-byte table row with
+// LDS.128 — one conflict-free wavefront — so the four quarters of a warp follow
+// FOUR different rows of A per instruction. Per (row, phase): 2 table reads,
+// 1/4 shuffle, ~4 integer ops for the two byte indices, 4 LOP3 (3-input XOR).
+// Build: lane = 32-bit column word, warp = (table, high nibble); the low nibble
+// runs in Gray-code order: one LOP3 + one conflict-free STS.32 per entry.
+//
+// Roofline: shared-memory wavefronts (128 B/clk/SM measured). Per
+// phase and CTA: 2048 gather + 256 shuffle + 512 build wavefronts for
+// 1024 x 1024 x 16 bit-MACs.
 #include "common.cuh"
 
 namespace m4b {
 
-constexpr int TM = 1024;          // tile rows
-constexpr int TNW = 32;           // tile columns in 32-bit words (1024 bits)
-constexpr int NTAB = 4;           // tables per pass (8 rows of B each)
-constexpr int M4RM_SMEM = NTAB * 256 * TNW * 4;  // 131072
+constexpr int TM = 1024;   // tile rows
+constexpr int TNW = 32;    // tile columns in 32-bit words (1024 bits)
+constexpr int NTHR = 512;  // 16 warps x 64 rows; 64 accumulator registers per thread
+constexpr int TAB_BYTES = 256 * TNW * 4;         // one table: 256 rows of 128 B = 32 KiB
+constexpr int ASTAGE_BYTES = TM * 16;            // A staging: 16 B (8 phases of k) per row
+constexpr int M4RM_SMEM = 2 * 2 * TAB_BYTES + 2 * ASTAGE_BYTES + 2 * 2048;  // 128 + 32 + 4 KiB
 
-__global__ void __launch_bounds__(1024, 1)
+__device__ __forceinline__ uint4 lds128(uint32_t saddr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "r"(saddr));
+  return v;
+}
+__device__ __forceinline__ uint32_t lds_u16(uint32_t saddr) {
+  uint16_t v;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(saddr));
+  return v;
+}
+// 16-byte global -> shared copy that bypasses registers; bytes beyond src_bytes are zero-filled
+__device__ __forceinline__ void cp_async16(uint32_t saddr, const void *gptr, int src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(saddr), "l"(gptr), "r"(src_bytes)
+               : "memory");
+}
+
+__global__ void __launch_bounds__(NTHR, 1)
 m4rm_kernel(uint32_t *__restrict__ C, const uint32_t *__restrict__ A,
             const uint32_t *__restrict__ B, int m, int k, int aw32, int bw32, int cw32, int as32,
             int bs32, int cs32, int clear) {
-  extern __shared__ __align__(16) uint32_t tab[];  // [NTAB][256][TNW]
+  extern __shared__ __align__(16) uint32_t tab[];  // [buf 2][table 2][256][TNW] | A stages
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int row0 = blockIdx.y * TM + warp * 32;  // first C row of this warp
-  const int cw = blockIdx.x * TNW + lane;        // column word of this lane
-  const bool col_ok = cw < bw32;
+  const int q = lane >> 3, l8 = lane & 7;
+  const int row0 = blockIdx.y * TM + warp * 64;  // first C row of this warp
 
-  uint32_t acc[32];
+  uint4 acc[16];
 #pragma unroll
-  for (int r = 0; r < 32; r++) acc[r] = 0;
+  for (int s = 0; s < 16; s++) acc[s] = make_uint4(0, 0, 0, 0);
 
-  // table-build role of this warp: table bt, entries [be0, be0+32)
-  const int bt = warp >> 3, be0 = (warp & 7) * 32;
-  uint32_t *mytab = tab + (bt * 256 + be0) * TNW + lane;
-  const uint32_t *tl = tab + lane;
-
-  const int my_row = row0 + lane;
-  const uint32_t *arow = A + (size_t)my_row * as32;
-  const int npass = (k + 31) >> 5;
-  uint32_t a_next = (my_row < m && 0 < aw32) ? arow[0] : 0;
-
-  for (int p = 0; p < npass; p++) {
-    // ---- build: 8 rows of B -> 32 of the 256 combinations (this warp's share) ----
-    const int kb = p * 32 + bt * 8;
+  // ---- build role: table bt, entries [bhi*32, bhi*32+32), column word `lane` ----
+  // The 16 rows of B a phase needs are staged in shared memory by cp.async two
+  // phases ahead (no registers held across the gather, no exposed LDG latency).
+  const int bt = warp >> 3, bhi = warp & 7;
+  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(tab);
+  const uint32_t bstage = sbase + 4 * TAB_BYTES + 2 * ASTAGE_BYTES;  // [2][16 rows][128 B]
+  auto stage_b = [&](int ph) {
+    if (threadIdx.x < 128) {
+      const int j = threadIdx.x >> 3, c = threadIdx.x & 7;
+      const int krow = ph * 16 + j, cw0 = blockIdx.x * TNW + c * 4;
+      int bytes = (krow < k) ? (bw32 - cw0) * 4 : 0;
+      bytes = bytes < 0 ? 0 : (bytes > 16 ? 16 : bytes);
+      const uint32_t *src = B + (bytes ? (size_t)krow * bs32 + cw0 : 0);
+      cp_async16(bstage + (ph & 1) * 2048 + j * 128 + c * 16, src, bytes);
+    }
+  };
+  auto build = [&](int ph) {
+    const uint32_t *bs = tab + (4 * TAB_BYTES + 2 * ASTAGE_BYTES) / 4 + (ph & 1) * 512 + bt * 256 + lane;
     uint32_t b[8];
 #pragma unroll
-    for (int j = 0; j < 8; j++)
-      b[j] = (col_ok && kb + j < k) ? B[(size_t)(kb + j) * bs32 + cw] : 0;
-    // high three index bits are fixed per warp, low five run in Gray-code order
-    uint32_t cur = ((warp & 1) ? b[5] : 0) ^ ((warp & 2) ? b[6] : 0) ^ ((warp & 4) ? b[7] : 0);
-    mytab[0] = cur;
+    for (int j = 0; j < 8; j++) b[j] = bs[j * TNW];
+    uint32_t *dst = tab + ((ph & 1) * 2 + bt) * (TAB_BYTES / 4) + (bhi * 32) * TNW + lane;
+    uint32_t cur = ((bhi & 1) ? b[5] : 0u) ^ ((bhi & 2) ? b[6] : 0u) ^ ((bhi & 4) ? b[7] : 0u);
+    dst[0] = cur;
 #pragma unroll
     for (int g = 1; g < 32; g++) {
-      const int bit = __ffs(g) - 1;           // Gray code: step g flips bit ctz(g)
-      const int idx = g ^ (g >> 1);           // the index reached after the flip
-      cur ^= b[bit];
-      mytab[idx * TNW] = cur;
+      cur ^= b[__ffs(g) - 1];               // Gray code: step g flips bit ctz(g)
+      dst[(g ^ (g >> 1)) * TNW] = cur;      // ... and lands on index gray(g)
     }
-    const uint32_t a_mine = a_next;
-    if (p + 1 < npass) a_next = (my_row < m && p + 1 < aw32) ? arow[p + 1] : 0;
-    __syncthreads();
-    // ---- gather: 32 rows x 4 lookups per warp ----
+  };
+
+  // ---- A staging: group g = phases [8g, 8g+8) = 16 bytes of every tile row ----
+  const uint32_t abase = sbase + 4 * TAB_BYTES;
+  const int nph = (k + 15) >> 4;
+  const int ngrp = (nph + 7) >> 3;
+  auto stage_a = [&](int g) {
 #pragma unroll
-    for (int r = 0; r < 32; r++) {
-      const uint32_t a = __shfl_sync(0xffffffffu, a_mine, r);
-      const uint32_t t0 = tl[((a & 0xff)) * TNW];
-      const uint32_t t1 = tl[(256 + ((a >> 8) & 0xff)) * TNW];
-      const uint32_t t2 = tl[(512 + ((a >> 16) & 0xff)) * TNW];
-      const uint32_t t3 = tl[(768 + (a >> 24)) * TNW];
-      acc[r] ^= t0 ^ t1 ^ t2 ^ t3;
+    for (int h = 0; h < 2; h++) {
+      const int r = threadIdx.x + h * NTHR;
+      const int grow = blockIdx.y * TM + r;
+      int bytes = (grow < m) ? (aw32 - g * 4) * 4 : 0;
+      bytes = bytes < 0 ? 0 : (bytes > 16 ? 16 : bytes);
+      const uint32_t *src = A + (size_t)(grow < m ? grow : 0) * as32 + (bytes ? g * 4 : 0);
+      cp_async16(abase + (g & 1) * ASTAGE_BYTES + r * 16, src, bytes);
     }
-    __syncthreads();
-  }
-  if (cw < cw32) {
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+
+  // ---- gather role: rows row0 + 4s + q (s = 0..15), 16-byte column chunk l8 ----
+  const uint32_t gbase = sbase + l8 * 16;
+  const uint32_t arow_s = abase + (warp * 64 + q) * 16;  // + s*64 + stage + (ph&7)*2
+
+  stage_b(0);
+  if (nph > 1) stage_b(1);
+  stage_a(0);  // commits the group
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
+  build(0);
+  __syncthreads();
+  if (nph > 2) stage_b(2);  // slot 0 is free again once build(0) has read it
+  asm volatile("cp.async.commit_group;" ::: "memory");
+
+  for (int ph = 0; ph < nph; ph++) {
+    if (ph + 1 < nph) build(ph + 1);
+
+    const uint32_t t0 = gbase + (ph & 1) * 2 * TAB_BYTES;
+    const uint32_t ap = arow_s + ((ph >> 3) & 1) * ASTAGE_BYTES + (ph & 7) * 2;
+    // four batches of four steps: 4 index loads, then 8 independent LDS.128 in flight
 #pragma unroll
-    for (int r = 0; r < 32; r++) {
-      const int row = row0 + r;
-      if (row < m) {
-        uint32_t *dst = C + (size_t)row * cs32 + cw;
-        *dst = clear ? acc[r] : (*dst ^ acc[r]);
+    for (int bch = 0; bch < 4; bch++) {
+      uint32_t a[4];
+#pragma unroll
+      for (int i = 0; i < 4; i++) a[i] = lds_u16(ap + (bch * 4 + i) * 64);
+      uint4 x[4], y[4];
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        x[i] = lds128(t0 + ((a[i] & 0xffu) << 7));
+        y[i] = lds128(t0 + TAB_BYTES + ((a[i] >> 8) << 7));
       }
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        const int s = bch * 4 + i;
+        acc[s].x ^= x[i].x ^ y[i].x;
+        acc[s].y ^= x[i].y ^ y[i].y;
+        acc[s].z ^= x[i].z ^ y[i].z;
+        acc[s].w ^= x[i].w ^ y[i].w;
+      }
+    }
+    // stage B rows of phase ph+3 (their slot was last read by build(ph+1), a barrier
+    // ago) and, every 8 phases, the next 16 bytes of every A row; all of it has the
+    // whole next phase to land.
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    if (ph + 3 < nph) stage_b(ph + 3);
+    if ((ph & 7) == 0 && (ph >> 3) + 1 < ngrp) stage_a((ph >> 3) + 1);
+    else asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+
+  // ---- epilogue: 16-byte stores, word-guarded at the right edge ----
+  const int cw = blockIdx.x * TNW + l8 * 4;
+#pragma unroll
+  for (int s = 0; s < 16; s++) {
+    const int row = row0 + 4 * s + q;
+    if (row >= m || cw >= cw32) continue;
+    uint32_t *dst = C + (size_t)row * cs32 + cw;
+    if (cw + 4 <= cw32) {
+      uint4 v = acc[s];
+      if (!clear) {
+        const uint4 o = *reinterpret_cast<const uint4 *>(dst);
+        v.x ^= o.x; v.y ^= o.y; v.z ^= o.z; v.w ^= o.w;
+      }
+      *reinterpret_cast<uint4 *>(dst) = v;
+    } else {
+      const uint32_t v[4] = {acc[s].x, acc[s].y, acc[s].z, acc[s].w};
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+        if (cw + j < cw32) dst[j] = clear ? v[j] : (dst[j] ^ v[j]);
     }
   }
 }
@@ -100,6 +193,8 @@ void k_mul_m4rm(DMat *C, const DMat *A, const DMat *B, int clear, cudaStream_t s
     if (clear) k_zero(C, s);
     return;
   }
+  if (((uintptr_t)C->d & 15) || (C->rowstride & 1) || ((uintptr_t)A->d & 15) || (A->rowstride & 1))
+    die("m4ri_b200: m4rm kernel needs 16-byte aligned rows of A and C\n");
   static bool attr_set = false;
   if (!attr_set) {
     M4B_CUDA(cudaFuncSetAttribute(m4rm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -108,7 +203,7 @@ void k_mul_m4rm(DMat *C, const DMat *A, const DMat *B, int clear, cudaStream_t s
   }
   dim3 grid((C->width * 2 + TNW - 1) / TNW, (C->nrows + TM - 1) / TM);
   timing_begin("m4rm_kernel", s);
-  m4rm_kernel<<<grid, 1024, M4RM_SMEM, s>>>((uint32_t *)C->d, (const uint32_t *)A->d,
+  m4rm_kernel<<<grid, NTHR, M4RM_SMEM, s>>>((uint32_t *)C->d, (const uint32_t *)A->d,
                                             (const uint32_t *)B->d, C->nrows, A->ncols,
                                             A->width * 2, B->width * 2, C->width * 2,
                                             A->rowstride * 2, B->rowstride * 2, C->rowstride * 2,
