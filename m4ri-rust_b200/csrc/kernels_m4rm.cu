@@ -84,17 +84,21 @@ m4rm_kernel(uint32_t *__restrict__ C, const uint32_t *__restrict__ A,
   };
   auto build = [&](int ph) {
     const uint32_t *bs = tab + (4 * TAB_BYTES + 2 * ASTAGE_BYTES) / 4 + (ph & 1) * 512 + bt * 256 + lane;
-    uint32_t b[8];
-#pragma unroll
-    for (int j = 0; j < 8; j++) b[j] = bs[j * TNW];
+    const uint32_t b0 = bs[0 * TNW], b1 = bs[1 * TNW], b2 = bs[2 * TNW], b3 = bs[3 * TNW],
+                   b4 = bs[4 * TNW], b5 = bs[5 * TNW], b6 = bs[6 * TNW], b7 = bs[7 * TNW];
     uint32_t *dst = tab + ((ph & 1) * 2 + bt) * (TAB_BYTES / 4) + (bhi * 32) * TNW + lane;
-    uint32_t cur = ((bhi & 1) ? b[5] : 0u) ^ ((bhi & 2) ? b[6] : 0u) ^ ((bhi & 4) ? b[7] : 0u);
+    uint32_t cur = ((bhi & 1) ? b5 : 0u) ^ ((bhi & 2) ? b6 : 0u) ^ ((bhi & 4) ? b7 : 0u);
     dst[0] = cur;
-#pragma unroll
-    for (int g = 1; g < 32; g++) {
-      cur ^= b[__ffs(g) - 1];               // Gray code: step g flips bit ctz(g)
-      dst[(g ^ (g >> 1)) * TNW] = cur;      // ... and lands on index gray(g)
-    }
+    // low five index bits in Gray-code order: step g flips bit ctz(g) and lands on
+    // index g ^ (g >> 1); one XOR and one conflict-free store per entry
+#define M4B_STEP(g, bb) cur ^= bb; dst[((g) ^ ((g) >> 1)) * TNW] = cur;
+    M4B_STEP(1, b0) M4B_STEP(2, b1) M4B_STEP(3, b0) M4B_STEP(4, b2) M4B_STEP(5, b0) M4B_STEP(6, b1)
+    M4B_STEP(7, b0) M4B_STEP(8, b3) M4B_STEP(9, b0) M4B_STEP(10, b1) M4B_STEP(11, b0) M4B_STEP(12, b2)
+    M4B_STEP(13, b0) M4B_STEP(14, b1) M4B_STEP(15, b0) M4B_STEP(16, b4) M4B_STEP(17, b0)
+    M4B_STEP(18, b1) M4B_STEP(19, b0) M4B_STEP(20, b2) M4B_STEP(21, b0) M4B_STEP(22, b1)
+    M4B_STEP(23, b0) M4B_STEP(24, b3) M4B_STEP(25, b0) M4B_STEP(26, b1) M4B_STEP(27, b0)
+    M4B_STEP(28, b2) M4B_STEP(29, b0) M4B_STEP(30, b1) M4B_STEP(31, b0)
+#undef M4B_STEP
   };
 
   // ---- A staging: group g = phases [8g, 8g+8) = 16 bytes of every tile row ----
