@@ -113,6 +113,15 @@ int m4ri_b200_get_algo(void);
 /* Strassen-Winograd levels applied above the leaf kernel on device products:
  * -1 = automatic from `cutoff`/shape, 0 = none. */
 void m4ri_b200_set_strassen_levels(int levels);
+/* Kernel variant behind M4RI_B200_ALGO_MMA (0 restores the default; also
+ * settable with M4RI_B200_MMA=v1|v2cg1|v2): benchmarking knob. */
+enum m4ri_b200_mma_variant {
+  M4RI_B200_MMA_DEFAULT = 0,
+  M4RI_B200_MMA_V1 = 1,        /* one CTA per 128x128 tile, operands expanded into shared memory */
+  M4RI_B200_MMA_V2_SINGLE = 2, /* TMA-staged bits, A in tensor memory, cta_group::1              */
+  M4RI_B200_MMA_V2_PAIR = 3    /* the same on CTA pairs (cta_group::2), 256x256 tiles            */
+};
+void m4ri_b200_set_mma_variant(int variant);
 
 /* Number of usable CUDA devices (0 when there is none; never aborts). */
 int m4ri_b200_device_count(void);

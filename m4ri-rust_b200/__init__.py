@@ -24,6 +24,7 @@ HEADER_PATH = os.path.join(_HERE, "..", "include", "m4ri_b200.h")
 
 ALGO_AUTO, ALGO_M4RM, ALGO_MMA, ALGO_SIMPLE = 0, 1, 2, 3
 ALGO_NAMES = {"auto": 0, "m4rm": 1, "mma": 2, "simple": 3}
+MMA_VARIANTS = {"default": 0, "v1": 1, "v2cg1": 2, "v2": 3}
 
 
 class MzdBlock(ctypes.Structure):
@@ -74,6 +75,7 @@ def lib():
         "mzd_mul_v": (MzdP, [MzdP, MzdP, MzdP]),
         "m4ri_b200_set_algo": (None, [i]), "m4ri_b200_get_algo": (i, []),
         "m4ri_b200_set_strassen_levels": (None, [i]),
+        "m4ri_b200_set_mma_variant": (None, [i]),
         "m4ri_b200_device_count": (i, []),
         "m4ri_b200_device_info": (i, [ctypes.c_char_p, i, ctypes.POINTER(i), ctypes.POINTER(i), ctypes.POINTER(i)]),
         "m4ri_b200_set_stream": (None, [vp]), "m4ri_b200_synchronize": (None, []),

@@ -56,6 +56,7 @@ static int g_ndev = 0, g_sms = 0, g_cc_major = 0, g_cc_minor = 0;
 static char g_name[256] = "";
 static std::atomic<int> g_algo{-1};
 static std::atomic<int> g_strassen{-1};
+static std::atomic<int> g_mma_variant{0};
 
 static void probe() {
   int n = 0;
@@ -115,6 +116,19 @@ cudaStream_t current_stream() {
   if (t_use_user_stream) return t_user_stream;
   if (!t_own_stream) M4B_CUDA(cudaStreamCreateWithFlags(&t_own_stream, cudaStreamNonBlocking));
   return t_own_stream;
+}
+
+// ---- path (b) variant ----
+void k_mul_abt_mma(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream_t s) {
+  int v = g_mma_variant.load();
+  if (v == 0) {
+    const char *e = getenv("M4RI_B200_MMA");
+    v = !e ? M4RI_B200_MMA_V2_PAIR
+        : !strcmp(e, "v1") ? M4RI_B200_MMA_V1
+        : !strcmp(e, "v2cg1") ? M4RI_B200_MMA_V2_SINGLE : M4RI_B200_MMA_V2_PAIR;
+  }
+  if (v == M4RI_B200_MMA_V1) k_mul_abt_mma1(C, A, Bt, clear, s);
+  else k_mul_abt_mma2(C, A, Bt, clear, v == M4RI_B200_MMA_V2_SINGLE ? 1 : 2, s);
 }
 
 // ---- device matrices -------------------------------------------------------------
@@ -374,6 +388,10 @@ int m4ri_b200_get_algo(void) {
   return g_algo.load();
 }
 void m4ri_b200_set_strassen_levels(int levels) { g_strassen.store(levels); }
+void m4ri_b200_set_mma_variant(int variant) {
+  if (variant < 0 || variant > 3) die("m4ri_b200: unknown MMA variant %d\n", variant);
+  g_mma_variant.store(variant);
+}
 
 int m4ri_b200_device_count(void) {
   std::call_once(g_once, probe);

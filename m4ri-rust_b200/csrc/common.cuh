@@ -90,7 +90,12 @@ void k_mul_m4rm(DMat *C, const DMat *A, const DMat *B, int clear, cudaStream_t s
 
 // ---- kernels_mma.cu ----------------------------------------------------------
 // C (^)= A*Bt^T, bits -> int8 in shared memory / TMEM, tcgen05 MMA, parity
+// dispatcher (api.cu): picks the variant set by m4ri_b200_set_mma_variant
 void k_mul_abt_mma(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream_t s);
+// v1: one CTA per 128x128 tile, both operands expanded into shared memory (SS form)
+void k_mul_abt_mma1(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream_t s);
+// ---- kernels_mma2.cu: TMA-staged bits, A in tensor memory (TS form), cg CTAs per MMA
+void k_mul_abt_mma2(DMat *C, const DMat *A, const DMat *Bt, int clear, int cg, cudaStream_t s);
 bool mma_shape_ok(const DMat *C, const DMat *A, const DMat *Bt);
 bool mma_available();
 

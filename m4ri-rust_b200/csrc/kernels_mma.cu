@@ -271,7 +271,7 @@ bool mma_shape_ok(const DMat *C, const DMat *A, const DMat *Bt) {
          !(Bt->rowstride & 1) && !(C->rowstride & 1);
 }
 
-void k_mul_abt_mma(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream_t s) {
+void k_mul_abt_mma1(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream_t s) {
   if (C->nrows == 0 || C->ncols == 0) return;
   if (A->ncols == 0) {
     if (clear) k_zero(C, s);
