@@ -200,19 +200,124 @@ static int resolve_algo(int algo, int m, int k, int n) {
   return algo;
 }
 
+// ---- Strassen-Winograd outer recursion (what mzd_mul does above its cutoff,
+// m4ri-sys/src/strassen.rs:5-18) ---------------------------------------------------
+// form 0: C = A*B (B is k x n). form 1: C = A*Bt^T (Bt is n x k). 7 leaf products
+// and 14 XOR passes + 1 copy on quadrant windows per level; the XORs are HBM-bound
+// elementwise kernels (k_add) on quarter-size matrices.
+static DMat dwin(const DMat *M, int r0, int c0, int nr, int nc) {
+  DMat W;
+  W.d = M->d + (size_t)r0 * M->rowstride + c0 / 64;
+  W.nrows = nr;
+  W.ncols = nc;
+  W.width = width_of(nc);
+  W.rowstride = M->rowstride;
+  W.base = nullptr;
+  return W;
+}
+
+static void leaf_mul(DMat *C, const DMat *A, const DMat *B, int clear, int algo, int form,
+                     cudaStream_t s) {
+  if (form == 0) k_mul_m4rm(C, A, B, clear, s);
+  else if (algo == M4RI_B200_ALGO_MMA) k_mul_abt_mma(C, A, B, clear, s);
+  else k_mul_abt_simple(C, A, B, clear, s);
+}
+
+// C = A (*) B, overwriting C. Quadrant (i,j) of the logical k x n matrix B.
+static void strassen_mul(DMat *C, const DMat *A, const DMat *B, int algo, int form, int levels,
+                         cudaStream_t s) {
+  const int m = C->nrows, n = C->ncols, k = A->ncols;
+  // halves must stay 128-bit aligned column windows and whole 256-row tiles
+  if (levels <= 0 || (m % 512) || (n % 512) || (k % 512)) {
+    leaf_mul(C, A, B, 1, algo, form, s);
+    return;
+  }
+  const int m2 = m / 2, n2 = n / 2, k2 = k / 2;
+  auto Bq = [&](int i, int j) {
+    return form == 0 ? dwin(B, i * k2, j * n2, k2, n2) : dwin(B, j * n2, i * k2, n2, k2);
+  };
+  DMat A11 = dwin(A, 0, 0, m2, k2), A12 = dwin(A, 0, k2, m2, k2), A21 = dwin(A, m2, 0, m2, k2),
+       A22 = dwin(A, m2, k2, m2, k2);
+  DMat B11 = Bq(0, 0), B12 = Bq(0, 1), B21 = Bq(1, 0), B22 = Bq(1, 1);
+  DMat C11 = dwin(C, 0, 0, m2, n2), C12 = dwin(C, 0, n2, m2, n2), C21 = dwin(C, m2, 0, m2, n2),
+       C22 = dwin(C, m2, n2, m2, n2);
+  DMat *X = dmat_new(m2, k2, s), *Y = dmat_new(B11.nrows, B11.ncols, s), *Z = dmat_new(m2, n2, s);
+  const int L = levels - 1;
+  k_add(X, &A21, &A22, s);                       // S1
+  k_add(Y, &B11, &B12, s);                       // T1
+  strassen_mul(&C22, X, Y, algo, form, L, s);    // P5
+  k_copy(&C12, &C22, s);
+  k_add(X, X, &A11, s);                          // S2
+  k_add(Y, Y, &B22, s);                          // T2
+  strassen_mul(&C21, X, Y, algo, form, L, s);    // P6
+  strassen_mul(&C11, &A11, &B11, algo, form, L, s);  // P1
+  k_add(&C21, &C21, &C11, s);                    // U2 = P1 + P6
+  k_add(&C12, &C12, &C21, s);                    // U2 + P5
+  k_add(&C22, &C22, &C21, s);                    // U2 + P5
+  k_add(X, X, &A12, s);                          // S4
+  strassen_mul(Z, X, &B22, algo, form, L, s);    // P3
+  k_add(&C12, &C12, Z, s);                       // C12 done
+  k_add(Y, Y, &B21, s);                          // T4
+  strassen_mul(Z, &A22, Y, algo, form, L, s);    // P4
+  k_add(&C21, &C21, Z, s);
+  strassen_mul(Z, &A12, &B21, algo, form, L, s); // P2
+  k_add(&C11, &C11, Z, s);                       // C11 done
+  k_add(X, &A11, &A21, s);                       // S3
+  k_add(Y, &B22, &B12, s);                       // T3
+  strassen_mul(Z, X, Y, algo, form, L, s);       // P7
+  k_add(&C21, &C21, Z, s);                       // C21 done
+  k_add(&C22, &C22, Z, s);                       // C22 done
+  dmat_delete(X, s);
+  dmat_delete(Y, s);
+  dmat_delete(Z, s);
+}
+
+// Levels of recursion for an m x k x n product: the explicit setting, else as many
+// as keep every leaf dimension >= the cutoff (tuned on B200).
+static int strassen_levels(int m, int k, int n, int algo, int cutoff) {
+  if (cutoff < 0) return 0;  // the explicit Four-Russians entry points never recurse
+  int set = g_strassen.load();
+  if (set >= 0) return set;
+  if (cutoff <= 0) cutoff = algo == M4RI_B200_ALGO_MMA ? 8192 : 16384;
+  if (cutoff < 2048) cutoff = 2048;
+  int L = 0, d = m < k ? m : k;
+  d = d < n ? d : n;
+  while (L < 4 && d / 2 >= cutoff) {
+    d /= 2;
+    L++;
+  }
+  return L;
+}
+
+static void product_with_strassen(DMat *C, const DMat *A, const DMat *B, int clear, int algo,
+                                  int form, int cutoff, cudaStream_t s) {
+  const int L = strassen_levels(C->nrows, A->ncols, C->ncols, algo, cutoff);
+  if (L <= 0 || (C->nrows % 512) || (C->ncols % 512) || (A->ncols % 512)) {
+    leaf_mul(C, A, B, clear, algo, form, s);
+  } else if (clear) {
+    strassen_mul(C, A, B, algo, form, L, s);
+  } else {
+    DMat *T = dmat_new(C->nrows, C->ncols, s);
+    strassen_mul(T, A, B, algo, form, L, s);
+    k_add(C, C, T, s);
+    dmat_delete(T, s);
+  }
+}
+
 // C (^)= A*B on device
-static void dmul(DMat *C, const DMat *A, const DMat *B, int clear, int algo, cudaStream_t s) {
+static void dmul(DMat *C, const DMat *A, const DMat *B, int clear, int algo, cudaStream_t s,
+                 int cutoff = 0) {
   if (A->ncols != B->nrows || C->nrows != A->nrows || C->ncols != B->ncols)
     die("m4ri_b200: mul: shapes (%d x %d) * (%d x %d) -> (%d x %d) do not match\n", A->nrows,
         A->ncols, B->nrows, B->ncols, C->nrows, C->ncols);
   algo = resolve_algo(algo, C->nrows, A->ncols, C->ncols);
   if (algo == M4RI_B200_ALGO_M4RM) {
-    k_mul_m4rm(C, A, B, clear, s);
+    product_with_strassen(C, A, B, clear, algo, 0, cutoff, s);
     return;
   }
   DMat *Bt = dmat_new(B->ncols, B->nrows, s);
   k_transpose(Bt, B, s);
-  if (algo == M4RI_B200_ALGO_MMA) k_mul_abt_mma(C, A, Bt, clear, s);
+  if (algo == M4RI_B200_ALGO_MMA) product_with_strassen(C, A, Bt, clear, algo, 1, cutoff, s);
   else k_mul_abt_simple(C, A, Bt, clear, s);
   dmat_delete(Bt, s);
 }
@@ -224,11 +329,11 @@ static void dmul_abt(DMat *C, const DMat *A, const DMat *Bt, int clear, int algo
         A->nrows, A->ncols, Bt->nrows, Bt->ncols, C->nrows, C->ncols);
   algo = resolve_algo(algo, C->nrows, A->ncols, C->ncols);
   if (algo == M4RI_B200_ALGO_MMA) {
-    k_mul_abt_mma(C, A, Bt, clear, s);
+    product_with_strassen(C, A, Bt, clear, algo, 1, 0, s);
   } else if (algo == M4RI_B200_ALGO_M4RM) {
     DMat *B = dmat_new(Bt->ncols, Bt->nrows, s);
     k_transpose(B, Bt, s);
-    k_mul_m4rm(C, A, B, clear, s);
+    product_with_strassen(C, A, B, clear, algo, 0, 0, s);
     dmat_delete(B, s);
   } else {
     k_mul_abt_simple(C, A, Bt, clear, s);
@@ -237,7 +342,7 @@ static void dmul_abt(DMat *C, const DMat *A, const DMat *Bt, int clear, int algo
 
 // Shared body of the host-ABI products. form: 0 = A*B, 1 = A*Bt^T, 2 = v*A.
 static mzd_t *host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int clear, int algo, int form,
-                           const char *who) {
+                           const char *who, int cutoff = 0) {
   rci_t m = A->nrows, k = A->ncols;
   rci_t n = form == 1 ? B->nrows : B->ncols;
   rci_t kb = form == 1 ? B->ncols : B->nrows;
@@ -256,7 +361,7 @@ static mzd_t *host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int clear, 
   upload(dA, A, s);
   upload(dB, B, s);
   if (!clear) upload(dC, C, s);
-  if (form == 0) dmul(dC, dA, dB, clear, algo, s);
+  if (form == 0) dmul(dC, dA, dB, clear, algo, s, cutoff);
   else if (form == 1) dmul_abt(dC, dA, dB, clear, algo, s);
   else k_mul_va(dC, dA, dB, clear, s);
   download(C, dC, s);
@@ -275,24 +380,24 @@ extern "C" {
 
 // ---- hot-path entry points (reference declarations cited in include/m4ri_b200.h) ----
 mzd_t *mzd_mul(mzd_t *C, const mzd_t *A, const mzd_t *B, int cutoff) {
-  (void)cutoff;  // a tuning hint in M4RI; the product does not depend on it
-  return host_product(C, A, B, 1, M4RI_B200_ALGO_AUTO, 0, "mzd_mul");
+  // cutoff = minimal dimension for the Strassen recursion (0 = tuned default); the
+  // product does not depend on it
+  return host_product(C, A, B, 1, M4RI_B200_ALGO_AUTO, 0, "mzd_mul", cutoff < 0 ? 0 : cutoff);
 }
 mzd_t *mzd_addmul(mzd_t *C, const mzd_t *A, const mzd_t *B, int cutoff) {
-  (void)cutoff;
-  return host_product(C, A, B, 0, M4RI_B200_ALGO_AUTO, 0, "mzd_addmul");
+  return host_product(C, A, B, 0, M4RI_B200_ALGO_AUTO, 0, "mzd_addmul", cutoff < 0 ? 0 : cutoff);
 }
 mzd_t *mzd_mul_m4rm(mzd_t *C, const mzd_t *A, const mzd_t *B, int k) {
   (void)k;  // table width is fixed by the shared-memory budget
-  return host_product(C, A, B, 1, M4RI_B200_ALGO_M4RM, 0, "mzd_mul_m4rm");
+  return host_product(C, A, B, 1, M4RI_B200_ALGO_M4RM, 0, "mzd_mul_m4rm", -1);
 }
 mzd_t *mzd_addmul_m4rm(mzd_t *C, const mzd_t *A, const mzd_t *B, int k) {
   (void)k;
-  return host_product(C, A, B, 0, M4RI_B200_ALGO_M4RM, 0, "mzd_addmul_m4rm");
+  return host_product(C, A, B, 0, M4RI_B200_ALGO_M4RM, 0, "mzd_addmul_m4rm", -1);
 }
 mzd_t *_mzd_mul_m4rm(mzd_t *C, const mzd_t *A, const mzd_t *B, int k, int clear) {
   (void)k;
-  return host_product(C, A, B, clear != 0, M4RI_B200_ALGO_M4RM, 0, "_mzd_mul_m4rm");
+  return host_product(C, A, B, clear != 0, M4RI_B200_ALGO_M4RM, 0, "_mzd_mul_m4rm", -1);
 }
 mzd_t *mzd_mul_naive(mzd_t *C, const mzd_t *A, const mzd_t *B) {
   return host_product(C, A, B, 1, M4RI_B200_ALGO_SIMPLE, 0, "mzd_mul_naive");

@@ -72,37 +72,64 @@ void k_add(DMat *C, const DMat *A, const DMat *B, cudaStream_t s) {
 }
 
 // ---------------------------------------------------------------------------
-// transpose: 32 x 1024-bit input tiles, 32x32 bit blocks turned with ballots
+// transpose: 256-row x 1024-bit input tiles. 32x32 bit blocks are turned in
+// registers (five masked shuffle exchanges), collected in shared memory and
+// written as 32 contiguous bytes per output row (whole sectors). HBM-bound:
+// algorithmic bytes = 2 * nrows * width * 8.
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(1024)
-transpose_kernel(uint32_t *__restrict__ D, const uint32_t *__restrict__ S, int nrows, int ncols,
-                 int sw32, int ss32, int ds32) {
-  __shared__ uint32_t tile[32][33];
-  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-  const int r0 = blockIdx.y * 32, cw0 = blockIdx.x * 32;
-  uint32_t v = 0;
-  if (r0 + w < nrows && cw0 + l < sw32) v = S[(size_t)(r0 + w) * ss32 + cw0 + l];
-  tile[w][l] = v;
-  __syncthreads();
-  uint32_t x = tile[l][w];  // input row r0+l, input column word cw0+w
-  uint32_t out = 0;
+__device__ __forceinline__ uint32_t transpose32(uint32_t x, int lane) {
+  uint32_t m = 0x0000FFFFu;
 #pragma unroll
-  for (int j = 0; j < 32; j++) {
-    uint32_t b = __ballot_sync(0xffffffffu, (x >> j) & 1u);
-    if (l == j) out = b;
+  for (int sft = 16; sft; sft >>= 1) {
+    const uint32_t y = __shfl_xor_sync(0xffffffffu, x, sft);
+    x = (lane & sft) ? ((x & ~m) | ((y >> sft) & m)) : ((x & m) | ((y << sft) & ~m));
+    m ^= m << (sft >> 1);
   }
-  int orow = (cw0 + w) * 32 + l;  // = input column
-  if (orow < ncols) D[(size_t)orow * ds32 + (r0 >> 5)] = out;
+  return x;
+}
+
+__global__ void __launch_bounds__(256)
+transpose_kernel(uint32_t *__restrict__ D, const uint32_t *__restrict__ S, int nrows, int ncols,
+                 int sw32, int ss32, int ds32, int dw32) {
+  __shared__ uint32_t buf[256 * 33];
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  const int r0 = blockIdx.y * 256, cw0 = blockIdx.x * 32;
+#pragma unroll 8
+  for (int i = 0; i < 32; i++) {
+    const int row = i * 8 + w;
+    uint32_t v = 0;
+    if (r0 + row < nrows && cw0 + l < sw32) v = S[(size_t)(r0 + row) * ss32 + cw0 + l];
+    buf[row * 33 + l] = v;
+  }
+  __syncthreads();
+  // warp w turns the 32 blocks of input rows [32w, 32w+32): afterwards lane j of
+  // res[c] is word w of output row (cw0 + c) * 32 + j
+  uint32_t res[32];
+#pragma unroll
+  for (int c = 0; c < 32; c++) res[c] = transpose32(buf[(32 * w + l) * 33 + c], l);
+  __syncthreads();
+  // out tile: 1024 rows x 8 words, word index swizzled by the row (conflict-free both ways)
+#pragma unroll
+  for (int c = 0; c < 32; c++) buf[(c * 32 + l) * 8 + (w ^ ((l >> 2) & 7))] = res[c];
+  __syncthreads();
+#pragma unroll 8
+  for (int i = 0; i < 32; i++) {
+    const int idx = i * 256 + threadIdx.x;
+    const int orl = idx >> 3, g = idx & 7;
+    const int orow = cw0 * 32 + orl, ow = (r0 >> 5) + g;
+    if (orow < ncols && ow < dw32)
+      D[(size_t)orow * ds32 + ow] = buf[orl * 8 + (g ^ ((orl >> 2) & 7))];
+  }
 }
 
 void k_transpose(DMat *D, const DMat *A, cudaStream_t s) {
   if (A->nrows == 0 || A->ncols == 0) return;
-  int sw32 = A->width * 2;
+  const int sw32 = A->width * 2, dw32 = D->width * 2;
   // row blocks cover every 32-bit half of D's words, so stale bits of a reused
   // destination are overwritten with zeros (rows >= nrows read as zero)
-  dim3 grid(cdiv(sw32, 32), D->width * 2);
-  transpose_kernel<<<grid, 1024, 0, s>>>((uint32_t *)D->d, (const uint32_t *)A->d, A->nrows,
-                                         A->ncols, sw32, A->rowstride * 2, D->rowstride * 2);
+  dim3 grid(cdiv(sw32, 32), cdiv(dw32, 8));
+  transpose_kernel<<<grid, 256, 0, s>>>((uint32_t *)D->d, (const uint32_t *)A->d, A->nrows,
+                                        A->ncols, sw32, A->rowstride * 2, D->rowstride * 2, dw32);
   M4B_LAUNCHED();
 }
 

@@ -70,9 +70,14 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 __device__ __forceinline__ void mbar_arrive_local(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
-// arrive on a barrier that may live in the peer CTA (address from map_to_rank)
+// arrive on a barrier that may live in the peer CTA (address from map_to_rank).
+// Default semantics (release at CTA scope): a cluster-scope release compiles to
+// MEMBAR.ALL.GPU + ERRBAR on the expanders' critical path (22 % of all stall samples
+// in profiles/r1c_ncu_mma_v2_n16384.txt). The operand bytes themselves never travel
+// through the generic proxy of the other CTA: they are ordered for the tensor core by
+// fence.proxy.async (shared memory) and tcgen05.wait::st + tcgen05.fence (TMEM).
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cbar) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cbar) : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cbar) : "memory");
 }
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
@@ -85,7 +90,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   for (uint32_t spin = 0;; spin++) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t}"
         : "=r"(done)
         : "r"(bar), "r"(parity)
