@@ -179,6 +179,8 @@ void m4ri_b200_timing_reset(void);
 double m4ri_b200_timing_ms(void);
 int m4ri_b200_timing_count(void);
 const char *m4ri_b200_timing_name(void);
+/* Sum of 2*m*n*k over the recorded launches (Strassen leaves are smaller than the job). */
+double m4ri_b200_timing_ops(void);
 /* 64-bit XOR-fold checksum of all words (position-mixed), computed on device. */
 uint64_t m4ri_b200_dchecksum(const m4ri_b200_dmat_t *M);
 /* 1 iff every valid word is zero (OR-reduction on device). */

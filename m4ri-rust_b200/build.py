@@ -74,6 +74,25 @@ def build_microbench(force=False):
     return MICROBENCH
 
 
+CPP_TEST = os.path.join(LIBDIR, "test_friendly")
+
+
+def build_cpp_tests(force=False):
+    """The reference's unit tests replayed through the C++ mirror of its operator API
+    (include/m4ri_b200.hpp, tests/cpp/test_friendly.cpp), linked against the library."""
+    src = os.path.join(HERE, "..", "tests", "cpp", "test_friendly.cpp")
+    inc = os.path.join(HERE, "..", "include")
+    deps = [src, os.path.join(inc, "m4ri_b200.hpp"), os.path.join(inc, "m4ri_b200.h"), LIB]
+    if not force and os.path.exists(CPP_TEST) and all(os.path.getmtime(CPP_TEST) >= os.path.getmtime(d) for d in deps):
+        return CPP_TEST
+    for extra in ([], ["-DM4RI_RUST_M4RM_MUL"], ["-DM4RI_RUST_NAIVE_MUL"]):
+        out = CPP_TEST + {0: "", 1: "_m4rm", 2: "_naive"}[[[], ["-DM4RI_RUST_M4RM_MUL"], ["-DM4RI_RUST_NAIVE_MUL"]].index(extra)]
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", "-I", inc] + extra + [src, "-o", out,
+                               "-L", LIBDIR, "-lm4ri_b200", "-Wl,-rpath,$ORIGIN"])
+    return CPP_TEST
+
+
 if __name__ == "__main__":
     build_microbench(force="--force" in sys.argv)
     print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))
+    build_cpp_tests(force="--force" in sys.argv)

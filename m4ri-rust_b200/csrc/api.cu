@@ -32,7 +32,8 @@ static std::mutex g_tmu;
 static std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_tev;
 static bool g_timing_on = false;
 static const char *g_tname = "";
-void timing_begin(const char *kernel_name, cudaStream_t s) {
+static double g_tops = 0;
+void timing_begin(const char *kernel_name, cudaStream_t s, double ops) {
   if (!g_timing_on) return;
   std::lock_guard<std::mutex> g(g_tmu);
   if (g_tev.size() >= 4096) return;
@@ -42,6 +43,7 @@ void timing_begin(const char *kernel_name, cudaStream_t s) {
   M4B_CUDA(cudaEventRecord(a, s));
   g_tev.push_back({a, b});
   g_tname = kernel_name;
+  g_tops += ops;
 }
 void timing_end(cudaStream_t s) {
   if (!g_timing_on) return;
@@ -73,6 +75,15 @@ static void probe() {
       g_cc_major = p.major;
       g_cc_minor = p.minor;
       snprintf(g_name, sizeof(g_name), "%s", p.name);
+      // Device mirrors and Strassen temporaries come from the stream-ordered pool; keep freed
+      // blocks cached instead of returning them to the driver at every synchronize (a fresh
+      // 128 MiB cudaMallocAsync costs ~0.5 ms, three of them per host-ABI product).
+      cudaMemPool_t pool;
+      if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+        unsigned long long keep = ~0ull;
+        (void)cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+      }
+      (void)cudaGetLastError();
     } else {
       (void)cudaGetLastError();
       g_ndev = 0;
@@ -86,6 +97,8 @@ static void probe() {
     else if (!strcmp(e, "simple")) a = M4RI_B200_ALGO_SIMPLE;
   }
   g_algo.store(a);
+  const char *sl = getenv("M4RI_B200_STRASSEN");
+  if (sl && *sl) g_strassen.store(atoi(sl));
 }
 
 void require_device() {
@@ -192,10 +205,12 @@ static int resolve_algo(int algo, int m, int k, int n) {
   std::call_once(g_once, probe);
   if (algo == M4RI_B200_ALGO_AUTO) algo = g_algo.load();
   if (algo == M4RI_B200_ALGO_AUTO) {
-    // Tiny products are launch-latency bound: the AND+popc kernel has the smallest
-    // fixed cost. Otherwise the shared-memory Four-Russians kernel.
+    // Chosen on the evidence of profiles/ (DESIGN.md 5): the tcgen05 path wins at every
+    // size from n = 2048 up (4.43 vs 2.92 Pbit-op/s at n = 32768). Tiny products are
+    // launch-latency bound: the AND+popc kernel has the smallest fixed cost.
     long long work = (long long)m * n;
-    algo = (work <= 64LL * 64 || k <= 64) ? M4RI_B200_ALGO_SIMPLE : M4RI_B200_ALGO_M4RM;
+    if (work <= 64LL * 64 || k <= 64) algo = M4RI_B200_ALGO_SIMPLE;
+    else algo = mma_available() ? M4RI_B200_ALGO_MMA : M4RI_B200_ALGO_M4RM;
   }
   return algo;
 }
@@ -593,6 +608,7 @@ void m4ri_b200_timing_reset(void) {
   std::lock_guard<std::mutex> g(g_tmu);
   for (auto &p : g_tev) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
   g_tev.clear();
+  g_tops = 0;
   g_timing_on = true;
 }
 double m4ri_b200_timing_ms(void) {
@@ -611,6 +627,10 @@ int m4ri_b200_timing_count(void) {
   return (int)g_tev.size();
 }
 const char *m4ri_b200_timing_name(void) { return g_tname; }
+double m4ri_b200_timing_ops(void) {
+  std::lock_guard<std::mutex> g(g_tmu);
+  return g_tops;
+}
 uint64_t m4ri_b200_dchecksum(const m4ri_b200_dmat_t *M) { return k_checksum(M, current_stream()); }
 
 int m4ri_b200_dis_zero(const m4ri_b200_dmat_t *M) { return k_is_zero(M, current_stream()) ? 1 : 0; }

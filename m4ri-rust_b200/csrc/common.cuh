@@ -38,7 +38,8 @@ int sm_count();
 bool has_tcgen05();  // compute capability 10.x
 
 // Event pair around the dominant product kernel (api.cu; no-ops until enabled).
-void timing_begin(const char *kernel_name, cudaStream_t s);
+// `ops` = the 2*m*n*k bit-operations of this launch (summed for the roofline).
+void timing_begin(const char *kernel_name, cudaStream_t s, double ops);
 void timing_end(cudaStream_t s);
 
 static inline int width_of(int ncols) { return (ncols + 63) / 64; }

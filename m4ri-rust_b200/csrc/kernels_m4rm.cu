@@ -206,7 +206,7 @@ void k_mul_m4rm(DMat *C, const DMat *A, const DMat *B, int clear, cudaStream_t s
     attr_set = true;
   }
   dim3 grid((C->width * 2 + TNW - 1) / TNW, (C->nrows + TM - 1) / TM);
-  timing_begin("m4rm_kernel", s);
+  timing_begin("m4rm_kernel", s, 2.0 * C->nrows * C->ncols * A->ncols);
   m4rm_kernel<<<grid, NTHR, M4RM_SMEM, s>>>((uint32_t *)C->d, (const uint32_t *)A->d,
                                             (const uint32_t *)B->d, C->nrows, A->ncols,
                                             A->width * 2, B->width * 2, C->width * 2,

@@ -285,7 +285,7 @@ void k_mul_abt_mma1(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStrea
     attr_set = true;
   }
   const int tiles_m = (C->nrows + BM - 1) / BM, tiles_n = (C->ncols + BN - 1) / BN;
-  timing_begin("mma_i8_kernel", s);
+  timing_begin("mma_i8_kernel", s, 2.0 * C->nrows * C->ncols * A->ncols);
   mma_i8_kernel<<<tiles_m * tiles_n, MMA_THREADS, SMEM_BYTES, s>>>(
       (uint32_t *)C->d, (const uint4 *)A->d, (const uint4 *)Bt->d, C->nrows, C->ncols, A->ncols,
       A->rowstride / 2, Bt->rowstride / 2, C->rowstride * 2, C->width * 2, tiles_m, tiles_n, clear);

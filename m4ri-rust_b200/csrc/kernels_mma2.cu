@@ -509,7 +509,7 @@ static void launch_mma2(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaS
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    timing_begin(CG == 2 ? "mma2_kernel<2>" : "mma2_kernel<1>", s);
+    timing_begin(CG == 2 ? "mma2_kernel<2>" : "mma2_kernel<1>", s, 2.0 * C->nrows * C->ncols * kc);
     M4B_CUDA(cudaLaunchKernelEx(&cfg, mma2_kernel<CG>, (uint32_t *)C->d, tmA, tmB, C->nrows, C->ncols,
                                 kc, C->rowstride * 2, C->width * 2, tiles_m, tiles_n,
                                 (clear && k0 == 0) ? 1 : 0));
