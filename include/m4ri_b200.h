@@ -114,12 +114,14 @@ int m4ri_b200_get_algo(void);
  * -1 = automatic from `cutoff`/shape, 0 = none. */
 void m4ri_b200_set_strassen_levels(int levels);
 /* Kernel variant behind M4RI_B200_ALGO_MMA (0 restores the default; also
- * settable with M4RI_B200_MMA=v1|v2cg1|v2): benchmarking knob. */
+ * settable with M4RI_B200_MMA=v1|v2cg1|v2|fp4cg1|fp4): benchmarking knob. */
 enum m4ri_b200_mma_variant {
   M4RI_B200_MMA_DEFAULT = 0,
   M4RI_B200_MMA_V1 = 1,        /* one CTA per 128x128 tile, operands expanded into shared memory */
   M4RI_B200_MMA_V2_SINGLE = 2, /* TMA-staged bits, A in tensor memory, cta_group::1              */
-  M4RI_B200_MMA_V2_PAIR = 3    /* the same on CTA pairs (cta_group::2), 256x256 tiles            */
+  M4RI_B200_MMA_V2_PAIR = 3,   /* the same on CTA pairs (cta_group::2), 256x256 tiles            */
+  M4RI_B200_MMA_FP4_SINGLE = 4,/* bits -> E2M1 nibbles, kind::mxf4 (2x the int8 rate), cta_group::1 */
+  M4RI_B200_MMA_FP4_PAIR = 5   /* the same on CTA pairs, 256x256 tiles                           */
 };
 void m4ri_b200_set_mma_variant(int variant);
 
@@ -181,6 +183,11 @@ int m4ri_b200_timing_count(void);
 const char *m4ri_b200_timing_name(void);
 /* Sum of 2*m*n*k over the recorded launches (Strassen leaves are smaller than the job). */
 double m4ri_b200_timing_ops(void);
+/* Diagnostics for the FP4 variant: C = A*Bt^T with the fp32 accumulators of the tensor
+ * cores copied to acc (device pointer, nrows(C) x ncols(C) floats, row-major): every value
+ * must be exactly (number of common set bits)/4. cg = 1 or 2 CTAs per MMA. */
+void m4ri_b200_dmul_abt_fp4_debug(m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *A,
+                                  const m4ri_b200_dmat_t *Bt, void *acc, int cg);
 /* 64-bit XOR-fold checksum of all words (position-mixed), computed on device. */
 uint64_t m4ri_b200_dchecksum(const m4ri_b200_dmat_t *M);
 /* 1 iff every valid word is zero (OR-reduction on device). */

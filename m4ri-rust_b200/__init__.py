@@ -24,7 +24,7 @@ HEADER_PATH = os.path.join(_HERE, "..", "include", "m4ri_b200.h")
 
 ALGO_AUTO, ALGO_M4RM, ALGO_MMA, ALGO_SIMPLE = 0, 1, 2, 3
 ALGO_NAMES = {"auto": 0, "m4rm": 1, "mma": 2, "simple": 3}
-MMA_VARIANTS = {"default": 0, "v1": 1, "v2cg1": 2, "v2": 3}
+MMA_VARIANTS = {"default": 0, "v1": 1, "v2cg1": 2, "v2": 3, "fp4cg1": 4, "fp4": 5}
 
 
 class MzdBlock(ctypes.Structure):
@@ -88,6 +88,7 @@ def lib():
         "m4ri_b200_upload": (None, [vp, MzdP]), "m4ri_b200_download": (None, [MzdP, vp]),
         "m4ri_b200_dmul": (None, [vp, vp, vp, i, i]),
         "m4ri_b200_dmul_abt": (None, [vp, vp, vp, i, i]),
+        "m4ri_b200_dmul_abt_fp4_debug": (None, [vp, vp, vp, vp, i]),
         "m4ri_b200_dmul_v": (None, [vp, vp, vp, i]),
         "m4ri_b200_dmul_va": (None, [vp, vp, vp, i]),
         "m4ri_b200_dtranspose": (None, [vp, vp]), "m4ri_b200_dadd": (None, [vp, vp, vp]),

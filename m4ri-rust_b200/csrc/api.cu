@@ -138,9 +138,13 @@ void k_mul_abt_mma(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream
     const char *e = getenv("M4RI_B200_MMA");
     v = !e ? M4RI_B200_MMA_V2_PAIR
         : !strcmp(e, "v1") ? M4RI_B200_MMA_V1
-        : !strcmp(e, "v2cg1") ? M4RI_B200_MMA_V2_SINGLE : M4RI_B200_MMA_V2_PAIR;
+        : !strcmp(e, "v2cg1") ? M4RI_B200_MMA_V2_SINGLE
+        : !strcmp(e, "fp4cg1") ? M4RI_B200_MMA_FP4_SINGLE
+        : !strcmp(e, "fp4") ? M4RI_B200_MMA_FP4_PAIR : M4RI_B200_MMA_V2_PAIR;
   }
   if (v == M4RI_B200_MMA_V1) k_mul_abt_mma1(C, A, Bt, clear, s);
+  else if (v == M4RI_B200_MMA_FP4_SINGLE || v == M4RI_B200_MMA_FP4_PAIR)
+    k_mul_abt_mma4(C, A, Bt, clear, v == M4RI_B200_MMA_FP4_SINGLE ? 1 : 2, nullptr, s);
   else k_mul_abt_mma2(C, A, Bt, clear, v == M4RI_B200_MMA_V2_SINGLE ? 1 : 2, s);
 }
 
@@ -509,7 +513,7 @@ int m4ri_b200_get_algo(void) {
 }
 void m4ri_b200_set_strassen_levels(int levels) { g_strassen.store(levels); }
 void m4ri_b200_set_mma_variant(int variant) {
-  if (variant < 0 || variant > 3) die("m4ri_b200: unknown MMA variant %d\n", variant);
+  if (variant < 0 || variant > 5) die("m4ri_b200: unknown MMA variant %d\n", variant);
   g_mma_variant.store(variant);
 }
 
@@ -630,6 +634,12 @@ const char *m4ri_b200_timing_name(void) { return g_tname; }
 double m4ri_b200_timing_ops(void) {
   std::lock_guard<std::mutex> g(g_tmu);
   return g_tops;
+}
+void m4ri_b200_dmul_abt_fp4_debug(m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *A,
+                                  const m4ri_b200_dmat_t *Bt, void *acc, int cg) {
+  if (A->ncols != Bt->ncols || C->nrows != A->nrows || C->ncols != Bt->nrows)
+    die("m4ri_b200: dmul_abt_fp4_debug: shapes do not match\n");
+  k_mul_abt_mma4(C, A, Bt, 1, cg == 1 ? 1 : 2, (float *)acc, current_stream());
 }
 uint64_t m4ri_b200_dchecksum(const m4ri_b200_dmat_t *M) { return k_checksum(M, current_stream()); }
 

@@ -97,6 +97,9 @@ void k_mul_abt_mma(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream
 void k_mul_abt_mma1(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream_t s);
 // ---- kernels_mma2.cu: TMA-staged bits, A in tensor memory (TS form), cg CTAs per MMA
 void k_mul_abt_mma2(DMat *C, const DMat *A, const DMat *Bt, int clear, int cg, cudaStream_t s);
+// ---- kernels_mma4.cu: bits -> E2M1 nibbles, tcgen05 kind::mxf4 with unit scale factors
+void k_mul_abt_mma4(DMat *C, const DMat *A, const DMat *Bt, int clear, int cg, float *raw_acc,
+                    cudaStream_t s);
 bool mma_shape_ok(const DMat *C, const DMat *A, const DMat *Bt);
 bool mma_available();
 
