@@ -280,14 +280,19 @@ def main():
         # strictest denominator); the fraction of 2 x the driver-measured cuBLAS bf16 burst
         # (power-capped at ~1.3 GHz) is reported beside it.
         sm_max = (clocks.get("sm_max_mhz") or 1965) * 1e6
-        peak = 16384.0 * 148 * sm_max / 1e12
-        meas = 2.0 * pk["bf16_tflops"]
-        roof = {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TOP/s (int8, executed 2mnk)",
+        fp4 = "mma4" in kern_name  # kind::mxf4: 64 elements per row per MMA, twice kind::i8
+        per_clk = 32768.0 if fp4 else 16384.0
+        peak = per_clk * 148 * sm_max / 1e12
+        meas = (4.0 if fp4 else 2.0) * pk["bf16_tflops"]
+        roof = {"bound": "tensor", "achieved": achieved, "peak": peak,
+                "unit": "TOP/s (%s, executed 2mnk)" % ("fp4 e2m1" if fp4 else "int8"),
                 "frac": achieved / peak if achieved else None, "traffic": None,
-                "peak_source": "tcgen05 kind::i8 issue rate 16384 op/clk/SM x 148 SMs x max SM clock",
-                "peak_measured_2x_bf16": meas,
-                "frac_of_measured_2x_bf16": achieved / meas if achieved else None,
-                "peak_measured_source": f"2 x bf16_tflops (burst) of MEASURED_PEAKS.json ({pk['src']})"}
+                "peak_source": "tcgen05 %s issue rate %d op/clk/SM x 148 SMs x max SM clock" % (
+                    "kind::mxf4" if fp4 else "kind::i8", int(per_clk)),
+                "peak_measured_scaled_bf16": meas,
+                "frac_of_measured_scaled_bf16": achieved / meas if achieved else None,
+                "peak_measured_source": "%d x bf16_tflops (burst) of MEASURED_PEAKS.json (%s): the dense %s rate is %dx bf16" % (
+                    4 if fp4 else 2, pk["src"], "fp4" if fp4 else "int8", 4 if fp4 else 2)}
     else:
         # Four-Russians gather: bound by shared-memory load bandwidth, measured by
         # m4ri-rust_b200/lib/microbench (profiles/); expressed in the metric's unit

@@ -136,11 +136,11 @@ void k_mul_abt_mma(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream
   int v = g_mma_variant.load();
   if (v == 0) {
     const char *e = getenv("M4RI_B200_MMA");
-    v = !e ? M4RI_B200_MMA_V2_PAIR
+    v = !e ? M4RI_B200_MMA_FP4_PAIR
         : !strcmp(e, "v1") ? M4RI_B200_MMA_V1
         : !strcmp(e, "v2cg1") ? M4RI_B200_MMA_V2_SINGLE
         : !strcmp(e, "fp4cg1") ? M4RI_B200_MMA_FP4_SINGLE
-        : !strcmp(e, "fp4") ? M4RI_B200_MMA_FP4_PAIR : M4RI_B200_MMA_V2_PAIR;
+        : !strcmp(e, "v2") ? M4RI_B200_MMA_V2_PAIR : M4RI_B200_MMA_FP4_PAIR;
   }
   if (v == M4RI_B200_MMA_V1) k_mul_abt_mma1(C, A, Bt, clear, s);
   else if (v == M4RI_B200_MMA_FP4_SINGLE || v == M4RI_B200_MMA_FP4_PAIR)
@@ -297,7 +297,9 @@ static int strassen_levels(int m, int k, int n, int algo, int cutoff) {
   if (cutoff < 0) return 0;  // the explicit Four-Russians entry points never recurse
   int set = g_strassen.load();
   if (set >= 0) return set;
-  if (cutoff <= 0) cutoff = algo == M4RI_B200_ALGO_MMA ? 8192 : 16384;
+  // tuned on B200 (profiles/r1g_size_sweep_fp4.jsonl): one level pays from n = 32768 up on the
+  // tensor path (leaves of 16384), never on the Four-Russians path below n = 65536
+  if (cutoff <= 0) cutoff = algo == M4RI_B200_ALGO_MMA ? 16384 : 32768;
   if (cutoff < 2048) cutoff = 2048;
   int L = 0, d = m < k ? m : k;
   d = d < n ? d : n;

@@ -15,11 +15,13 @@
 //
 // Pipeline (one CTA per SM, CTA pairs with cta_group::2 own a 256 x 256 tile of C,
 // persistent over the tiles) — the same roles as kernels_mma2.cu:
-//   warp 9       TMA: packed bits of 128 rows of A and of Bt, 1024 k-bits per stage
-//   warps 0-3    A rows: 512 k-bits -> 512 nibbles -> TENSOR MEMORY (tcgen05.st)
-//   warps 4-7    Bt rows: the same into 128B-swizzled K-major shared memory
-//   warp 8       one lane of the leader CTA issues 8 MMAs (K = 64) per 512-bit k-step
-//   warps 10-13  epilogue: TMEM -> registers -> parity bits -> C
+//   warp 17        TMA: packed bits of 128 rows of A and of Bt, 1024 k-bits per stage
+//   warps 0-3,8-11 A rows: 256 k-bits -> 256 nibbles -> TENSOR MEMORY (tcgen05.st)
+//   warps 4-7,12-15 Bt rows: the same into 128B-swizzled K-major shared memory
+//                  (warp / 8 = which 256-bit half of the 512-bit k-step: 16 warps fill one
+//                  stage together, which halves the time a stage is being written)
+//   warp 16        one lane of the leader CTA issues 8 MMAs (K = 64) per 512-bit k-step
+//   warps 18-21    epilogue: TMEM -> registers -> parity bits -> C
 #include <cuda.h>
 
 #include "common.cuh"
@@ -38,7 +40,11 @@ constexpr int RAW_TILE = 128 * 128;        // 128 rows x 128 B of packed bits (A
 constexpr int RAW_STAGE = 2 * RAW_TILE;    // A rows then Bt rows
 constexpr int B_TILE = 128 * 128;          // 128 rows x 128 B = 256 nibbles per row, SWIZZLE_128B
 constexpr int B_STAGE = 2 * B_TILE;        // two 256-nibble k-halves of the 512-bit k-step
-constexpr int NWARPS = 14;
+constexpr int HALVES = 1;                  // warps sharing one row's k-step (1 or 2)
+constexpr int NEXP = 8 * HALVES;           // expander warps: HALVES x (4 A + 4 Bt)
+constexpr int WBITS = KSTEP_BITS / HALVES; // k bits one warp expands per k-step
+constexpr int WWORDS = WBITS / 32;
+constexpr int NWARPS = NEXP + 6;           // + MMA issuer, TMA producer, 4 epilogue warps
 constexpr int NTHREADS = NWARPS * 32;
 constexpr int SMEM_V4 = RAW_STAGES * RAW_STAGE + STAGES * B_STAGE + 1024 /*align*/ + 256 /*barriers*/;
 constexpr int TMEM_A_COL = 256;            // A stages: 64 columns each in [256, 448)
@@ -86,16 +92,16 @@ template <int CG>
 __global__ void __launch_bounds__(NTHREADS, 1)
 mma4_kernel(uint32_t *__restrict__ C, const __grid_constant__ CUtensorMap tmA,
             const __grid_constant__ CUtensorMap tmB, int m, int n, int k, int cs32, int cw32,
-            int tiles_m, int tiles_n, int clear, float *__restrict__ raw_acc) {
+            int tiles_m, int tiles_n, int clear, float *__restrict__ raw_acc, int dbg) {
   constexpr int NCOL = 128 * CG;  // accumulator columns = tile columns
   extern __shared__ uint8_t smem_raw[];
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B: 1024-B alignment
   const uint32_t raw_base = sbase;
   const uint32_t bexp_base = sbase + RAW_STAGES * RAW_STAGE;
   const uint32_t bars = bexp_base + STAGES * B_STAGE;
-  const uint32_t full_bar = bars, empty_bar = bars + 32, rawfull_bar = bars + 64,
-                 rawempty_bar = bars + 96, accum_bar = bars + 128, dempty_bar = bars + 136,
-                 tmem_slot = bars + 144;
+  const uint32_t full_bar = bars, empty_bar = bars + 64, rawfull_bar = bars + 128,
+                 rawempty_bar = bars + 160, accum_bar = bars + 192, dempty_bar = bars + 200,
+                 tmem_slot = bars + 208;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = CG == 1 ? 0u : cluster_ctarank();
   const int cluster_id = blockIdx.x / CG, nclusters = gridDim.x / CG;
@@ -105,18 +111,18 @@ mma4_kernel(uint32_t *__restrict__ C, const __grid_constant__ CUtensorMap tmA,
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; s++) {
-      mbar_init(full_bar + 8 * s, 8 * CG);  // one arrival per expander warp of every CTA of the pair
+      mbar_init(full_bar + 8 * s, NEXP * CG);  // one arrival per expander warp of every CTA of the pair
       mbar_init(empty_bar + 8 * s, 1);      // tcgen05.commit
     }
     for (int s = 0; s < RAW_STAGES; s++) {
       mbar_init(rawfull_bar + 8 * s, 1);    // expect_tx arrival + TMA bytes
-      mbar_init(rawempty_bar + 8 * s, 8);   // one arrival per expander warp
+      mbar_init(rawempty_bar + 8 * s, NEXP); // one arrival per expander warp
     }
     mbar_init(accum_bar, 1);                // tcgen05.commit after the last k-step of a tile
     mbar_init(dempty_bar, 4 * CG);          // one arrival per epilogue warp of every CTA
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 8) tmem_alloc_all<CG>(tmem_slot);
+  if (warp == NEXP) tmem_alloc_all<CG>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   if constexpr (CG == 2) cluster_sync_all();  // the peer's barriers exist before anyone arrives on them
@@ -124,18 +130,21 @@ mma4_kernel(uint32_t *__restrict__ C, const __grid_constant__ CUtensorMap tmA,
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
-  if (warp < 8) {
-    // ================= expanders: warps 0-3 -> A (TMEM), warps 4-7 -> Bt (smem) =================
-    const bool isA = warp < 4;
+  if (warp < NEXP) {
+    // ===== expanders: warps with (warp & 4) == 0 -> A (TMEM), the others -> Bt (smem); warp / 8
+    // selects which WBITS-bit part of every 512-bit k-step the warp turns into nibbles.
+    // No tail masking: bits past k are zero in memory (excess bits of a row are kept zero by
+    // every kernel of the library, columns past the row are zero-filled by TMA).
+    const int half = warp >> 3;
+    const bool isA = (warp & 4) == 0;
     const int r = (warp & 3) * 32 + lane;  // row of the 128-row slab = TMEM lane
     const uint32_t sw = (uint32_t)(r & 7);
     const uint32_t raw_row = raw_base + (isA ? 0 : RAW_TILE) + r * 128;
-    const uint32_t brow = bexp_base + (r >> 3) * 1024 + (r & 7) * 128;
+    const uint32_t brow = bexp_base + (half * WBITS / 256) * B_TILE + (r >> 3) * 1024 + (r & 7) * 128;
     const uint32_t lane_base = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
-    const uint32_t a_lane = lane_base + TMEM_A_COL;
+    const uint32_t a_lane = lane_base + TMEM_A_COL + half * (WBITS / 8);
     const uint32_t full_leader = map_to_rank(full_bar, 0);
-    const int tail = k - (nks - 1) * KSTEP_BITS;  // 1..512 valid bits in the last k-step
-    if (isA) {
+    if (isA && half == 0) {
       // every scale factor the MMAs can address is UE8M0 127 = 2^0 (any layout reads the same byte)
       uint32_t one[32];
 #pragma unroll
@@ -152,25 +161,19 @@ mma4_kernel(uint32_t *__restrict__ C, const __grid_constant__ CUtensorMap tmA,
         const uint32_t rs = rit % RAW_STAGES;
         if (q == 0) mbar_wait(rawfull_bar + 8 * rs, (rit / RAW_STAGES) & 1);
         const uint32_t rrow = raw_row + rs * RAW_STAGE;
-        uint32_t x[16];
+        uint32_t x[WWORDS];
 #pragma unroll
-        for (int c = 0; c < 4; c++) {
-          const uint4 v4 = lds128(rrow + (((uint32_t)(4 * q + c) ^ sw) << 4));
+        for (int c = 0; c < WWORDS / 4; c++) {
+          const uint4 v4 = lds128(rrow + (((uint32_t)(4 * q + (WWORDS / 4) * half + c) ^ sw) << 4));
           x[4 * c] = v4.x; x[4 * c + 1] = v4.y; x[4 * c + 2] = v4.z; x[4 * c + 3] = v4.w;
-        }
-        if (ks == nks - 1 && tail < KSTEP_BITS) {
-#pragma unroll
-          for (int j = 0; j < 16; j++) {
-            const int lo = j * 32;
-            x[j] = tail <= lo ? 0u : (tail >= lo + 32 ? x[j] : (x[j] & ((1u << (tail - lo)) - 1u)));
-          }
         }
         const uint32_t s = it % STAGES;
         mbar_wait(empty_bar + 8 * s, ((it / STAGES) & 1) ^ 1);
-        if (isA) {
+        if (dbg & 1) {
+        } else if (isA) {
           tc_fence_after();
 #pragma unroll
-          for (int h = 0; h < 2; h++) {
+          for (int h = 0; h < WWORDS / 8; h++) {
             uint32_t v[32];
 #pragma unroll
             for (int c = 0; c < 8; c++)
@@ -180,10 +183,10 @@ mma4_kernel(uint32_t *__restrict__ C, const __grid_constant__ CUtensorMap tmA,
           }
           tmem_wait_st();
           tc_fence_before();
-        } else {
+        } else if (!(dbg & 2)) {
           const uint32_t dst = brow + s * B_STAGE;
 #pragma unroll
-          for (int h = 0; h < 2; h++)
+          for (int h = 0; h < WWORDS / 8; h++)
 #pragma unroll
             for (int c = 0; c < 8; c++) {
               const uint32_t w = x[8 * h + c];
@@ -200,7 +203,7 @@ mma4_kernel(uint32_t *__restrict__ C, const __grid_constant__ CUtensorMap tmA,
         if (q == RAW_KSTEPS - 1 || ks == nks - 1) rit++;
       }
     }
-  } else if (warp == 8) {
+  } else if (warp == NEXP) {
     // ================= MMA issuer: one lane of the leader CTA =================
     if (rank == 0 && lane == 0) {
       constexpr uint32_t idesc = make_idesc_mxf4(128 * CG, NCOL);
@@ -231,7 +234,7 @@ mma4_kernel(uint32_t *__restrict__ C, const __grid_constant__ CUtensorMap tmA,
         umma_commit<CG>(accum_bar);
       }
     }
-  } else if (warp == 9) {
+  } else if (warp == NEXP + 1) {
     // ================= TMA producer =================
     if (lane == 0) {
       uint32_t rit = 0;
@@ -241,7 +244,7 @@ mma4_kernel(uint32_t *__restrict__ C, const __grid_constant__ CUtensorMap tmA,
         const int arow = (tm * CG + (int)rank) * 128, brow = (tn * CG + (int)rank) * 128;
         for (int ri = 0; ri < nrs; ri++, rit++) {
           const uint32_t rs = rit % RAW_STAGES;
-          mbar_wait(rawempty_bar + 8 * rs, ((rit / RAW_STAGES) & 1) ^ 1);
+          mbar_wait_long(rawempty_bar + 8 * rs, ((rit / RAW_STAGES) & 1) ^ 1);
           mbar_expect_tx(rawfull_bar + 8 * rs, RAW_STAGE);
           tma_load_2d(raw_base + rs * RAW_STAGE, &tmA, ri * 128, arow, rawfull_bar + 8 * rs);
           tma_load_2d(raw_base + rs * RAW_STAGE + RAW_TILE, &tmB, ri * 128, brow, rawfull_bar + 8 * rs);
@@ -249,7 +252,7 @@ mma4_kernel(uint32_t *__restrict__ C, const __grid_constant__ CUtensorMap tmA,
       }
     }
   } else {
-    // ================= epilogue: warps 10-13, TMEM lane quarter = warp % 4 =================
+    // ================= epilogue: the last four warps, TMEM lane quarter = warp % 4 =================
     const int qd = warp & 3;
     const uint32_t dempty_leader = map_to_rank(dempty_bar, 0);
     uint32_t tile_it = 0;
@@ -257,7 +260,7 @@ mma4_kernel(uint32_t *__restrict__ C, const __grid_constant__ CUtensorMap tmA,
       int tm, tn;
       tile_coords(t, tiles_m, tiles_n, tm, tn);
       const int row = (tm * CG + (int)rank) * 128 + qd * 32 + lane;
-      mbar_wait(accum_bar, tile_it & 1);
+      mbar_wait_long(accum_bar, tile_it & 1);
       tc_fence_after();
       uint32_t out[NCOL / 32];
 #pragma unroll
@@ -306,7 +309,7 @@ mma4_kernel(uint32_t *__restrict__ C, const __grid_constant__ CUtensorMap tmA,
   tc_fence_before();
   __syncthreads();
   if constexpr (CG == 2) cluster_sync_all();
-  if (warp == 8) tmem_dealloc_all<CG>(tmem_base);
+  if (warp == NEXP) tmem_dealloc_all<CG>(tmem_base);
 }
 
 }  // namespace
@@ -325,6 +328,7 @@ static void launch_mma4(DMat *C, const DMat *A, const DMat *Bt, int clear, float
   const int ntiles = tiles_m * tiles_n;
   int nclusters = sm_count() / CG;
   if (nclusters > ntiles) nclusters = ntiles;
+  static const int dbg = getenv("M4RI_B200_DBG") ? atoi(getenv("M4RI_B200_DBG")) : 0;  // perf experiments only
   for (int k0 = 0; k0 < A->ncols; k0 += K_CHUNK_MAX) {
     const int kc = A->ncols - k0 < K_CHUNK_MAX ? A->ncols - k0 : K_CHUNK_MAX;
     const CUtensorMap tmA = packed_rows_map(A->d + k0 / 64, A->nrows, width_of(kc), A->rowstride);
@@ -344,7 +348,7 @@ static void launch_mma4(DMat *C, const DMat *A, const DMat *Bt, int clear, float
     timing_begin(CG == 2 ? "mma4_kernel<2>" : "mma4_kernel<1>", s, 2.0 * C->nrows * C->ncols * kc);
     M4B_CUDA(cudaLaunchKernelEx(&cfg, mma4_kernel<CG>, (uint32_t *)C->d, tmA, tmB, C->nrows, C->ncols,
                                 kc, C->rowstride * 2, C->width * 2, tiles_m, tiles_n,
-                                (clear && k0 == 0) ? 1 : 0, raw_acc));
+                                (clear && k0 == 0) ? 1 : 0, raw_acc, dbg));
     M4B_LAUNCHED();
     timing_end(s);
   }

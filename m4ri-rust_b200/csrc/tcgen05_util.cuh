@@ -74,6 +74,35 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     }
   }
 }
+// The same for waits that normally last thousands of cycles (epilogue waiting for a tile,
+// TMA producer waiting for a free stage): the thread is suspended by the hardware for up to
+// `hint_ns` and woken when the phase completes, instead of re-issuing try_wait every ~70
+// cycles — in profiles/r1g_ncu_mma4_n32768.txt the polling loops were 3/4 of all issued
+// instructions and took issue slots from the expander warps of the same scheduler.
+__device__ __forceinline__ void mbar_wait_long(uint32_t bar, uint32_t parity, uint32_t hint_ns = 20000u) {
+  uint32_t done = 0;
+  unsigned long long t0 = 0;
+  for (uint32_t spin = 0;; spin++) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity), "r"(hint_ns)
+        : "memory");
+    if (done) return;
+    if ((spin & 0x3f) == 0x3f) {
+      unsigned long long now;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 4000000000ull) {
+        printf("m4ri_b200: tcgen05 pipeline stalled (block %d thread %d barrier %u parity %u)\n",
+               (int)blockIdx.x, (int)threadIdx.x, bar, parity);
+        __trap();
+      }
+    }
+  }
+}
 __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }

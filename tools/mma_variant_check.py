@@ -16,7 +16,7 @@ SWEEP = [(128, 256, 128), (256, 256, 256), (128, 1024, 128), (256, 2048, 256), (
          (191, 193, 129), (200, 257, 321), (5, 700, 1100), (1030, 40, 1030), (1024, 1024, 1024),
          (257, 2050, 1500), (256, 4096, 128), (1500, 96, 70), (3000, 5000, 2500), (700, 9000, 300)]
 bad = 0
-for (m, k, n) in SWEEP:
+for (m, k, n) in ([] if '--time-only' in sys.argv else SWEEP):
     A, B = oracle.random(m, k, 77 + m), oracle.random(k, n, 99 + n)
     want = oracle.mul_m4rm(A, B, k, n, threads=0)[:, : oracle.width(n)]
     a, b = m4.mzd_from_words(A, k), m4.mzd_from_words(B, n)
@@ -34,9 +34,9 @@ for (m, k, n) in SWEEP:
     else:
         print(f"{variant} {m}x{k}x{n}: ok", flush=True)
 print(f"{variant}: {len(SWEEP) - bad}/{len(SWEEP)} shapes bit-exact", flush=True)
-if "--time" in sys.argv and bad == 0:
+if ("--time" in sys.argv or "--time-only" in sys.argv) and bad == 0:
     import ctypes
-    for n in (4096, 8192, 16384, 32768):
+    for n in ((32768,) if '--time-only' in sys.argv else (4096, 8192, 16384, 32768)):
         dA, dB, dBt, dC = (m4.DMat.init(n, n) for _ in range(4))
         dA.fill_random(1); dB.fill_random(2)
         L.m4ri_b200_dtranspose(dBt.h, dB.h)

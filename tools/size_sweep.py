@@ -13,7 +13,7 @@ out = []
 for n in sizes:
     dA, dB, dC = (m4.DMat.init(n, n) for _ in range(3))
     dA.fill_random(1); dB.fill_random(2)
-    for algo in ("m4rm", "mma"):
+    for algo in (os.environ.get("SWEEP_ALGOS", "m4rm,mma").split(",")):
         for lv in (0, 1, 2, 3):
             if n // (1 << lv) < 2048:
                 continue
