@@ -125,6 +125,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--n", type=int, default=0)
     ap.add_argument("--algo", default="auto", choices=["auto", "m4rm", "mma", "simple"])
+    ap.add_argument("--chunks", type=int, default=2, help="k-chunks of the broadcast of B (N > 1)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
@@ -133,7 +134,8 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     n = args.n or (32768 if world == 1 else 65536)
     workload = f"square mzd_mul n={n} random" + (
-        "" if world == 1 else f", C/A row-blocks sharded over {world} ranks, NCCL broadcast of B per step")
+        "" if world == 1 else f", C/A row-blocks sharded over {world} ranks, NCCL broadcast of B per step "
+        f"in {args.chunks} k-chunks overlapped with the product")
     config = {"workload": workload, "m": n, "k": n, "n": n, "algo": args.algo,
               "l2": "operands (3 x n*n/8 bytes) exceed the 126 MB L2; no explicit flush" if n >= 32768
               else "L2 flushed between steps by writing a 256 MiB buffer"}
@@ -170,8 +172,8 @@ def main():
     algo = m4.ALGO_NAMES[args.algo]
 
     # row-block of this rank
-    rows = n // world
-    r0 = rank * rows
+    from m4ri_rust_b200 import sharded
+    r0, rows = sharded.row_block(n, world, rank)
     ws = n // 64  # words per row (n % 128 == 0 so device stride == width)
     tA = torch.empty((rows, ws), dtype=torch.int64, device="cuda")
     tB = torch.empty((n, ws), dtype=torch.int64, device="cuda")
@@ -187,11 +189,11 @@ def main():
     else:
         tB.zero_()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda") if n < 32768 else None
-
-    def step():
-        if dist is not None:
-            dist.broadcast(tB, src=0)
-        m4.dmul(dC, dA, dB, clear=True, algo=algo)
+    # one step = NCCL broadcast of B from rank 0 in k-chunks (N > 1), each chunk's product
+    # overlapped with the next chunk's transfer (m4ri-rust_b200/sharded.py)
+    sm = sharded.ShardedMul(n, n, n, dist=dist, src=0, chunks=args.chunks, tB=tB,
+                            chunk_product=sharded.gpu_chunk_product(m4, tA, tB, tC, rows, n, n, algo))
+    step = sm.step
 
     def barrier():
         torch.cuda.synchronize()

@@ -170,39 +170,48 @@ static void dmat_delete(DMat *M, cudaStream_t s) {
   free(M);
 }
 
-static void upload(DMat *D, const mzd_t *H, cudaStream_t s) {
+// Rows [r0, r1) of H -> the same rows of D. rows[] is the only thing the reference
+// guarantees ("multi-block"): maximal runs of evenly strided rows go as one
+// 2-D copy each.
+static void upload_rows(DMat *D, const mzd_t *H, rci_t r0, rci_t r1, cudaStream_t s) {
   if (D->nrows != H->nrows || D->ncols != H->ncols)
     die("m4ri_b200: upload: shape mismatch (%d x %d vs %d x %d)\n", D->nrows, D->ncols, H->nrows,
         H->ncols);
-  if (H->nrows == 0 || H->width == 0) return;
-  // rows[] is the only thing the reference guarantees ("multi-block");
-  // copy maximal runs of evenly strided rows with one 2-D copy each.
-  rci_t i = 0;
-  while (i < H->nrows) {
+  if (r1 <= r0 || H->width == 0) return;
+  rci_t i = r0;
+  while (i < r1) {
     rci_t j = i + 1;
-    while (j < H->nrows && H->rows[j] == H->rows[i] + (size_t)(j - i) * H->rowstride) j++;
+    while (j < r1 && H->rows[j] == H->rows[i] + (size_t)(j - i) * H->rowstride) j++;
     M4B_CUDA(cudaMemcpy2DAsync(D->d + (size_t)i * D->rowstride, (size_t)D->rowstride * 8,
                                H->rows[i], (size_t)H->rowstride * 8, (size_t)H->width * 8, j - i,
                                cudaMemcpyHostToDevice, s));
     i = j;
   }
-  k_mask_excess(D, s);  // never trust excess bits of a caller's matrix
+  if (D->ncols % 64) {  // never trust excess bits of a caller's matrix
+    DMat W = *D;
+    W.d = D->d + (size_t)r0 * D->rowstride;
+    W.nrows = r1 - r0;
+    W.base = nullptr;
+    k_mask_excess(&W, s);
+  }
 }
+static void upload(DMat *D, const mzd_t *H, cudaStream_t s) { upload_rows(D, H, 0, H->nrows, s); }
 
-static void download(mzd_t *H, const DMat *D, cudaStream_t s) {
+static void download_rows(mzd_t *H, const DMat *D, rci_t r0, rci_t r1, cudaStream_t s) {
   if (D->nrows != H->nrows || D->ncols != H->ncols)
     die("m4ri_b200: download: shape mismatch\n");
-  if (H->nrows == 0 || H->width == 0) return;
-  rci_t i = 0;
-  while (i < H->nrows) {
+  if (r1 <= r0 || H->width == 0) return;
+  rci_t i = r0;
+  while (i < r1) {
     rci_t j = i + 1;
-    while (j < H->nrows && H->rows[j] == H->rows[i] + (size_t)(j - i) * H->rowstride) j++;
+    while (j < r1 && H->rows[j] == H->rows[i] + (size_t)(j - i) * H->rowstride) j++;
     M4B_CUDA(cudaMemcpy2DAsync(H->rows[i], (size_t)H->rowstride * 8,
                                D->d + (size_t)i * D->rowstride, (size_t)D->rowstride * 8,
                                (size_t)H->width * 8, j - i, cudaMemcpyDeviceToHost, s));
     i = j;
   }
 }
+static void download(mzd_t *H, const DMat *D, cudaStream_t s) { download_rows(H, D, 0, H->nrows, s); }
 
 // ---- algorithm choice ---------------------------------------------------------------
 static int resolve_algo(int algo, int m, int k, int n) {
@@ -361,6 +370,59 @@ static void dmul_abt(DMat *C, const DMat *A, const DMat *Bt, int clear, int algo
   }
 }
 
+// Large host-ABI products on the tensor path: the PCIe copies are hidden behind the
+// kernels. B goes up first (and is bit-transposed once); then A travels in row-chunks on a
+// copy stream while the tensor cores multiply the previous chunk and a third stream brings
+// finished rows of C back — H2D, compute and D2H overlap (separate copy engines), so the
+// call costs about upload(B) + kernels instead of upload(A,B) + kernels + download(C).
+static thread_local cudaStream_t t_h2d = nullptr, t_d2h = nullptr;
+static const size_t PIPELINE_MIN_BYTES = (size_t)24 << 20;
+
+static void pipelined_host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int clear, int form,
+                                   cudaStream_t s) {
+  if (!t_h2d) M4B_CUDA(cudaStreamCreateWithFlags(&t_h2d, cudaStreamNonBlocking));
+  if (!t_d2h) M4B_CUDA(cudaStreamCreateWithFlags(&t_d2h, cudaStreamNonBlocking));
+  const rci_t m = A->nrows, n = C->ncols;
+  DMat *dA = dmat_new(A->nrows, A->ncols, s), *dB = dmat_new(B->nrows, B->ncols, s),
+       *dC = dmat_new(m, n, s);
+  DMat *dBt = form == 0 ? dmat_new(B->ncols, B->nrows, s) : dB;
+  int nchunks = 8;
+  rci_t per = ((m + nchunks - 1) / nchunks + 255) / 256 * 256;
+  nchunks = (m + per - 1) / per;
+  std::vector<cudaEvent_t> ev(2 * nchunks + 2);
+  for (auto &e : ev) M4B_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  cudaEvent_t e_alloc = ev[2 * nchunks], e_b = ev[2 * nchunks + 1];
+  M4B_CUDA(cudaEventRecord(e_alloc, s));  // buffers exist and are zeroed
+  M4B_CUDA(cudaStreamWaitEvent(t_h2d, e_alloc, 0));
+  upload(dB, B, t_h2d);
+  M4B_CUDA(cudaEventRecord(e_b, t_h2d));
+  for (int i = 0; i < nchunks; i++) {
+    const rci_t r0 = i * per, r1 = r0 + per < m ? r0 + per : m;
+    upload_rows(dA, A, r0, r1, t_h2d);
+    if (!clear) upload_rows(dC, C, r0, r1, t_h2d);
+    M4B_CUDA(cudaEventRecord(ev[i], t_h2d));
+  }
+  M4B_CUDA(cudaStreamWaitEvent(s, e_b, 0));
+  if (form == 0) k_transpose(dBt, dB, s);
+  for (int i = 0; i < nchunks; i++) {
+    const rci_t r0 = i * per, r1 = r0 + per < m ? r0 + per : m;
+    DMat Ai = dwin(dA, r0, 0, r1 - r0, A->ncols), Ci = dwin(dC, r0, 0, r1 - r0, n);
+    M4B_CUDA(cudaStreamWaitEvent(s, ev[i], 0));
+    k_mul_abt_mma(&Ci, &Ai, dBt, clear, s);
+    M4B_CUDA(cudaEventRecord(ev[nchunks + i], s));
+    M4B_CUDA(cudaStreamWaitEvent(t_d2h, ev[nchunks + i], 0));
+    download_rows(C, dC, r0, r1, t_d2h);
+  }
+  M4B_CUDA(cudaEventRecord(e_alloc, t_d2h));  // reuse: everything has left the device
+  M4B_CUDA(cudaStreamWaitEvent(s, e_alloc, 0));
+  if (dBt != dB) dmat_delete(dBt, s);
+  dmat_delete(dA, s);
+  dmat_delete(dB, s);
+  dmat_delete(dC, s);
+  M4B_CUDA(cudaStreamSynchronize(s));
+  for (auto &e : ev) M4B_CUDA(cudaEventDestroy(e));
+}
+
 // Shared body of the host-ABI products. form: 0 = A*B, 1 = A*Bt^T, 2 = v*A.
 static mzd_t *host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int clear, int algo, int form,
                            const char *who, int cutoff = 0) {
@@ -377,6 +439,13 @@ static mzd_t *host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int clear, 
   }
   if (C == A || C == B) die("m4ri_b200: %s: C must not alias an input\n", who);
   cudaStream_t s = current_stream();
+  if (form != 2 && m > 0 && n > 0 && k > 0 && resolve_algo(algo, m, k, n) == M4RI_B200_ALGO_MMA &&
+      ((size_t)m * A->width + (size_t)B->nrows * B->width) * 8 >= PIPELINE_MIN_BYTES &&
+      strassen_levels(m, k, n, M4RI_B200_ALGO_MMA, cutoff) <= 1) {
+    // (deeper recursions only pay beyond n = 65536, where the 7/8 per level outweighs the copies)
+    pipelined_host_product(C, A, B, clear, form, s);
+    return C;
+  }
   DMat *dA = dmat_new(A->nrows, A->ncols, s), *dB = dmat_new(B->nrows, B->ncols, s),
        *dC = dmat_new(m, n, s);
   upload(dA, A, s);

@@ -302,3 +302,39 @@ def test_lpn_shape(gpu, m4, orc):
         assert L.m4ri_b200_dfreivalds(dC.h, dA.h, dB.h, 7) == 1
         head = m4.DMat.wrap(dC.ptr, rows, n, dC.rowstride, keepalive=dC)
         assert (head.to_words() == want).all()
+
+
+def test_pipelined_host_products(gpu, m4, orc):
+    """Host-ABI products large enough for the copy/compute-overlapped path (api.cu,
+    pipelined_host_product): ragged shapes, accumulate, an operand that is a window of
+    a bigger matrix (rows[] with a foreign stride), and the pre-transposed form."""
+    L = m4.lib()
+    for (m, k, n) in [(5000, 20000, 9000), (2049, 30001, 4099), (9000, 16384, 8192)]:
+        A, B, C0 = orc.random(m, k, 21), orc.random(k, n, 22), orc.random(m, n, 23)
+        want = orc.mul_m4rm(A, B, k, n, threads=0)[:, : orc.width(n)]
+        a, b = host(m4, A, k), host(m4, B, n)
+        assert (result_words(m4, L.mzd_mul(None, a, b, 0)) == want).all(), (m, k, n)
+        c = host(m4, C0, n)
+        L.mzd_addmul(c, a, b, 0)
+        assert (result_words(m4, c, free=False) == (C0[:, : orc.width(n)] ^ want)).all(), (m, k, n)
+        L.mzd_addmul(c, a, b, 0)
+        assert (result_words(m4, c) == C0[:, : orc.width(n)]).all()
+        # A*Bt^T with the tensor path forced (the *_naive entry maps to the simple kernel otherwise)
+        bt = L.mzd_transpose(None, b)
+        L.m4ri_b200_set_algo(m4.ALGO_MMA)
+        got = result_words(m4, L._mzd_mul_naive(None, a, bt, 1))
+        L.m4ri_b200_set_algo(m4.ALGO_AUTO)
+        assert (got == want).all(), (m, k, n)
+        for p in (a, b, bt):
+            L.mzd_free(p)
+    # window operand: 4000 x 16384 window at column 128 of a 4100 x 20000 parent
+    P = orc.random(4100, 20000, 31)
+    p = host(m4, P, 20000)
+    w = L.mzd_init_window(p, 50, 128, 4050, 128 + 16384)
+    A = np.ascontiguousarray(P[50:4050, 2:2 + 256])
+    B = orc.random(16384, 3000, 32)
+    b = host(m4, B, 3000)
+    want = orc.mul_m4rm(A, B, 16384, 3000, threads=0)[:, : orc.width(3000)]
+    assert (result_words(m4, L.mzd_mul(None, w, b, 0)) == want).all()
+    for q in (w, p, b):
+        L.mzd_free(q)
