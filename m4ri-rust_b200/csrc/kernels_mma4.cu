@@ -179,6 +179,12 @@ mma4_kernel(uint32_t *__restrict__ C, const __grid_constant__ CUtensorMap tmA,
             for (int c = 0; c < 8; c++)
 #pragma unroll
               for (int j = 0; j < 4; j++) v[4 * c + j] = (x[8 * h + c] >> j) & NIB;
+            if (dbg & 8) {  // perf experiment: expansion ALU work without the tensor-memory store
+              uint32_t acc = 0;
+#pragma unroll
+              for (int j = 0; j < 32; j++) acc ^= v[j];
+              if (acc == 0x12345678u) asm volatile("nanosleep.u32 1;");
+            } else
             tmem_st32(a_lane + s * 64 + h * 32, v);
           }
           tmem_wait_st();
@@ -190,6 +196,10 @@ mma4_kernel(uint32_t *__restrict__ C, const __grid_constant__ CUtensorMap tmA,
 #pragma unroll
             for (int c = 0; c < 8; c++) {
               const uint32_t w = x[8 * h + c];
+              if (dbg & 16) {
+                if ((((w & NIB) ^ ((w >> 1) & NIB)) ^ (((w >> 2) & NIB) ^ ((w >> 3) & NIB))) == 0x12345678u)
+                  asm volatile("nanosleep.u32 1;");
+              } else
               sts128(dst + h * B_TILE + (((uint32_t)c ^ sw) << 4), w & NIB, (w >> 1) & NIB,
                      (w >> 2) & NIB, (w >> 3) & NIB);
             }
@@ -263,6 +273,10 @@ mma4_kernel(uint32_t *__restrict__ C, const __grid_constant__ CUtensorMap tmA,
       mbar_wait_long(accum_bar, tile_it & 1);
       tc_fence_after();
       uint32_t out[NCOL / 32];
+      if (dbg & 4) {  // perf experiment: no drain
+#pragma unroll
+        for (int c = 0; c < NCOL / 32; c++) out[c] = 0;
+      } else
 #pragma unroll
       for (int c = 0; c < NCOL / 32; c++) {
         uint32_t v[32];
