@@ -114,14 +114,16 @@ int m4ri_b200_get_algo(void);
  * -1 = automatic from `cutoff`/shape, 0 = none. */
 void m4ri_b200_set_strassen_levels(int levels);
 /* Kernel variant behind M4RI_B200_ALGO_MMA (0 restores the default; also
- * settable with M4RI_B200_MMA=v1|v2cg1|v2|fp4cg1|fp4): benchmarking knob. */
+ * settable with M4RI_B200_MMA=v1|v2cg1|v2|fp4cg1|fp4|fp4tma): benchmarking knob. */
 enum m4ri_b200_mma_variant {
   M4RI_B200_MMA_DEFAULT = 0,
   M4RI_B200_MMA_V1 = 1,        /* one CTA per 128x128 tile, operands expanded into shared memory */
   M4RI_B200_MMA_V2_SINGLE = 2, /* TMA-staged bits, A in tensor memory, cta_group::1              */
   M4RI_B200_MMA_V2_PAIR = 3,   /* the same on CTA pairs (cta_group::2), 256x256 tiles            */
   M4RI_B200_MMA_FP4_SINGLE = 4,/* bits -> E2M1 nibbles, kind::mxf4 (2x the int8 rate), cta_group::1 */
-  M4RI_B200_MMA_FP4_PAIR = 5   /* the same on CTA pairs, 256x256 tiles                           */
+  M4RI_B200_MMA_FP4_PAIR = 5,  /* the same on CTA pairs, 256x256 tiles                           */
+  M4RI_B200_MMA_FP4_LDG_SINGLE = 6, /* FP4, packed bits by direct 256-bit global loads (no TMA)  */
+  M4RI_B200_MMA_FP4_LDG_PAIR = 7    /* the same on CTA pairs (default)                           */
 };
 void m4ri_b200_set_mma_variant(int variant);
 

@@ -24,7 +24,7 @@ HEADER_PATH = os.path.join(_HERE, "..", "include", "m4ri_b200.h")
 
 ALGO_AUTO, ALGO_M4RM, ALGO_MMA, ALGO_SIMPLE = 0, 1, 2, 3
 ALGO_NAMES = {"auto": 0, "m4rm": 1, "mma": 2, "simple": 3}
-MMA_VARIANTS = {"default": 0, "v1": 1, "v2cg1": 2, "v2": 3, "fp4cg1": 4, "fp4": 5}
+MMA_VARIANTS = {"default": 0, "v1": 1, "v2cg1": 2, "v2": 3, "fp4cg1": 4, "fp4": 5, "fp4ldgcg1": 6, "fp4ldg": 7}
 
 
 class MzdBlock(ctypes.Structure):

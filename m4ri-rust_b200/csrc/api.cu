@@ -136,13 +136,18 @@ void k_mul_abt_mma(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream
   int v = g_mma_variant.load();
   if (v == 0) {
     const char *e = getenv("M4RI_B200_MMA");
-    v = !e ? M4RI_B200_MMA_FP4_PAIR
+    v = !e ? M4RI_B200_MMA_FP4_LDG_PAIR
         : !strcmp(e, "v1") ? M4RI_B200_MMA_V1
         : !strcmp(e, "v2cg1") ? M4RI_B200_MMA_V2_SINGLE
         : !strcmp(e, "fp4cg1") ? M4RI_B200_MMA_FP4_SINGLE
-        : !strcmp(e, "v2") ? M4RI_B200_MMA_V2_PAIR : M4RI_B200_MMA_FP4_PAIR;
+        : !strcmp(e, "v2") ? M4RI_B200_MMA_V2_PAIR
+        : !strcmp(e, "fp4ldg") ? M4RI_B200_MMA_FP4_LDG_PAIR
+        : !strcmp(e, "fp4ldgcg1") ? M4RI_B200_MMA_FP4_LDG_SINGLE
+        : !strcmp(e, "fp4") ? M4RI_B200_MMA_FP4_PAIR : M4RI_B200_MMA_FP4_LDG_PAIR;
   }
   if (v == M4RI_B200_MMA_V1) k_mul_abt_mma1(C, A, Bt, clear, s);
+  else if (v == M4RI_B200_MMA_FP4_LDG_SINGLE || v == M4RI_B200_MMA_FP4_LDG_PAIR)
+    k_mul_abt_mma5(C, A, Bt, clear, v == M4RI_B200_MMA_FP4_LDG_SINGLE ? 1 : 2, s);
   else if (v == M4RI_B200_MMA_FP4_SINGLE || v == M4RI_B200_MMA_FP4_PAIR)
     k_mul_abt_mma4(C, A, Bt, clear, v == M4RI_B200_MMA_FP4_SINGLE ? 1 : 2, nullptr, s);
   else k_mul_abt_mma2(C, A, Bt, clear, v == M4RI_B200_MMA_V2_SINGLE ? 1 : 2, s);
@@ -584,7 +589,7 @@ int m4ri_b200_get_algo(void) {
 }
 void m4ri_b200_set_strassen_levels(int levels) { g_strassen.store(levels); }
 void m4ri_b200_set_mma_variant(int variant) {
-  if (variant < 0 || variant > 5) die("m4ri_b200: unknown MMA variant %d\n", variant);
+  if (variant < 0 || variant > 7) die("m4ri_b200: unknown MMA variant %d\n", variant);
   g_mma_variant.store(variant);
 }
 

@@ -100,6 +100,8 @@ void k_mul_abt_mma2(DMat *C, const DMat *A, const DMat *Bt, int clear, int cg, c
 // ---- kernels_mma4.cu: bits -> E2M1 nibbles, tcgen05 kind::mxf4 with unit scale factors
 void k_mul_abt_mma4(DMat *C, const DMat *A, const DMat *Bt, int clear, int cg, float *raw_acc,
                     cudaStream_t s);
+// ---- kernels_mma5.cu: the same contraction, packed bits by direct global loads
+void k_mul_abt_mma5(DMat *C, const DMat *A, const DMat *Bt, int clear, int cg, cudaStream_t s);
 bool mma_shape_ok(const DMat *C, const DMat *A, const DMat *Bt);
 bool mma_available();
 
