@@ -111,6 +111,21 @@ __device__ __forceinline__ void load_kstep(uint32_t (&x)[16], const uint8_t *p, 
   }
 }
 
+// bit j of the result = parity of 4 * v[j] (v[j] = popcount / 4 exactly, < 2^21): the mantissa
+// LSB of v[j] + 2^21. Four independent shift-or chains of eight instead of one of 32.
+__device__ __forceinline__ uint32_t pack_parity(const uint32_t (&v)[32]) {
+  uint32_t w[4];
+#pragma unroll
+  for (int g = 0; g < 4; g++) {
+    uint32_t acc = 0;
+#pragma unroll
+    for (int j = 7; j >= 0; j--)
+      acc = (acc << 1) | (__float_as_uint(__uint_as_float(v[8 * g + j]) + 2097152.0f) & 1u);
+    w[g] = acc;
+  }
+  return w[0] | (w[1] << 8) | (w[2] << 16) | (w[3] << 24);
+}
+
 template <int CG, bool WIDE>
 __global__ void __launch_bounds__(NTHREADS, 1)
 mma5_kernel(uint32_t *__restrict__ C, const uint8_t *__restrict__ Ab, const uint8_t *__restrict__ Bb,
@@ -278,16 +293,20 @@ mma5_kernel(uint32_t *__restrict__ C, const uint8_t *__restrict__ Ab, const uint
       if (dbg & 4) {  // perf experiment: no drain
 #pragma unroll
         for (int c = 0; c < NCOL / 32; c++) out[c] = 0;
-      } else
+      } else {
+        // two chunks of 32 columns in flight: the load of chunk c+1 overlaps the packing of chunk c
+        const uint32_t d_lane = tmem_base + ((uint32_t)(qd * 32) << 16);
+        uint32_t va[32], vb[32];
+        tmem_ld32_nowait(d_lane, va);
 #pragma unroll
-      for (int c = 0; c < NCOL / 32; c++) {
-        uint32_t v[32];
-        tmem_ld32(tmem_base + ((uint32_t)(qd * 32) << 16) + c * 32, v);
-        uint32_t word = 0;
-#pragma unroll
-        for (int j = 0; j < 32; j++)
-          word |= (__float_as_uint(__uint_as_float(v[j]) + 2097152.0f) & 1u) << j;
-        out[c] = word;
+        for (int c = 0; c < NCOL / 32; c += 2) {
+          tmem_wait_ld();
+          tmem_ld32_nowait(d_lane + (c + 1) * 32, vb);
+          out[c] = pack_parity(va);
+          tmem_wait_ld();
+          if (c + 2 < NCOL / 32) tmem_ld32_nowait(d_lane + (c + 2) * 32, va);
+          out[c + 1] = pack_parity(vb);
+        }
       }
       tc_fence_before();
       __syncwarp();
