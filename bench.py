@@ -282,7 +282,7 @@ def main():
         # strictest denominator); the fraction of 2 x the driver-measured cuBLAS bf16 burst
         # (power-capped at ~1.3 GHz) is reported beside it.
         sm_max = (clocks.get("sm_max_mhz") or 1965) * 1e6
-        fp4 = "mma4" in kern_name  # kind::mxf4: 64 elements per row per MMA, twice kind::i8
+        fp4 = "mma4" in kern_name or "mma5" in kern_name  # kind::mxf4: 64 elements per row per MMA, twice kind::i8
         per_clk = 32768.0 if fp4 else 16384.0
         peak = per_clk * 148 * sm_max / 1e12
         meas = (4.0 if fp4 else 2.0) * pk["bf16_tflops"]

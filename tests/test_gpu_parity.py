@@ -338,3 +338,70 @@ def test_pipelined_host_products(gpu, m4, orc):
     assert (result_words(m4, L.mzd_mul(None, w, b, 0)) == want).all()
     for q in (w, p, b):
         L.mzd_free(q)
+
+
+VARIANT_SWEEP = [(1, 1, 1), (2, 63, 65), (65, 64, 64), (191, 193, 129), (200, 257, 321), (5, 700, 1100),
+                 (1030, 40, 1030), (257, 2050, 1500), (256, 4096, 128), (300, 512, 300), (129, 1536, 257)]
+
+
+@pytest.mark.parametrize("variant", ["v1", "v2cg1", "v2", "fp4cg1", "fp4", "fp4ldgcg1", "fp4ldg"])
+def test_every_tensor_kernel_variant(gpu, m4, orc, variant):
+    """Each kernel behind ALGO_MMA (int8 SS, int8 TS single/pair, FP4 with TMA staging
+    single/pair, FP4 with direct global loads single/pair) is bit-exact on ragged shapes,
+    accumulates, handles contractions longer than one 65536-bit chunk and Strassen windows."""
+    L = m4.lib()
+    L.m4ri_b200_set_mma_variant(m4.MMA_VARIANTS[variant])
+    try:
+        for (m, k, n) in VARIANT_SWEEP + [(70, 70000, 90)]:
+            A, B = orc.random(m, k, 3 + m), orc.random(k, n, 4 + n)
+            want = orc.mul_m4rm(A, B, k, n, threads=0)[:, : orc.width(n)]
+            a, b = host(m4, A, k), host(m4, B, n)
+            dA, dB, dC = m4.DMat.from_host(a), m4.DMat.from_host(b), m4.DMat.init(m, n)
+            m4.dmul(dC, dA, dB, clear=True, algo=m4.ALGO_MMA)
+            got = dC.to_words()
+            assert not got[:, orc.width(n):].any()
+            assert (got[:, : orc.width(n)] == want).all(), f"{variant} differs at {m}x{k}x{n}"
+            m4.dmul(dC, dA, dB, clear=False, algo=m4.ALGO_MMA)
+            assert not dC.to_words().any(), f"{variant} addmul differs at {m}x{k}x{n}"
+            L.mzd_free(a)
+            L.mzd_free(b)
+        # one Strassen level on (pointer, stride) windows: operands whose rows continue past the window
+        L.m4ri_b200_set_strassen_levels(1)
+        m = k = n = 1024
+        A, B = orc.random(m, k, 8), orc.random(k, n, 9)
+        want = orc.mul_m4rm(A, B, k, n, threads=0)[:, : orc.width(n)]
+        a, b = host(m4, A, k), host(m4, B, n)
+        dA, dB, dC = m4.DMat.from_host(a), m4.DMat.from_host(b), m4.DMat.init(m, n)
+        m4.dmul(dC, dA, dB, clear=True, algo=m4.ALGO_MMA)
+        assert (dC.to_words()[:, : orc.width(n)] == want).all(), f"{variant} with one Strassen level"
+        L.mzd_free(a)
+        L.mzd_free(b)
+    finally:
+        L.m4ri_b200_set_strassen_levels(-1)
+        L.m4ri_b200_set_mma_variant(0)
+
+
+def test_fp4_accumulators_are_exact(gpu, m4, orc):
+    """The FP4 path's fp32 accumulators equal popcount(A_i & Bt_j)/4 exactly, also in the worst
+    case the wrapper allows (all ones, k = 65536): no rounding anywhere in the tensor core."""
+    import torch
+    L = m4.lib()
+    for cg in (1, 2):
+        for (m, k, n, ones) in [(200, 1000, 300, False), (256, 65536, 256, True), (128, 20000, 130, False)]:
+            if ones:
+                A = np.full((m, orc.width(k)), np.uint64(0xFFFFFFFFFFFFFFFF))
+                B = np.full((n, orc.width(k)), np.uint64(0xFFFFFFFFFFFFFFFF))
+            else:
+                A, B = orc.random(m, k, 5 + m)[:, : orc.width(k)].copy(), orc.random(n, k, 7 + n)[:, : orc.width(k)].copy()
+            a, b = host(m4, A, k), host(m4, B, k)
+            dA, dB, dC = m4.DMat.from_host(a), m4.DMat.from_host(b), m4.DMat.init(m, n)
+            acc = torch.full((m, n), -1.0, dtype=torch.float32, device="cuda")
+            torch.cuda.synchronize()
+            L.m4ri_b200_dmul_abt_fp4_debug(dC.h, dA.h, dB.h, acc.data_ptr(), cg)
+            L.m4ri_b200_synchronize()
+            a8 = np.unpackbits(m4.mzd_words(a)[:, : orc.width(k)].copy().view(np.uint8), axis=1, bitorder="little").astype(np.float32)
+            b8 = np.unpackbits(m4.mzd_words(b)[:, : orc.width(k)].copy().view(np.uint8), axis=1, bitorder="little").astype(np.float32)
+            want = (a8 @ b8.T) / 4.0
+            assert (acc.cpu().numpy() == want).all(), (cg, m, k, n)
+            L.mzd_free(a)
+            L.mzd_free(b)
