@@ -117,6 +117,73 @@ def cpu_arm(n, m_total, steps, warmup, target_s=12.0):
             "ms_per_step": t * 1e3, "rows": rows}
 
 
+def run_lpn(args):
+    """BASELINE configs[4] (extra bench line, not the headline): the LPN covering-code shapes.
+    (a) tall product 2^20 x 512 times 512 x 512 — compute bound, every algorithm;
+    (b) mat-vec y = A*x on the resident 2^20 x 512 A, packed words in and out — HBM bound:
+        algorithmic bytes = 8*(m*width + width) + ceil(m/64)*8 per product."""
+    import torch
+    import m4ri_rust_b200 as m4
+    L = m4.lib()
+    stream = torch.cuda.current_stream()
+    L.m4ri_b200_set_stream(ctypes.c_void_p(stream.cuda_stream))
+    m, k, n = 1 << 20, 512, 512
+    dA = m4.DMat.init(m, k).fill_random(21)
+    dB = m4.DMat.init(k, n).fill_random(22)
+    dC = m4.DMat.init(m, n)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(steps):
+            flush.fill_(1)  # operands (64 MiB + 64 MiB) fit the 126 MB L2: flush between steps
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            fn()
+            b.record(stream)
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b))
+        return sum(ts) / len(ts)
+
+    out = {"metric": "GF(2) LPN covering-code workload", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+           "data": "synthetic", "dtype": "u64", "higher_is_better": True,
+           "config": {"workload": "tall 2^20x512 * 512x512 + mat-vec on the resident A", "m": m, "k": k, "n": n,
+                      "l2": "L2 flushed between steps by writing a 256 MiB buffer"}}
+    prod = {}
+    for name in ("auto", "mma", "m4rm"):
+        ms = timed(lambda: m4.dmul(dC, dA, dB, clear=True, algo=m4.ALGO_NAMES[name]), args.steps, args.warmup)
+        ok = L.m4ri_b200_dfreivalds(dC.h, dA.h, dB.h, 0xF5E1)
+        prod[name] = {"ms": ms, "tbitops": 2.0 * m * k * n / ms / 1e9, "freivalds": bool(ok),
+                      "gbs_compulsory": (2 * m * 64 + k * 64) / ms / 1e6}
+    out["product"] = prod
+    out["value"], out["unit"], out["ms_per_step"] = prod["auto"]["tbitops"], "Tbit-op/s", prod["auto"]["ms"]
+    # mat-vec
+    dx = m4.DMat.init(1, k).fill_random(23)
+    dy = m4.DMat.init(1, m)
+    ms = timed(lambda: L.m4ri_b200_dmul_v(dy.h, dA.h, dx.h, 1), args.steps, args.warmup)
+    bytes_alg = 8 * (m * (k // 64) + k // 64) + (m // 64) * 8
+    pk = peaks()
+    out["matvec"] = {"ms": ms, "tbitops": 2.0 * m * k / ms / 1e9,
+                     "roofline": {"bound": "hbm", "achieved": bytes_alg / ms / 1e6, "peak": pk["hbm_gbs"],
+                                  "unit": "GB/s", "frac": bytes_alg / ms / 1e6 / pk["hbm_gbs"], "traffic": None,
+                                  "kernel": "mul_v_rows_kernel<4>", "algorithmic_bytes": bytes_alg}}
+    # the same kernel on a 4x taller A (256 MiB > L2): launch latency amortised, no flush needed
+    m2 = 1 << 22
+    dA2 = m4.DMat.init(m2, k).fill_random(31)
+    dy2 = m4.DMat.init(1, m2)
+    ms2 = timed(lambda: L.m4ri_b200_dmul_v(dy2.h, dA2.h, dx.h, 1), args.steps, args.warmup)
+    b2 = 8 * (m2 * (k // 64) + k // 64) + (m2 // 64) * 8
+    out["matvec_2^22_rows"] = {"ms": ms2, "tbitops": 2.0 * m2 * k / ms2 / 1e9,
+                               "roofline": {"bound": "hbm", "achieved": b2 / ms2 / 1e6, "peak": pk["hbm_gbs"],
+                                            "unit": "GB/s", "frac": b2 / ms2 / 1e6 / pk["hbm_gbs"],
+                                            "traffic": None, "kernel": "mul_v_rows_kernel<4>",
+                                            "algorithmic_bytes": b2}}
+    print(json.dumps(out))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -126,6 +193,7 @@ def main():
     ap.add_argument("--n", type=int, default=0)
     ap.add_argument("--algo", default="auto", choices=["auto", "m4rm", "mma", "simple"])
     ap.add_argument("--chunks", type=int, default=2, help="k-chunks of the broadcast of B (N > 1)")
+    ap.add_argument("--workload", default="square", choices=["square", "lpn"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
@@ -140,6 +208,10 @@ def main():
               "l2": "operands (3 x n*n/8 bytes) exceed the 126 MB L2; no explicit flush" if n >= 32768
               else "L2 flushed between steps by writing a 256 MiB buffer"}
 
+    if args.workload == "lpn" and args.impl != "reference":
+        if rank == 0:
+            run_lpn(args)
+        return
     if args.impl == "reference":
         if rank != 0:
             return

@@ -263,13 +263,62 @@ mul_v_kernel(uint32_t *__restrict__ y, const ulonglong2 *__restrict__ A,
   }
 }
 
+// Short rows (width <= 16 words, the LPN shapes): one thread per row reads its whole row with
+// 16-byte loads, a warp's 32 parities are one ballot = one aligned 32-bit word of y: no
+// atomics, no memset of y, one launch.
+template <int WV /*16-byte vectors per row*/>
+__global__ void __launch_bounds__(256)
+mul_v_rows_kernel(uint32_t *__restrict__ y, const ulonglong2 *__restrict__ A,
+                  const ulonglong2 *__restrict__ x, int m, int as, int clear) {
+  const long long row = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  ulonglong2 a[WV];
+  uint64_t acc = 0;
+  if (row < m) {
+    const ulonglong2 *arow = A + (size_t)row * as;
+#pragma unroll
+    for (int w = 0; w < WV; w++)
+      asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0,%1}, [%2];" : "=l"(a[w].x), "=l"(a[w].y) : "l"(arow + w));
+#pragma unroll
+    for (int w = 0; w < WV; w++) {
+      const ulonglong2 b = __ldg(&x[w]);
+      acc ^= (a[w].x & b.x) ^ (a[w].y & b.y);
+    }
+  }
+  const unsigned bits = __ballot_sync(0xffffffffu, (row < m) && (__popcll(acc) & 1));
+  if ((threadIdx.x & 31) == 0 && row < (((long long)m + 63) & ~63LL)) {  // whole 64-bit words of y
+    uint32_t *dst = y + (row >> 5);
+    *dst = clear ? bits : (*dst ^ bits);
+  }
+}
+
 void k_mul_v(DMat *y, const DMat *A, const DMat *x, int clear, cudaStream_t s) {
-  if (clear) k_zero(y, s);
-  if (A->nrows == 0 || A->ncols == 0) return;
+  if (A->nrows == 0 || A->ncols == 0) {
+    if (clear) k_zero(y, s);
+    return;
+  }
   if (A->rowstride % 2 || ((uintptr_t)A->d % 16) || ((uintptr_t)x->d % 16))
     die("m4ri_b200: mul_v needs 16-byte aligned rows\n");
   // x is read in 16-byte vectors up to ceil(width/2): its row is padded to an even stride.
   int wv = (A->width + 1) / 2, as = A->rowstride / 2;
+  if (wv <= 8) {  // thread per row; the last 64-bit word of y (rows past m) is written whole
+    unsigned grid = cdiv(((long long)A->nrows + 63) / 64 * 64, 256);
+    uint32_t *yy = (uint32_t *)y->d;
+    const ulonglong2 *AA = (const ulonglong2 *)A->d, *xx = (const ulonglong2 *)x->d;
+    const int mm = A->nrows;
+    switch (wv) {
+      case 1: mul_v_rows_kernel<1><<<grid, 256, 0, s>>>(yy, AA, xx, mm, as, clear); break;
+      case 2: mul_v_rows_kernel<2><<<grid, 256, 0, s>>>(yy, AA, xx, mm, as, clear); break;
+      case 3: mul_v_rows_kernel<3><<<grid, 256, 0, s>>>(yy, AA, xx, mm, as, clear); break;
+      case 4: mul_v_rows_kernel<4><<<grid, 256, 0, s>>>(yy, AA, xx, mm, as, clear); break;
+      case 5: mul_v_rows_kernel<5><<<grid, 256, 0, s>>>(yy, AA, xx, mm, as, clear); break;
+      case 6: mul_v_rows_kernel<6><<<grid, 256, 0, s>>>(yy, AA, xx, mm, as, clear); break;
+      case 7: mul_v_rows_kernel<7><<<grid, 256, 0, s>>>(yy, AA, xx, mm, as, clear); break;
+      default: mul_v_rows_kernel<8><<<grid, 256, 0, s>>>(yy, AA, xx, mm, as, clear); break;
+    }
+    M4B_LAUNCHED();
+    return;
+  }
+  if (clear) k_zero(y, s);
   int G = wv >= 32 ? 32 : wv >= 16 ? 16 : wv >= 8 ? 8 : wv >= 4 ? 4 : wv >= 2 ? 2 : 1;
   long long warps = cdiv(A->nrows, 32 / G);
   unsigned grid = cdiv(warps * 32, 256);

@@ -199,7 +199,8 @@ def test_transpose_add_device_and_host(gpu, m4, orc):
 
 def test_matvec_shapes(gpu, m4, orc):
     L = m4.lib()
-    for (m, n) in [(34, 128), (10, 10), (64, 1000), (1000, 64), (1, 1), (4097, 777), (300, 8192)]:
+    for (m, n) in [(34, 128), (10, 10), (64, 1000), (1000, 64), (1, 1), (4097, 777), (300, 8192),
+                   (20, 512), (33, 64), (100, 129), (70000, 512), (65, 1024), (4096, 960)]:
         A = orc.random(m, n, 3)
         x = orc.random(1, n, 4)
         a = host(m4, A, n)
@@ -217,6 +218,8 @@ def test_matvec_shapes(gpu, m4, orc):
         dy = m4.DMat.init(1, m)
         L.m4ri_b200_dmul_v(dy.h, dA.h, dx.h, 1)
         assert (dy.to_words()[0, : orc.width(m)] == want).all()
+        L.m4ri_b200_dmul_v(dy.h, dA.h, dx.h, 0)  # accumulate: y ^= A*x restores zero
+        assert not dy.to_words().any()
         L.mzd_free(hx)
 
 
