@@ -377,6 +377,17 @@ def main():
         roof = {"bound": "smem", "achieved": achieved, "peak": peak, "unit": "Tbit-op/s",
                 "frac": achieved / peak if achieved else None, "traffic": None,
                 "peak_source": "measured shared-memory load bandwidth x 512 bit-ops per 32-bit table word (t=8)"}
+    # DRAM traffic of one launch of that kernel at the leaf shape, from the committed ncu capture
+    try:
+        leaf = round((kern_ops / kern_count / 2.0) ** (1.0 / 3.0))
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        ent = tj.get(f"{kern_name}@{leaf}x{leaf}x{leaf}") if world == 1 else None
+        if ent:
+            roof["traffic"] = ent["bytes"]
+            roof["traffic_source"] = ent["source"]
+            roof["algorithmic_bytes"] = 3 * leaf * leaf // 8
+    except Exception:
+        pass
     roof["kernel"] = kern_name
     roof["kernel_ms"] = kern_ms
     roof["kernel_launches_per_step"] = timing_count / max(1, args.steps)
