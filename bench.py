@@ -192,18 +192,27 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--n", type=int, default=0)
     ap.add_argument("--algo", default="auto", choices=["auto", "m4rm", "mma", "simple"])
-    ap.add_argument("--chunks", type=int, default=2, help="k-chunks of the broadcast of B (N > 1)")
+    ap.add_argument("--chunks", default="auto", help="k-chunks of the broadcast of B (N > 1): a count, 'ramp' = 1/8, 3/8, 1/2 of k, or 'auto'")
+    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
+                    help="N > 1: 'fused' = transpose kernel that reads the root's B and stores Bt to every rank over NVLink; "
+                         "'nccl' = NCCL broadcast of B in k-chunks overlapped with the product")
+    ap.add_argument("--reserve", type=int, default=8, help="SMs left to NCCL while a broadcast chunk is in flight (N > 1)")
     ap.add_argument("--workload", default="square", choices=["square", "lpn"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
+    if args.chunks not in ("ramp", "ramp4", "auto"):
+        args.chunks = int(args.chunks)
+    os.environ.setdefault("NCCL_MAX_NCHANNELS", str(max(1, args.reserve)))  # the broadcast runs on the 8 SMs the product leaves free
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     n = args.n or (32768 if world == 1 else 65536)
     workload = f"square mzd_mul n={n} random" + (
-        "" if world == 1 else f", C/A row-blocks sharded over {world} ranks, NCCL broadcast of B per step "
-        f"in {args.chunks} k-chunks overlapped with the product")
+        "" if world == 1 else f", C/A row-blocks sharded over {world} ranks, B of rank 0 distributed every step: "
+        + ("exchange fused into the transpose (each rank transposes one k-slab of the root's B, read over NVLink, and stores it into every rank's Bt with peer stores)"
+           if args.exchange == "fused" else
+           f"NCCL broadcast in k-chunks ({args.chunks}) overlapped with the product; the product leaves {args.reserve} SMs to NCCL while a chunk is in flight"))
     config = {"workload": workload, "m": n, "k": n, "n": n, "algo": args.algo,
               "l2": "operands (3 x n*n/8 bytes) exceed the 126 MB L2; no explicit flush" if n >= 32768
               else "L2 flushed between steps by writing a 256 MiB buffer"}
@@ -247,12 +256,19 @@ def main():
     from m4ri_rust_b200 import sharded
     r0, rows = sharded.row_block(n, world, rank)
     ws = n // 64  # words per row (n % 128 == 0 so device stride == width)
-    tA = torch.empty((rows, ws), dtype=torch.int64, device="cuda")
-    tB = torch.empty((n, ws), dtype=torch.int64, device="cuda")
-    tC = torch.empty((rows, ws), dtype=torch.int64, device="cuda")
-    dA = m4.DMat.wrap(tA.data_ptr(), rows, n, ws, keepalive=tA)
-    dB = m4.DMat.wrap(tB.data_ptr(), n, n, ws, keepalive=tB)
-    dC = m4.DMat.wrap(tC.data_ptr(), rows, n, ws, keepalive=tC)
+    fused = world > 1 and args.exchange == "fused"
+    if fused:
+        # exchange fused into the transpose: each rank transposes one k-slab of the root's B over
+        # NVLink and stores it into every rank's Bt (peer stores); one product launch per step
+        fm = sharded.FusedBroadcastMul(m4, n, n, n, dist, src=0)
+        tA, tB, tC, dA, dB, dC = fm.tA, fm.tB, fm.tC, fm.dA, fm.dB, fm.dC
+    else:
+        tA = torch.empty((rows, ws), dtype=torch.int64, device="cuda")
+        tB = torch.empty((n, ws), dtype=torch.int64, device="cuda")
+        tC = torch.empty((rows, ws), dtype=torch.int64, device="cuda")
+        dA = m4.DMat.wrap(tA.data_ptr(), rows, n, ws, keepalive=tA)
+        dB = m4.DMat.wrap(tB.data_ptr(), n, n, ws, keepalive=tB)
+        dC = m4.DMat.wrap(tC.data_ptr(), rows, n, ws, keepalive=tC)
     # word (r,w) of A = splitmix64 stream index r*width+w: generate the full-matrix
     # stream positions of this rank's rows
     L.m4ri_b200_dfill_random_at(dA.h, SEED_A, r0 * ws)
@@ -261,11 +277,16 @@ def main():
     else:
         tB.zero_()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda") if n < 32768 else None
-    # one step = NCCL broadcast of B from rank 0 in k-chunks (N > 1), each chunk's product
-    # overlapped with the next chunk's transfer (m4ri-rust_b200/sharded.py)
-    sm = sharded.ShardedMul(n, n, n, dist=dist, src=0, chunks=args.chunks, tB=tB,
-                            chunk_product=sharded.gpu_chunk_product(m4, tA, tB, tC, rows, n, n, algo))
-    step = sm.step
+    if fused:
+        step = lambda: fm.step(algo)
+    else:
+        # one step = NCCL broadcast of B from rank 0 in k-chunks (N > 1), each chunk's product
+        # overlapped with the next chunk's transfer (m4ri-rust_b200/sharded.py)
+        nsm = m4.device_info()["sms"]
+        sm = sharded.ShardedMul(n, n, n, dist=dist, src=0, chunks=args.chunks, tB=tB,
+                                reserve_sms=(lambda r: L.m4ri_b200_set_sm_limit(nsm - args.reserve if r else 0)) if world > 1 and args.reserve > 0 else None,
+                                chunk_product=sharded.gpu_chunk_product(m4, tA, tB, tC, rows, n, n, algo))
+        step = sm.step
 
     def barrier():
         torch.cuda.synchronize()
@@ -301,6 +322,9 @@ def main():
     kern_ms = kern_total_ms / max(1, timing_count)
     kern_name = L.m4ri_b200_timing_name().decode()
 
+    if fused:
+        dist.broadcast(tB, src=0)  # only Bt travelled inside the steps; the check below needs B itself
+        torch.cuda.synchronize()
     # parity inside the run: Freivalds on this rank's block (false accept 2^-64)
     ok = L.m4ri_b200_dfreivalds(dC.h, dA.h, dB.h, 0xF5E1)
     if ok != 1:

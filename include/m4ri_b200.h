@@ -113,6 +113,10 @@ int m4ri_b200_get_algo(void);
 /* Strassen-Winograd levels applied above the leaf kernel on device products:
  * -1 = automatic from `cutoff`/shape, 0 = none. */
 void m4ri_b200_set_strassen_levels(int levels);
+/* The persistent product kernels normally take every SM. A collective that should overlap a
+ * product (the NCCL broadcast of the next k-chunk of B, sharded.py) needs a few SMs of its own:
+ * sms > 0 caps the SMs the product kernels launched after this call use (0 = all). */
+void m4ri_b200_set_sm_limit(int sms);
 /* Kernel variant behind M4RI_B200_ALGO_MMA (0 restores the default; also
  * settable with M4RI_B200_MMA=v1|v2cg1|v2|fp4cg1|fp4|fp4tma): benchmarking knob. */
 enum m4ri_b200_mma_variant {
@@ -167,6 +171,9 @@ void m4ri_b200_dmul_v(m4ri_b200_dmat_t *y, const m4ri_b200_dmat_t *A, const m4ri
 void m4ri_b200_dmul_va(m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *v, const m4ri_b200_dmat_t *A,
                        int clear);
 void m4ri_b200_dtranspose(m4ri_b200_dmat_t *DST, const m4ri_b200_dmat_t *A);
+/* A^T written to ndst (1..8) destinations at once; A and the destinations may be peer-GPU
+ * memory mapped into this process (fused broadcast + transpose of the sharded product). */
+void m4ri_b200_dtranspose_scatter(m4ri_b200_dmat_t *const *DST, int ndst, const m4ri_b200_dmat_t *A);
 void m4ri_b200_dadd(m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *A, const m4ri_b200_dmat_t *B);
 void m4ri_b200_dcopy(m4ri_b200_dmat_t *DST, const m4ri_b200_dmat_t *A);
 /* Fill with splitmix64(seed) words, row by row, excess bits masked: the same

@@ -111,9 +111,11 @@ void require_device() {
         g_name, g_cc_major, g_cc_minor);
 }
 
+static std::atomic<int> g_sm_limit{0};
 int sm_count() {
   require_device();
-  return g_sms;
+  const int lim = g_sm_limit.load();
+  return (lim > 0 && lim < g_sms) ? lim : g_sms;
 }
 bool has_tcgen05() {
   require_device();
@@ -588,6 +590,7 @@ int m4ri_b200_get_algo(void) {
   return g_algo.load();
 }
 void m4ri_b200_set_strassen_levels(int levels) { g_strassen.store(levels); }
+void m4ri_b200_set_sm_limit(int sms) { g_sm_limit.store(sms < 0 ? 0 : (sms & ~1)); }
 void m4ri_b200_set_mma_variant(int variant) {
   if (variant < 0 || variant > 7) die("m4ri_b200: unknown MMA variant %d\n", variant);
   g_mma_variant.store(variant);
@@ -668,6 +671,9 @@ void m4ri_b200_dtranspose(m4ri_b200_dmat_t *DST, const m4ri_b200_dmat_t *A) {
   if (DST->nrows != A->ncols || DST->ncols != A->nrows)
     die("m4ri_b200: dtranspose: wrong size for return matrix\n");
   k_transpose(DST, A, current_stream());
+}
+void m4ri_b200_dtranspose_scatter(m4ri_b200_dmat_t *const *DST, int ndst, const m4ri_b200_dmat_t *A) {
+  k_transpose_scatter(DST, ndst, A, current_stream());
 }
 void m4ri_b200_dadd(m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *A, const m4ri_b200_dmat_t *B) {
   if (A->nrows != B->nrows || A->ncols != B->ncols || C->nrows != A->nrows || C->ncols != A->ncols)

@@ -74,6 +74,7 @@ void k_mask_excess(DMat *M, cudaStream_t s);
 void k_add(DMat *C, const DMat *A, const DMat *B, cudaStream_t s);
 void k_copy(DMat *D, const DMat *A, cudaStream_t s);
 void k_transpose(DMat *D, const DMat *A, cudaStream_t s);
+void k_transpose_scatter(DMat *const *D, int ndst, const DMat *A, cudaStream_t s);
 void k_fill_random(DMat *M, uint64_t seed, uint64_t first_index, cudaStream_t s);
 uint64_t k_checksum(const DMat *M, cudaStream_t s);
 bool k_is_zero(const DMat *M, cudaStream_t s);

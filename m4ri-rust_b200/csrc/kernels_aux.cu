@@ -122,6 +122,64 @@ transpose_kernel(uint32_t *__restrict__ D, const uint32_t *__restrict__ S, int n
   }
 }
 
+// The same transpose written to up to 8 destinations at once: the fused "broadcast + transpose"
+// of the row-sharded product (sharded.py). The source slab may live in a peer GPU's memory
+// (read once over NVLink) and every destination but one is a peer's Bt buffer (P2P stores):
+// one pass over the data instead of an NCCL broadcast followed by a local transpose.
+struct TransposeDsts {
+  uint32_t *p[8];
+  int n;
+};
+__global__ void __launch_bounds__(256)
+transpose_scatter_kernel(TransposeDsts dsts, const uint32_t *__restrict__ S, int nrows, int ncols,
+                         int sw32, int ss32, int ds32, int dw32) {
+  __shared__ uint32_t buf[256 * 33];
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  const int r0 = blockIdx.y * 256, cw0 = blockIdx.x * 32;
+#pragma unroll 8
+  for (int i = 0; i < 32; i++) {
+    const int row = i * 8 + w;
+    uint32_t v = 0;
+    if (r0 + row < nrows && cw0 + l < sw32) v = S[(size_t)(r0 + row) * ss32 + cw0 + l];
+    buf[row * 33 + l] = v;
+  }
+  __syncthreads();
+  uint32_t res[32];
+#pragma unroll
+  for (int c = 0; c < 32; c++) res[c] = transpose32(buf[(32 * w + l) * 33 + c], l);
+  __syncthreads();
+#pragma unroll
+  for (int c = 0; c < 32; c++) buf[(c * 32 + l) * 8 + (w ^ ((l >> 2) & 7))] = res[c];
+  __syncthreads();
+#pragma unroll 4
+  for (int i = 0; i < 32; i++) {
+    const int idx = i * 256 + threadIdx.x;
+    const int orl = idx >> 3, g = idx & 7;
+    const int orow = cw0 * 32 + orl, ow = (r0 >> 5) + g;
+    if (orow < ncols && ow < dw32) {
+      const uint32_t v = buf[orl * 8 + (g ^ ((orl >> 2) & 7))];
+      for (int d = 0; d < dsts.n; d++) dsts.p[d][(size_t)orow * ds32 + ow] = v;
+    }
+  }
+}
+
+void k_transpose_scatter(DMat *const *D, int ndst, const DMat *A, cudaStream_t s) {
+  if (ndst < 1 || ndst > 8) die("m4ri_b200: transpose_scatter takes 1 to 8 destinations\n");
+  if (A->nrows == 0 || A->ncols == 0) return;
+  TransposeDsts dsts;
+  dsts.n = ndst;
+  for (int i = 0; i < ndst; i++) {
+    if (D[i]->nrows != A->ncols || D[i]->ncols != A->nrows || D[i]->rowstride != D[0]->rowstride)
+      die("m4ri_b200: transpose_scatter: every destination must be ncols(A) x nrows(A) with one stride\n");
+    dsts.p[i] = (uint32_t *)D[i]->d;
+  }
+  const int sw32 = A->width * 2, dw32 = D[0]->width * 2;
+  dim3 grid(cdiv(sw32, 32), cdiv(dw32, 8));
+  transpose_scatter_kernel<<<grid, 256, 0, s>>>(dsts, (const uint32_t *)A->d, A->nrows, A->ncols, sw32,
+                                                A->rowstride * 2, D[0]->rowstride * 2, dw32);
+  M4B_LAUNCHED();
+}
+
 void k_transpose(DMat *D, const DMat *A, cudaStream_t s) {
   if (A->nrows == 0 || A->ncols == 0) return;
   const int sw32 = A->width * 2, dw32 = D->width * 2;

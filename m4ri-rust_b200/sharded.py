@@ -14,6 +14,8 @@ the partition, the chunk plan and the broadcast plumbing are covered without a G
 """
 import torch
 
+RESERVED_SMS = 8  # SMs left to NCCL while a broadcast overlaps a product (bench: NCCL_MAX_NCHANNELS=8)
+
 
 def row_block(m, world, rank, align=256):
     """Contiguous row-block of rank `rank`: (first row, number of rows). Blocks are
@@ -40,6 +42,17 @@ def k_chunks(k, chunks, align=1024):
     return out or [(0, 0)]
 
 
+def k_chunks_ramp(k, align=1024, parts=3):
+    """Slabs ending at 1/8, 1/2 and all of k (parts = 3; 1/16, 1/4, 1/2, 1 for parts = 4): the first
+    transfer is the only exposed one, so it is the smallest; the later, larger products hide the
+    later, larger transfers."""
+    if k < 16 * align:
+        return k_chunks(k, 1, align)
+    cuts = [k // 8, k // 2] if parts == 3 else [k // 16, k // 4, k // 2]
+    cuts = [c // align * align for c in cuts]
+    return list(zip([0] + cuts, cuts + [k]))
+
+
 class ShardedMul:
     """Holds the plan of one sharded product and runs steps of it.
 
@@ -48,16 +61,32 @@ class ShardedMul:
     chunk_product(i, k0, k1, clear) computes C_block (^)= A_block[:, k0:k1] * B[k0:k1, :]
     on the current stream/device."""
 
-    def __init__(self, m, k, n, dist=None, src=0, chunks=4, chunk_product=None, tB=None):
+    def __init__(self, m, k, n, dist=None, src=0, chunks=4, chunk_product=None, tB=None,
+                 reserve_sms=None):
         self.m, self.k, self.n = m, k, n
         self.dist = dist
         self.src = src
         self.world = dist.get_world_size() if dist is not None else 1
         self.rank = dist.get_rank() if dist is not None else 0
         self.r0, self.rows = row_block(m, self.world, self.rank)
-        self.plan = k_chunks(k, chunks if self.world > 1 else 1)
+        if self.world == 1:
+            self.plan = k_chunks(k, 1)
+        elif chunks == "auto":
+            # a block tall enough for a Strassen level (leaves of 16384) gains more from it than
+            # from hiding the transfer; shorter blocks hide the transfer behind ramped chunks
+            self.plan = k_chunks(k, 1) if self.rows >= 32768 and k >= 32768 and n >= 32768 else k_chunks_ramp(k)
+        elif chunks == "ramp":
+            self.plan = k_chunks_ramp(k)
+        elif chunks == "ramp4":
+            self.plan = k_chunks_ramp(k, parts=4)
+        else:
+            self.plan = k_chunks(k, chunks)
         self.chunk_product = chunk_product
         self.tB = tB
+        # reserve_sms(n): called with n > 0 before a product that must leave n SMs to the
+        # collective still in flight (the persistent product kernels otherwise hold every SM and
+        # NCCL's kernel could only start when they end), and with 0 before the last product
+        self.reserve_sms = reserve_sms
 
     def step(self):
         works = []
@@ -67,6 +96,8 @@ class ShardedMul:
         for i, (k0, k1) in enumerate(self.plan):
             if works:
                 works[i].wait()  # the compute stream waits for chunk i only
+            if self.reserve_sms is not None and works:
+                self.reserve_sms(0 if i == len(self.plan) - 1 else RESERVED_SMS)
             if self.rows > 0:
                 self.chunk_product(i, k0, k1, i == 0)
 
@@ -90,3 +121,57 @@ def gpu_chunk_product(m4, tA, tB, tC, rows, k, n, algo=0):
         m4.dmul(dC, dA, dB, clear=clear, algo=algo)
 
     return product
+
+
+class FusedBroadcastMul:
+    """The same sharded product with the exchange fused into the transpose (GPU only).
+
+    The tensor path consumes B transposed (Bt, n x k, k-contiguous). Instead of "NCCL
+    broadcast of B, then every rank transposes all of it", rank g transposes ONE k-slab of
+    B — read straight from the root's memory over NVLink — and the same kernel stores the
+    slab of Bt into every rank's Bt buffer with peer stores (transpose_scatter_kernel). Root
+    egress is |B| instead of (G-1)|B|, every link carries (G-1)/G |B| in parallel, no SM is
+    held by a collective while the product runs, and the product is one launch over the full
+    k. Buffers are torch symmetric memory (NVLink-mapped into every process of the node);
+    two device-side barriers per step order the peer stores against the products.
+    """
+
+    def __init__(self, m4, m, k, n, dist, src=0):
+        import ctypes
+        import torch.distributed._symmetric_memory as symm_mem
+        self.m4, self.L, self.dist, self.src = m4, m4.lib(), dist, src
+        self.m, self.k, self.n = m, k, n
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        if self.world > 8:
+            raise ValueError("one NVLink domain of at most 8 GPUs")
+        if k % 128 or n % 128:
+            raise ValueError("k and n must be multiples of 128 bits")
+        self.r0, self.rows = row_block(m, self.world, self.rank)
+        self.s0, self.srows = row_block(k, self.world, self.rank)  # this rank's k-slab of B
+        ws, kws = n // 64, k // 64
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self.tB = symm_mem.empty((k, ws), dtype=torch.int64, device=dev)    # valid on src only
+        self.tBt = symm_mem.empty((n, kws), dtype=torch.int64, device=dev)  # filled by all ranks
+        self.hB = symm_mem.rendezvous(self.tB, dist.group.WORLD)
+        self.hBt = symm_mem.rendezvous(self.tBt, dist.group.WORLD)
+        self.tA = torch.empty((self.rows, kws), dtype=torch.int64, device=dev)
+        self.tC = torch.empty((self.rows, ws), dtype=torch.int64, device=dev)
+        D = m4.DMat
+        self.dA = D.wrap(self.tA.data_ptr(), self.rows, k, kws, keepalive=self.tA)
+        self.dC = D.wrap(self.tC.data_ptr(), self.rows, n, ws, keepalive=self.tC)
+        self.dB = D.wrap(self.tB.data_ptr(), k, n, ws, keepalive=self.tB)
+        self.dBt = D.wrap(self.tBt.data_ptr(), n, k, kws, keepalive=self.tBt)
+        if self.srows > 0:
+            src_ptr = int(self.hB.buffer_ptrs[src]) + self.s0 * ws * 8
+            self.dSlab = D.wrap(src_ptr, self.srows, n, ws, keepalive=self.tB)
+            self.dDst = [D.wrap(int(p) + (self.s0 // 64) * 8, n, self.srows, kws, keepalive=self.tBt)
+                         for p in self.hBt.buffer_ptrs]
+            self.dst_arr = (ctypes.c_void_p * self.world)(*[d.h for d in self.dDst])
+
+    def step(self, algo=0):
+        self.hBt.barrier(channel=0)  # every rank is done reading its Bt of the previous step
+        if self.srows > 0:
+            self.L.m4ri_b200_dtranspose_scatter(self.dst_arr, self.world, self.dSlab.h)
+        self.hBt.barrier(channel=1)  # every slab of Bt has landed everywhere
+        if self.rows > 0:
+            self.m4.dmul_abt(self.dC, self.dA, self.dBt, clear=True, algo=algo)

@@ -98,3 +98,37 @@ def test_sharded_product_gloo(tmp_path, orc, world, m, k, n, chunks):
     assert got.shape == want.shape and (got == want).all()
     for r in range(world):  # every rank ended up with rank 0's B
         assert (np.load(tmp_path / f"b{r}.npy") == B[:, : w(n)]).all()
+
+
+def test_k_chunks_ramp_and_sm_reservation(m4):
+    from m4ri_rust_b200 import sharded
+    assert sharded.k_chunks_ramp(65536) == [(0, 8192), (8192, 32768), (32768, 65536)]
+    assert sharded.k_chunks_ramp(4096) == [(0, 4096)] and sharded.k_chunks_ramp(8192) == [(0, 8192)]
+    for k in (16384, 20000, 70000):
+        plan = sharded.k_chunks_ramp(k)
+        assert plan[0][0] == 0 and plan[-1][1] == k
+        assert all(a % 1024 == 0 and b > a for a, b in plan) and all(p[1] == q[0] for p, q in zip(plan, plan[1:]))
+
+    class FakeWork:
+        def wait(self):
+            pass
+
+    class FakeDist:  # world of 2 without a process group: records the order of the calls
+        def __init__(self, log):
+            self.log = log
+        def get_world_size(self):
+            return 2
+        def get_rank(self):
+            return 0
+        def broadcast(self, t, src, async_op):
+            self.log.append(("bcast", t.shape[0]))
+            return FakeWork()
+
+    import torch
+    log = []
+    sm = sharded.ShardedMul(512, 65536, 64, dist=FakeDist(log), chunks="ramp", tB=torch.zeros((65536, 1), dtype=torch.int64),
+                            chunk_product=lambda i, k0, k1, clear: log.append(("mul", i, clear)),
+                            reserve_sms=lambda r: log.append(("reserve", r)))
+    sm.step()
+    assert log == [("bcast", 8192), ("bcast", 24576), ("bcast", 32768),
+                   ("reserve", 8), ("mul", 0, True), ("reserve", 8), ("mul", 1, False), ("reserve", 0), ("mul", 2, False)]
