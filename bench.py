@@ -169,7 +169,7 @@ def run_lpn(args):
     out["matvec"] = {"ms": ms, "tbitops": 2.0 * m * k / ms / 1e9,
                      "roofline": {"bound": "hbm", "achieved": bytes_alg / ms / 1e6, "peak": pk["hbm_gbs"],
                                   "unit": "GB/s", "frac": bytes_alg / ms / 1e6 / pk["hbm_gbs"], "traffic": None,
-                                  "kernel": "mul_v_rows_kernel<4>", "algorithmic_bytes": bytes_alg}}
+                                  "kernel": "mul_v_coal_kernel<4>", "algorithmic_bytes": bytes_alg}}
     # the same kernel on a 4x taller A (256 MiB > L2): launch latency amortised, no flush needed
     m2 = 1 << 22
     dA2 = m4.DMat.init(m2, k).fill_random(31)
@@ -179,8 +179,21 @@ def run_lpn(args):
     out["matvec_2^22_rows"] = {"ms": ms2, "tbitops": 2.0 * m2 * k / ms2 / 1e9,
                                "roofline": {"bound": "hbm", "achieved": b2 / ms2 / 1e6, "peak": pk["hbm_gbs"],
                                             "unit": "GB/s", "frac": b2 / ms2 / 1e6 / pk["hbm_gbs"],
-                                            "traffic": None, "kernel": "mul_v_rows_kernel<4>",
+                                            "traffic": None, "kernel": "mul_v_coal_kernel<4>",
                                             "algorithmic_bytes": b2}}
+    del dA2, dy2
+    # long rows: square 32768 x 32768 A (128 MiB), one warp per row
+    m3 = n3 = 32768
+    dA3 = m4.DMat.init(m3, n3).fill_random(41)
+    dx3 = m4.DMat.init(1, n3).fill_random(42)
+    dy3 = m4.DMat.init(1, m3)
+    ms3 = timed(lambda: L.m4ri_b200_dmul_v(dy3.h, dA3.h, dx3.h, 1), args.steps, args.warmup)
+    b3 = 8 * (m3 * (n3 // 64) + n3 // 64) + (m3 // 64) * 8
+    out["matvec_32768x32768"] = {"ms": ms3, "tbitops": 2.0 * m3 * n3 / ms3 / 1e9,
+                                 "roofline": {"bound": "hbm", "achieved": b3 / ms3 / 1e6, "peak": pk["hbm_gbs"],
+                                              "unit": "GB/s", "frac": b3 / ms3 / 1e6 / pk["hbm_gbs"],
+                                              "traffic": None, "kernel": "mul_v_long_kernel",
+                                              "algorithmic_bytes": b3}}
     print(json.dumps(out))
 
 

@@ -117,6 +117,10 @@ void m4ri_b200_set_strassen_levels(int levels);
  * product (the NCCL broadcast of the next k-chunk of B, sharded.py) needs a few SMs of its own:
  * sms > 0 caps the SMs the product kernels launched after this call use (0 = all). */
 void m4ri_b200_set_sm_limit(int sms);
+/* Block plan the host-ABI products use to overlap PCIe copies with the kernels on an
+ * m x k x n product: row-chunks of A and column blocks of B (pure host arithmetic, no device
+ * needed; M4RI_B200_PIPE_ROWS / M4RI_B200_PIPE_COLS override it). */
+void m4ri_b200_pipeline_plan(int m, int k, int n, int clear, int *row_chunks, int *col_blocks);
 /* Kernel variant behind M4RI_B200_ALGO_MMA (0 restores the default; also
  * settable with M4RI_B200_MMA=v1|v2cg1|v2|fp4cg1|fp4|fp4tma): benchmarking knob. */
 enum m4ri_b200_mma_variant {

@@ -383,42 +383,155 @@ static void dmul_abt(DMat *C, const DMat *A, const DMat *Bt, int clear, int algo
 // finished rows of C back — H2D, compute and D2H overlap (separate copy engines), so the
 // call costs about upload(B) + kernels instead of upload(A,B) + kernels + download(C).
 static thread_local cudaStream_t t_h2d = nullptr, t_d2h = nullptr;
+static int pipeline_parts(const char *env, int dflt) {  // experiment hook: chunk counts of the host pipeline
+  const char *e = getenv(env);
+  int v = e ? atoi(e) : 0;
+  return v >= 1 && v <= 64 ? v : dflt;
+}
 static const size_t PIPELINE_MIN_BYTES = (size_t)24 << 20;
+
+// Block plan of the pipeline below: (row-chunks of A) x (column blocks of B), chosen by replaying
+// the schedule on a cost model — PCIe at 55 GB/s each way, a product = ceil(tiles / 74 CTA pairs)
+// waves of 256 x 256 x k tiles at the measured 7.4 Pop/s (1.31 ns per wave per bit of k) + 8 us
+// per launch. Few blocks start late (all of B's first block and A's first chunk must arrive);
+// many blocks waste partial waves. The model reproduces the measured sweep at n = 32768 within
+// 2 % (profiles/r1k_e2e_sweep.jsonl: 8x1 12.85, 8x4 11.15, 4x4 10.98, 8x8 13.2, 16x8 14.0 ms).
+static void plan_pipeline(rci_t m, rci_t k, rci_t n, int clear, int *best_na, int *best_nb) {
+  static const int cand[] = {1, 2, 3, 4, 6, 8, 12, 16};
+  const double pcie = 55e9 * 1e-3 /* bytes per ms */, wave = k * 1.31e-6, launch = 0.008;
+  double best = 1e300;
+  *best_na = *best_nb = 1;
+  for (int ca : cand)
+    for (int cb : cand) {
+      const rci_t per = ((m + ca - 1) / ca + 255) / 256 * 256, cper = ((n + cb - 1) / cb + 255) / 256 * 256;
+      const int na = (m + per - 1) / per, nb = (n + cper - 1) / cper;
+      auto rows_of = [&](int i) { return (double)((i + 1) * (long long)per < m ? per : m - i * (long long)per); };
+      auto cols_of = [&](int j) { return (double)((j + 1) * (long long)cper < n ? cper : n - j * (long long)cper); };
+      std::vector<double> arr_a(na), arr_b(nb);
+      double up = cols_of(0) * k / 8 / pcie;
+      arr_b[0] = up;
+      for (int i = 0; i < na; i++) {
+        up += rows_of(i) * (k + (clear ? 0 : n)) / 8 / pcie;
+        arr_a[i] = up;
+      }
+      for (int j = 1; j < nb; j++) {
+        up += cols_of(j) * k / 8 / pcie;
+        arr_b[j] = up;
+      }
+      double t = 0;
+      for (int j = 0; j < nb; j++)
+        for (int i = 0; i < na; i++) {
+          const double ready = arr_a[i] > arr_b[j] ? arr_a[i] : arr_b[j];
+          const double tiles = ceil(rows_of(i) / 256) * ceil(cols_of(j) / 256);
+          t = (t > ready ? t : ready) + ceil(tiles / 74) * wave + launch;
+        }
+      t += rows_of(na - 1) * cols_of(nb - 1) / 8 / pcie;  // the last block's way home
+      if (t < best) best = t, *best_na = na, *best_nb = nb;
+    }
+}
+
+// Words [w0, w1) of every row of H -> the same words of D (a column block), and words [w0, w1)
+// of rows [r0, r1) of D -> H: the 2-D copies of upload_rows/download_rows on a column window.
+static void upload_cols(DMat *D, const mzd_t *H, wi_t w0, wi_t w1, cudaStream_t s) {
+  if (w1 <= w0 || H->nrows == 0) return;
+  rci_t i = 0;
+  while (i < H->nrows) {
+    rci_t j = i + 1;
+    while (j < H->nrows && H->rows[j] == H->rows[i] + (size_t)(j - i) * H->rowstride) j++;
+    M4B_CUDA(cudaMemcpy2DAsync(D->d + (size_t)i * D->rowstride + w0, (size_t)D->rowstride * 8,
+                               H->rows[i] + w0, (size_t)H->rowstride * 8, (size_t)(w1 - w0) * 8,
+                               j - i, cudaMemcpyHostToDevice, s));
+    i = j;
+  }
+  if (w1 == H->width && D->ncols % 64) k_mask_excess(D, s);  // touches the last word of each row only
+}
+static void download_block(mzd_t *H, const DMat *D, rci_t r0, rci_t r1, wi_t w0, wi_t w1,
+                           cudaStream_t s) {
+  if (r1 <= r0 || w1 <= w0) return;
+  rci_t i = r0;
+  while (i < r1) {
+    rci_t j = i + 1;
+    while (j < r1 && H->rows[j] == H->rows[i] + (size_t)(j - i) * H->rowstride) j++;
+    M4B_CUDA(cudaMemcpy2DAsync(H->rows[i] + w0, (size_t)H->rowstride * 8,
+                               D->d + (size_t)i * D->rowstride + w0, (size_t)D->rowstride * 8,
+                               (size_t)(w1 - w0) * 8, j - i, cudaMemcpyDeviceToHost, s));
+    i = j;
+  }
+}
+
+// Device buffer every word of which is about to be overwritten: skips dmat_new's memset when
+// the rows have no padding word (stride == width).
+static DMat *dmat_new_overwritten(rci_t nrows, rci_t ncols, cudaStream_t s) {
+  if (dev_rowstride(ncols) != width_of(ncols) || nrows <= 0) return dmat_new(nrows, ncols, s);
+  DMat *M = (DMat *)calloc(1, sizeof(DMat));
+  if (!M) die("m4ri_b200: out of memory\n");
+  M->nrows = nrows;
+  M->ncols = ncols;
+  M->width = M->rowstride = width_of(ncols);
+  M4B_CUDA(cudaMallocAsync(&M->base, (size_t)nrows * M->rowstride * 8, s));
+  M->d = (word *)M->base;
+  return M;
+}
 
 static void pipelined_host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int clear, int form,
                                    cudaStream_t s) {
   if (!t_h2d) M4B_CUDA(cudaStreamCreateWithFlags(&t_h2d, cudaStreamNonBlocking));
   if (!t_d2h) M4B_CUDA(cudaStreamCreateWithFlags(&t_d2h, cudaStreamNonBlocking));
-  const rci_t m = A->nrows, n = C->ncols;
-  DMat *dA = dmat_new(A->nrows, A->ncols, s), *dB = dmat_new(B->nrows, B->ncols, s),
-       *dC = dmat_new(m, n, s);
-  DMat *dBt = form == 0 ? dmat_new(B->ncols, B->nrows, s) : dB;
-  int nchunks = 8;
-  rci_t per = ((m + nchunks - 1) / nchunks + 255) / 256 * 256;
-  nchunks = (m + per - 1) / per;
-  std::vector<cudaEvent_t> ev(2 * nchunks + 2);
+  const rci_t m = A->nrows, n = C->ncols, k = A->ncols;
+  DMat *dA = dmat_new_overwritten(m, k, s), *dB = dmat_new_overwritten(B->nrows, B->ncols, s),
+       *dC = dmat_new_overwritten(m, n, s);
+  DMat *dBt = form == 0 ? dmat_new_overwritten(n, k, s) : dB;
+  // C is computed in (row-chunk of A) x (column block of B) pieces so that the tensor cores
+  // start after one column block of B and one row-chunk of A have arrived (1/NB + 1/NA of the
+  // upload), not after all of B. Blocks are multiples of the 256 x 256 tile.
+  int na, nb;
+  plan_pipeline(m, k, n, clear, &na, &nb);
+  na = pipeline_parts("M4RI_B200_PIPE_ROWS", na);
+  nb = pipeline_parts("M4RI_B200_PIPE_COLS", nb);
+  rci_t per = ((m + na - 1) / na + 255) / 256 * 256;
+  na = (m + per - 1) / per;
+  rci_t cper = ((n + nb - 1) / nb + 255) / 256 * 256;
+  nb = (n + cper - 1) / cper;
+  std::vector<cudaEvent_t> ev(na + nb + na * nb + 1);
   for (auto &e : ev) M4B_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-  cudaEvent_t e_alloc = ev[2 * nchunks], e_b = ev[2 * nchunks + 1];
-  M4B_CUDA(cudaEventRecord(e_alloc, s));  // buffers exist and are zeroed
+  cudaEvent_t *ev_a = ev.data(), *ev_b = ev.data() + na, *ev_c = ev.data() + na + nb;
+  cudaEvent_t e_alloc = ev[na + nb + na * nb];
+  M4B_CUDA(cudaEventRecord(e_alloc, s));  // buffers exist
   M4B_CUDA(cudaStreamWaitEvent(t_h2d, e_alloc, 0));
-  upload(dB, B, t_h2d);
-  M4B_CUDA(cudaEventRecord(e_b, t_h2d));
-  for (int i = 0; i < nchunks; i++) {
+  auto upload_b = [&](int j) {
+    const rci_t c0 = j * cper, c1 = c0 + cper < n ? c0 + cper : n;
+    if (form == 0) upload_cols(dB, B, c0 / 64, (c1 + 63) / 64, t_h2d);  // k x n: a column block
+    else upload_rows(dB, B, c0, c1, t_h2d);                             // n x k: a row block
+    M4B_CUDA(cudaEventRecord(ev_b[j], t_h2d));
+  };
+  // upload order: B block 0, every row-chunk of A (the first column block's products follow
+  // them one by one), then the other blocks of B
+  upload_b(0);
+  for (int i = 0; i < na; i++) {
     const rci_t r0 = i * per, r1 = r0 + per < m ? r0 + per : m;
     upload_rows(dA, A, r0, r1, t_h2d);
     if (!clear) upload_rows(dC, C, r0, r1, t_h2d);
-    M4B_CUDA(cudaEventRecord(ev[i], t_h2d));
+    M4B_CUDA(cudaEventRecord(ev_a[i], t_h2d));
   }
-  M4B_CUDA(cudaStreamWaitEvent(s, e_b, 0));
-  if (form == 0) k_transpose(dBt, dB, s);
-  for (int i = 0; i < nchunks; i++) {
-    const rci_t r0 = i * per, r1 = r0 + per < m ? r0 + per : m;
-    DMat Ai = dwin(dA, r0, 0, r1 - r0, A->ncols), Ci = dwin(dC, r0, 0, r1 - r0, n);
-    M4B_CUDA(cudaStreamWaitEvent(s, ev[i], 0));
-    k_mul_abt_mma(&Ci, &Ai, dBt, clear, s);
-    M4B_CUDA(cudaEventRecord(ev[nchunks + i], s));
-    M4B_CUDA(cudaStreamWaitEvent(t_d2h, ev[nchunks + i], 0));
-    download_rows(C, dC, r0, r1, t_d2h);
+  for (int j = 1; j < nb; j++) upload_b(j);
+  for (int j = 0; j < nb; j++) {
+    const rci_t c0 = j * cper, c1 = c0 + cper < n ? c0 + cper : n;
+    M4B_CUDA(cudaStreamWaitEvent(s, ev_b[j], 0));
+    DMat Btj = dwin(dBt, c0, 0, c1 - c0, k);
+    if (form == 0) {
+      DMat Bj = dwin(dB, 0, c0, k, c1 - c0);
+      k_transpose(&Btj, &Bj, s);
+    }
+    for (int i = 0; i < na; i++) {
+      const rci_t r0 = i * per, r1 = r0 + per < m ? r0 + per : m;
+      DMat Ai = dwin(dA, r0, 0, r1 - r0, k), Cij = dwin(dC, r0, c0, r1 - r0, c1 - c0);
+      if (j == 0) M4B_CUDA(cudaStreamWaitEvent(s, ev_a[i], 0));
+      k_mul_abt_mma(&Cij, &Ai, &Btj, clear, s);
+      cudaEvent_t e = ev_c[j * na + i];
+      M4B_CUDA(cudaEventRecord(e, s));
+      M4B_CUDA(cudaStreamWaitEvent(t_d2h, e, 0));
+      download_block(C, dC, r0, r1, c0 / 64, (c1 + 63) / 64, t_d2h);
+    }
   }
   M4B_CUDA(cudaEventRecord(e_alloc, t_d2h));  // reuse: everything has left the device
   M4B_CUDA(cudaStreamWaitEvent(s, e_alloc, 0));
@@ -590,6 +703,9 @@ int m4ri_b200_get_algo(void) {
   return g_algo.load();
 }
 void m4ri_b200_set_strassen_levels(int levels) { g_strassen.store(levels); }
+void m4ri_b200_pipeline_plan(int m, int k, int n, int clear, int *row_chunks, int *col_blocks) {
+  plan_pipeline(m, k, n, clear, row_chunks, col_blocks);
+}
 void m4ri_b200_set_sm_limit(int sms) { g_sm_limit.store(sms < 0 ? 0 : (sms & ~1)); }
 void m4ri_b200_set_mma_variant(int variant) {
   if (variant < 0 || variant > 7) die("m4ri_b200: unknown MMA variant %d\n", variant);

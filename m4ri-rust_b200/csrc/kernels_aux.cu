@@ -349,6 +349,98 @@ mul_v_rows_kernel(uint32_t *__restrict__ y, const ulonglong2 *__restrict__ A,
   }
 }
 
+// Long rows (>= 32 16-byte vectors) and many of them: a CTA of 8 warps owns 32 consecutive rows
+// = one aligned 32-bit word of y (no atomics, no memset of y). Warp w walks its 4 rows together:
+// per step one 16-byte load of x feeds four independent 16-byte loads of A (two steps unrolled:
+// 128 B in flight per lane); a row's parity is the parity of one ballot of the lane parities.
+__global__ void __launch_bounds__(256)
+mul_v_long_kernel(uint32_t *__restrict__ y, const ulonglong2 *__restrict__ A,
+                  const ulonglong2 *__restrict__ x, int m, int wv, int as, int clear) {
+  __shared__ unsigned sbits[8];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const long long row0 = blockIdx.x * 32LL + w * 4;
+  const ulonglong2 *ar[4];
+#pragma unroll
+  for (int r = 0; r < 4; r++) {
+    const long long row = row0 + r < m ? row0 + r : m - 1;  // rows past m: read a valid row, drop the bit
+    ar[r] = A + (size_t)row * as;
+  }
+  uint64_t acc[4] = {0, 0, 0, 0};
+#pragma unroll 2
+  for (int v = lane; v < wv; v += 32) {
+    const ulonglong2 b = __ldg(&x[v]);
+#pragma unroll
+    for (int r = 0; r < 4; r++) {
+      ulonglong2 a;
+      asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0,%1}, [%2];" : "=l"(a.x), "=l"(a.y) : "l"(ar[r] + v));
+      acc[r] ^= (a.x & b.x) ^ (a.y & b.y);
+    }
+  }
+  unsigned bits = 0;
+#pragma unroll
+  for (int r = 0; r < 4; r++) {
+    const unsigned ball = __ballot_sync(0xffffffffu, __popcll(acc[r]) & 1);
+    if (row0 + r < m) bits |= (unsigned)(__popc(ball) & 1) << r;
+  }
+  if (lane == 0) sbits[w] = bits;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned word32 = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) word32 |= sbits[i] << (4 * i);
+    uint32_t *dst = y + blockIdx.x;
+    *dst = clear ? word32 : (*dst ^ word32);
+  }
+}
+
+static bool mul_v_force_rows() {  // M4RI_B200_MULV=rows: keep the thread-per-row kernel (A/B timing, tests)
+  const char *e = getenv("M4RI_B200_MULV");
+  return e && !strcmp(e, "rows");
+}
+
+// Short rows of 1, 2, 4 or 8 16-byte vectors stored back to back (row stride == row length):
+// a warp owns 32 consecutive rows = 32*WV consecutive vectors and reads them with WV fully
+// coalesced 512-byte requests (lane l of request j takes vector j*32 + l, i.e. row
+// j*(32/WV) + l/WV, column l%WV — every 32-byte sector is fetched once, by one request).
+// Lane parities are folded over the WV lanes of a row with shuffles; one more shuffle and one
+// ballot put the 32 row parities in row order = one aligned 32-bit word of y.
+template <int WV, int U /* 32-row groups per warp: U*WV 16-byte loads in flight per lane */>
+__global__ void __launch_bounds__(256)
+mul_v_coal_kernel(uint32_t *__restrict__ y, const ulonglong2 *__restrict__ A,
+                  const ulonglong2 *__restrict__ x, long long m, int clear) {
+  constexpr int RPI = 32 / WV;  // rows per request
+  const int lane = threadIdx.x & 31;
+  const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  const long long row0 = warp * (32 * U), mpad = (m + 63) & ~63LL;  // y is written in whole 64-bit words
+  if (row0 >= mpad) return;
+  const long long nvec = m * WV, v0 = row0 * WV + lane;
+  ulonglong2 a[U * WV];
+#pragma unroll
+  for (int j = 0; j < U * WV; j++) {
+    a[j] = make_ulonglong2(0, 0);
+    if (v0 + j * 32 < nvec)
+      asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0,%1}, [%2];"
+                   : "=l"(a[j].x), "=l"(a[j].y) : "l"(A + v0 + j * 32));
+  }
+  const ulonglong2 b = __ldg(&x[lane % WV]);
+  unsigned v = 0;  // bit j = parity of this lane's vector of request j
+#pragma unroll
+  for (int j = 0; j < U * WV; j++)
+    v |= (unsigned)(__popcll((a[j].x & b.x) ^ (a[j].y & b.y)) & 1) << j;
+#pragma unroll
+  for (int o = 1; o < WV; o <<= 1) v ^= __shfl_xor_sync(0xffffffffu, v, o);
+  // row r (0..31) of group u: request u*WV + r / RPI, lanes (r % RPI)*WV ...
+  const unsigned t = __shfl_sync(0xffffffffu, v, (lane % RPI) * WV) >> (lane / RPI);
+#pragma unroll
+  for (int u = 0; u < U; u++) {
+    const unsigned bits = __ballot_sync(0xffffffffu, (t >> (u * WV)) & 1u);
+    if (lane == 0 && row0 + u * 32 < mpad) {
+      uint32_t *dst = y + ((row0 >> 5) + u);
+      *dst = clear ? bits : (*dst ^ bits);
+    }
+  }
+}
+
 void k_mul_v(DMat *y, const DMat *A, const DMat *x, int clear, cudaStream_t s) {
   if (A->nrows == 0 || A->ncols == 0) {
     if (clear) k_zero(y, s);
@@ -363,6 +455,17 @@ void k_mul_v(DMat *y, const DMat *A, const DMat *x, int clear, cudaStream_t s) {
     uint32_t *yy = (uint32_t *)y->d;
     const ulonglong2 *AA = (const ulonglong2 *)A->d, *xx = (const ulonglong2 *)x->d;
     const int mm = A->nrows;
+    if (as == wv && (wv & (wv - 1)) == 0 && !mul_v_force_rows()) {  // rows back to back: coalesced warp-per-32-rows kernel
+      const long long groups = ((long long)mm + 63) / 64 * 2;  // 32-row groups
+      switch (wv) {
+        case 1: mul_v_coal_kernel<1, 8><<<cdiv(cdiv(groups, 8), 8), 256, 0, s>>>(yy, AA, xx, mm, clear); break;
+        case 2: mul_v_coal_kernel<2, 4><<<cdiv(cdiv(groups, 4), 8), 256, 0, s>>>(yy, AA, xx, mm, clear); break;
+        case 4: mul_v_coal_kernel<4, 2><<<cdiv(cdiv(groups, 2), 8), 256, 0, s>>>(yy, AA, xx, mm, clear); break;
+        default: mul_v_coal_kernel<8, 1><<<cdiv(groups, 8), 256, 0, s>>>(yy, AA, xx, mm, clear); break;
+      }
+      M4B_LAUNCHED();
+      return;
+    }
     switch (wv) {
       case 1: mul_v_rows_kernel<1><<<grid, 256, 0, s>>>(yy, AA, xx, mm, as, clear); break;
       case 2: mul_v_rows_kernel<2><<<grid, 256, 0, s>>>(yy, AA, xx, mm, as, clear); break;
@@ -373,6 +476,14 @@ void k_mul_v(DMat *y, const DMat *A, const DMat *x, int clear, cudaStream_t s) {
       case 7: mul_v_rows_kernel<7><<<grid, 256, 0, s>>>(yy, AA, xx, mm, as, clear); break;
       default: mul_v_rows_kernel<8><<<grid, 256, 0, s>>>(yy, AA, xx, mm, as, clear); break;
     }
+    M4B_LAUNCHED();
+    return;
+  }
+  if (wv >= 32 && A->nrows >= 2048 && !mul_v_force_rows()) {
+    // whole 64-bit words of y: an even number of 32-row CTAs
+    unsigned grid = cdiv(((long long)A->nrows + 63) / 64 * 64, 32);
+    mul_v_long_kernel<<<grid, 256, 0, s>>>((uint32_t *)y->d, (const ulonglong2 *)A->d,
+                                           (const ulonglong2 *)x->d, A->nrows, wv, as, clear);
     M4B_LAUNCHED();
     return;
   }

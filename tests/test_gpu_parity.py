@@ -200,7 +200,9 @@ def test_transpose_add_device_and_host(gpu, m4, orc):
 def test_matvec_shapes(gpu, m4, orc):
     L = m4.lib()
     for (m, n) in [(34, 128), (10, 10), (64, 1000), (1000, 64), (1, 1), (4097, 777), (300, 8192),
-                   (20, 512), (33, 64), (100, 129), (70000, 512), (65, 1024), (4096, 960)]:
+                   (20, 512), (33, 64), (100, 129), (70000, 512), (65, 1024), (4096, 960),
+                   (1000, 256), (100001, 128), (12345, 1024), (31, 200), (8191, 70), (2049, 500),
+                   (4100, 4096), (2049, 5000), (3000, 2112), (2048, 32768), (2081, 4097)]:
         A = orc.random(m, n, 3)
         x = orc.random(1, n, 4)
         a = host(m4, A, n)
@@ -221,6 +223,28 @@ def test_matvec_shapes(gpu, m4, orc):
         L.m4ri_b200_dmul_v(dy.h, dA.h, dx.h, 0)  # accumulate: y ^= A*x restores zero
         assert not dy.to_words().any()
         L.mzd_free(hx)
+
+
+def test_matvec_short_row_kernels_agree(gpu, m4, orc, monkeypatch):
+    """Rows of 1/2/4/8 16-byte vectors: the coalesced warp-per-32-rows kernel (default) and the
+    thread-per-row kernel (M4RI_B200_MULV=rows) against the oracle, ragged m, clear and accumulate."""
+    L = m4.lib()
+    for n in (64, 128, 200, 256, 512, 1000, 1024):
+        for m in (1, 31, 32, 33, 63, 64, 65, 255, 4097, 100003):
+            A = orc.random(m, n, 5)
+            x = orc.random(1, n, 6)
+            want = orc.mul_v(A, x[0], n)
+            a, hx = host(m4, A, n), host(m4, x, n)
+            dA, dx = m4.DMat.from_host(a), m4.DMat.from_host(hx)
+            for mode in ("", "rows"):
+                monkeypatch.setenv("M4RI_B200_MULV", mode)
+                dy = m4.DMat.init(1, m)
+                L.m4ri_b200_dmul_v(dy.h, dA.h, dx.h, 1)
+                assert (dy.to_words()[0, : orc.width(m)] == want).all(), (m, n, mode)
+                L.m4ri_b200_dmul_v(dy.h, dA.h, dx.h, 0)
+                assert not dy.to_words().any(), (m, n, mode)
+            L.mzd_free(hx)
+            L.mzd_free(a)
 
 
 def test_device_generator_and_checksum_match_oracle(gpu, m4, orc):
@@ -307,7 +331,7 @@ def test_lpn_shape(gpu, m4, orc):
         assert (head.to_words() == want).all()
 
 
-def test_pipelined_host_products(gpu, m4, orc):
+def test_pipelined_host_products(gpu, m4, orc, monkeypatch):
     """Host-ABI products large enough for the copy/compute-overlapped path (api.cu,
     pipelined_host_product): ragged shapes, accumulate, an operand that is a window of
     a bigger matrix (rows[] with a foreign stride), and the pre-transposed form."""
@@ -330,6 +354,22 @@ def test_pipelined_host_products(gpu, m4, orc):
         assert (got == want).all(), (m, k, n)
         for p in (a, b, bt):
             L.mzd_free(p)
+    # other block plans of the pipeline (rows of A x column blocks of B), ragged blocks
+    m, k, n = 3000, 30000, 5003
+    A, B, C0 = orc.random(m, k, 41), orc.random(k, n, 42), orc.random(m, n, 43)
+    want = orc.mul_m4rm(A, B, k, n, threads=0)[:, : orc.width(n)]
+    a, b = host(m4, A, k), host(m4, B, n)
+    for rows_, cols_ in [(1, 1), (3, 5), (12, 2), (2, 20)]:
+        monkeypatch.setenv("M4RI_B200_PIPE_ROWS", str(rows_))
+        monkeypatch.setenv("M4RI_B200_PIPE_COLS", str(cols_))
+        assert (result_words(m4, L.mzd_mul(None, a, b, 0)) == want).all(), (rows_, cols_)
+        c = host(m4, C0, n)
+        L.mzd_addmul(c, a, b, 0)
+        assert (result_words(m4, c) == (C0[:, : orc.width(n)] ^ want)).all(), (rows_, cols_)
+    monkeypatch.delenv("M4RI_B200_PIPE_ROWS")
+    monkeypatch.delenv("M4RI_B200_PIPE_COLS")
+    for q in (a, b):
+        L.mzd_free(q)
     # window operand: 4000 x 16384 window at column 128 of a 4100 x 20000 parent
     P = orc.random(4100, 20000, 31)
     p = host(m4, P, 20000)
