@@ -252,10 +252,11 @@ def main():
 
     import torch
     import m4ri_rust_b200 as m4
+    if torch.cuda.is_available():
+        torch.cuda.set_device(local_rank)  # before the library is touched: its context is this rank's GPU
     L = m4.lib()
     if m4.device_count() <= 0:
         raise SystemExit("bench.py: no CUDA device; libm4ri_b200 has no CPU fallback")
-    torch.cuda.set_device(local_rank)
     dist = None
     if world > 1:
         import torch.distributed as dist_mod
@@ -433,7 +434,8 @@ def main():
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": config,
             "clocks": clocks, "gpu_launches": int(launches), "roofline": roof,
-            "parity": {"freivalds_2^-64": True, "checksum_rank0": f"{chk:016x}"}}
+            "parity": {"freivalds_2^-64": True, "checksum_rank0": f"{chk:016x}"},
+            "step_ms_rank0": [round(x, 3) for x in step_ms]}
     if e2e_ms is not None:
         bytes_in = (rows * ws + n * ws) * 8
         line["e2e"] = {"value": total_ops / (e2e_max * 1e-3) / 1e12, "unit": "Tbit-op/s",

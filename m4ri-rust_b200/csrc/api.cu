@@ -75,14 +75,6 @@ static void probe() {
       g_cc_major = p.major;
       g_cc_minor = p.minor;
       snprintf(g_name, sizeof(g_name), "%s", p.name);
-      // Device mirrors and Strassen temporaries come from the stream-ordered pool; keep freed
-      // blocks cached instead of returning them to the driver at every synchronize (a fresh
-      // 128 MiB cudaMallocAsync costs ~0.5 ms, three of them per host-ABI product).
-      cudaMemPool_t pool;
-      if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
-        unsigned long long keep = ~0ull;
-        (void)cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
-      }
       (void)cudaGetLastError();
     } else {
       (void)cudaGetLastError();
@@ -156,7 +148,27 @@ void k_mul_abt_mma(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream
 }
 
 // ---- device matrices -------------------------------------------------------------
+// Keep freed blocks of the CURRENT device's stream-ordered pool cached instead of returning them
+// to the driver at every synchronize (a fresh 128 MiB cudaMallocAsync costs ~0.5 ms, more with
+// peer mappings). Per device: a process may select its GPU after the library was first touched
+// (one rank per GPU under torchrun), so this cannot live in the one-time probe().
+static void keep_pool_cached() {
+  static std::atomic<unsigned long long> done{0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return;
+  const unsigned long long bit = 1ull << dev;
+  if (done.load(std::memory_order_relaxed) & bit) return;
+  cudaMemPool_t pool;
+  if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+    unsigned long long keep = ~0ull;
+    (void)cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+  }
+  (void)cudaGetLastError();
+  done.fetch_or(bit);
+}
+
 static DMat *dmat_new(rci_t nrows, rci_t ncols, cudaStream_t s) {
+  keep_pool_cached();
   if (nrows < 0 || ncols < 0) die("m4ri_b200: negative matrix dimension\n");
   DMat *M = (DMat *)calloc(1, sizeof(DMat));
   if (!M) die("m4ri_b200: out of memory\n");
@@ -259,6 +271,7 @@ static void leaf_mul(DMat *C, const DMat *A, const DMat *B, int clear, int algo,
 }
 
 // C = A (*) B, overwriting C. Quadrant (i,j) of the logical k x n matrix B.
+static DMat *dmat_new_overwritten(rci_t nrows, rci_t ncols, cudaStream_t s);
 static void strassen_mul(DMat *C, const DMat *A, const DMat *B, int algo, int form, int levels,
                          cudaStream_t s) {
   const int m = C->nrows, n = C->ncols, k = A->ncols;
@@ -276,7 +289,9 @@ static void strassen_mul(DMat *C, const DMat *A, const DMat *B, int algo, int fo
   DMat B11 = Bq(0, 0), B12 = Bq(0, 1), B21 = Bq(1, 0), B22 = Bq(1, 1);
   DMat C11 = dwin(C, 0, 0, m2, n2), C12 = dwin(C, 0, n2, m2, n2), C21 = dwin(C, m2, 0, m2, n2),
        C22 = dwin(C, m2, n2, m2, n2);
-  DMat *X = dmat_new(m2, k2, s), *Y = dmat_new(B11.nrows, B11.ncols, s), *Z = dmat_new(m2, n2, s);
+  // (every word of the three temporaries is written before it is read: no memset)
+  DMat *X = dmat_new_overwritten(m2, k2, s), *Y = dmat_new_overwritten(B11.nrows, B11.ncols, s),
+       *Z = dmat_new_overwritten(m2, n2, s);
   const int L = levels - 1;
   k_add(X, &A21, &A22, s);                       // S1
   k_add(Y, &B11, &B12, s);                       // T1
@@ -315,6 +330,19 @@ static int strassen_levels(int m, int k, int n, int algo, int cutoff) {
   if (set >= 0) return set;
   // tuned on B200 (profiles/r1g_size_sweep_fp4.jsonl): one level pays from n = 32768 up on the
   // tensor path (leaves of 16384), never on the Four-Russians path below n = 65536
+  if (cutoff <= 0 && algo == M4RI_B200_ALGO_MMA) {
+    // the leaf kernel's efficiency depends on the leaf's volume (tiles x k), not on its smallest
+    // side: a level pays while the leaves keep the volume of a 16384-cube and whole tiles —
+    // e.g. the 8192 x 65536 x 65536 row-block of the 8-GPU product (leaves 4096 x 32768 x 32768)
+    long long mm = m, kk = k, nn = n;
+    int L = 0;
+    while (L < 4 && mm / 2 >= 4096 && kk / 2 >= 4096 && nn / 2 >= 4096 &&
+           (double)(mm / 2) * (double)(kk / 2) * (double)(nn / 2) >= 16384.0 * 16384.0 * 16384.0) {
+      mm /= 2, kk /= 2, nn /= 2;
+      L++;
+    }
+    return L;
+  }
   if (cutoff <= 0) cutoff = algo == M4RI_B200_ALGO_MMA ? 16384 : 32768;
   if (cutoff < 2048) cutoff = 2048;
   int L = 0, d = m < k ? m : k;
@@ -468,6 +496,7 @@ static DMat *dmat_new_overwritten(rci_t nrows, rci_t ncols, cudaStream_t s) {
   M->nrows = nrows;
   M->ncols = ncols;
   M->width = M->rowstride = width_of(ncols);
+  keep_pool_cached();
   M4B_CUDA(cudaMallocAsync(&M->base, (size_t)nrows * M->rowstride * 8, s));
   M->d = (word *)M->base;
   return M;

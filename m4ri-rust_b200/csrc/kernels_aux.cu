@@ -4,6 +4,8 @@
 // m4ri-rust/src/friendly/binary_matrix.rs:416-431), vec-mat (_mzd_mul_va,
 // mzd.rs:181), the AND+popcount product behind the *_naive entry points
 // (mzd.rs:152-173), plus input generation and checksums for the harness.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace m4b {
@@ -163,6 +165,91 @@ transpose_scatter_kernel(TransposeDsts dsts, const uint32_t *__restrict__ S, int
   }
 }
 
+// Wide form of the same scatter: 1024-row x 1024-bit input tiles, so that every output row
+// leaves the SM as 128 contiguous bytes (16-byte stores, a quarter-warp per row) instead of 32.
+// Over NVLink the 32-byte peer stores of the kernel above reach ~190 GB/s per GPU; 128-byte
+// segments are whole NVLink write packets (profiles/r1k_exchange_probe_*.json).
+// 512 threads: each half-CTA turns two 256-row sub-tiles (own 33 KB input buffer, named
+// barrier) into a shared 128 KB staging tile of 1024 output rows x 32 words; row r is stored
+// rotated by r words, which makes both the transposed stores (32 rows, one word each) and the
+// row-wise read-out (8 lanes x 4 words per row) conflict-free.
+constexpr int TW_IN = 256 * 33;                       // words per input buffer
+constexpr int TW_SMEM = (1024 * 32 + 2 * TW_IN) * 4;  // bytes
+__global__ void __launch_bounds__(512)
+transpose_wide_kernel(TransposeDsts dsts, const uint32_t *__restrict__ S, int nrows, int ncols,
+                      int sw32, int ss32, int ds32, int dw32) {
+  extern __shared__ __align__(16) uint32_t tw_smem[];
+  uint32_t *out = tw_smem;
+  const int half = threadIdx.x >> 8, t = threadIdx.x & 255;
+  uint32_t *in = tw_smem + 1024 * 32 + half * TW_IN;
+  const int w = t >> 5, l = t & 31;
+  const int r0 = blockIdx.y * 1024, cw0 = blockIdx.x * 32;
+  for (int sub = half; sub < 4; sub += 2) {
+    const int rs = r0 + sub * 256;
+#pragma unroll 8
+    for (int i = 0; i < 32; i++) {
+      const int row = i * 8 + w;
+      uint32_t v = 0;
+      if (rs + row < nrows && cw0 + l < sw32) v = S[(size_t)(rs + row) * ss32 + cw0 + l];
+      in[row * 33 + l] = v;
+    }
+    asm volatile("bar.sync %0, 256;" ::"r"(1 + half) : "memory");
+    uint32_t res[32];
+#pragma unroll
+    for (int c = 0; c < 32; c++) res[c] = transpose32(in[(32 * w + l) * 33 + c], l);
+    asm volatile("bar.sync %0, 256;" ::"r"(1 + half) : "memory");  // the input buffer may be refilled
+    // lane l of res[c] = word (sub*8 + w) of output row c*32 + l
+#pragma unroll
+    for (int c = 0; c < 32; c++) out[(c * 32 + l) * 32 + ((sub * 8 + w + l) & 31)] = res[c];
+  }
+  __syncthreads();
+#pragma unroll 4
+  for (int it = 0; it < 16; it++) {
+    const int idx = it * 512 + threadIdx.x;
+    const int r = idx >> 3, g = idx & 7;
+    const int orow = cw0 * 32 + r, ow = (r0 >> 5) + 4 * g;
+    if (orow < ncols && ow < dw32) {
+      uint4 v;
+      v.x = out[r * 32 + ((4 * g + 0 + r) & 31)];
+      v.y = out[r * 32 + ((4 * g + 1 + r) & 31)];
+      v.z = out[r * 32 + ((4 * g + 2 + r) & 31)];
+      v.w = out[r * 32 + ((4 * g + 3 + r) & 31)];
+      const size_t off = (size_t)orow * ds32 + ow;
+      if (ow + 4 <= dw32) {
+        for (int d = 0; d < dsts.n; d++) *reinterpret_cast<uint4 *>(dsts.p[d] + off) = v;
+      } else {  // ragged last chunk of a row: never write past the destination's width (windows)
+        const uint32_t vv[4] = {v.x, v.y, v.z, v.w};
+        for (int d = 0; d < dsts.n; d++)
+          for (int i = 0; i < 4 && ow + i < dw32; i++) dsts.p[d][off + i] = vv[i];
+      }
+    }
+  }
+}
+
+static int transpose_variant() {  // M4RI_B200_TRANSPOSE=narrow|wide (experiments, tests); default: see callers
+  const char *e = getenv("M4RI_B200_TRANSPOSE");
+  return !e ? 0 : !strcmp(e, "narrow") ? 1 : !strcmp(e, "wide") ? 2 : 0;
+}
+
+static bool transpose_wide_ok(const uint32_t *const *dst, int ndst, int ds32) {
+  if (ds32 % 4) return false;
+  for (int i = 0; i < ndst; i++)
+    if ((uintptr_t)dst[i] % 16) return false;
+  return true;
+}
+
+static void launch_transpose_wide(const TransposeDsts &dsts, const DMat *A, int ds32, int dw32, cudaStream_t s) {
+  static std::once_flag once;
+  std::call_once(once, [] {
+    M4B_CUDA(cudaFuncSetAttribute(transpose_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TW_SMEM));
+  });
+  const int sw32 = A->width * 2;
+  dim3 grid(cdiv(sw32, 32), cdiv(dw32, 32));
+  transpose_wide_kernel<<<grid, 512, TW_SMEM, s>>>(dsts, (const uint32_t *)A->d, A->nrows, A->ncols, sw32,
+                                                   A->rowstride * 2, ds32, dw32);
+  M4B_LAUNCHED();
+}
+
 void k_transpose_scatter(DMat *const *D, int ndst, const DMat *A, cudaStream_t s) {
   if (ndst < 1 || ndst > 8) die("m4ri_b200: transpose_scatter takes 1 to 8 destinations\n");
   if (A->nrows == 0 || A->ncols == 0) return;
@@ -174,6 +261,12 @@ void k_transpose_scatter(DMat *const *D, int ndst, const DMat *A, cudaStream_t s
     dsts.p[i] = (uint32_t *)D[i]->d;
   }
   const int sw32 = A->width * 2, dw32 = D[0]->width * 2;
+  // several destinations = peer stores over NVLink: the wide kernel unless told otherwise
+  const int var = transpose_variant();
+  if ((var == 2 || (var == 0 && ndst > 1)) && transpose_wide_ok(dsts.p, ndst, D[0]->rowstride * 2)) {
+    launch_transpose_wide(dsts, A, D[0]->rowstride * 2, dw32, s);
+    return;
+  }
   dim3 grid(cdiv(sw32, 32), cdiv(dw32, 8));
   transpose_scatter_kernel<<<grid, 256, 0, s>>>(dsts, (const uint32_t *)A->d, A->nrows, A->ncols, sw32,
                                                 A->rowstride * 2, D[0]->rowstride * 2, dw32);
@@ -183,6 +276,15 @@ void k_transpose_scatter(DMat *const *D, int ndst, const DMat *A, cudaStream_t s
 void k_transpose(DMat *D, const DMat *A, cudaStream_t s) {
   if (A->nrows == 0 || A->ncols == 0) return;
   const int sw32 = A->width * 2, dw32 = D->width * 2;
+  if (transpose_variant() == 2) {
+    TransposeDsts dsts;
+    dsts.n = 1;
+    dsts.p[0] = (uint32_t *)D->d;
+    if (transpose_wide_ok(dsts.p, 1, D->rowstride * 2)) {
+      launch_transpose_wide(dsts, A, D->rowstride * 2, dw32, s);
+      return;
+    }
+  }
   // row blocks cover every 32-bit half of D's words, so stale bits of a reused
   // destination are overwritten with zeros (rows >= nrows read as zero)
   dim3 grid(cdiv(sw32, 32), cdiv(dw32, 8));

@@ -123,6 +123,23 @@ def gpu_chunk_product(m4, tA, tB, tC, rows, k, n, algo=0):
     return product
 
 
+def exchange_slab(k, world, rank, src=0, align=1024, root_serves=False):
+    """k-slab of B that `rank` transposes and scatters in the fused exchange: (first row, rows).
+    Slab boundaries are multiples of `align` rows (whole 1024-row tiles of the wide transpose,
+    128-byte aligned column offsets in Bt).
+
+    Default: every rank takes one slab. root_serves=True (3 or more GPUs) makes the root only
+    serve its B while the other world-1 ranks share the work: the root's NVLink egress drops from
+    2(G-1)/G |B| to |B|, but the workers' own read + store traffic grows by G/(G-1) and they
+    become the bottleneck — measured equal at N = 4 (1.16 vs 1.21 ms,
+    profiles/r1k_exchange_probe_n4*.json), so the simpler plan is the default."""
+    if not root_serves or world < 3:
+        return row_block(k, world, rank, align)
+    if rank == src:
+        return 0, 0
+    return row_block(k, world - 1, rank - 1 if rank > src else rank, align)
+
+
 class FusedBroadcastMul:
     """The same sharded product with the exchange fused into the transpose (GPU only).
 
@@ -147,7 +164,7 @@ class FusedBroadcastMul:
         if k % 128 or n % 128:
             raise ValueError("k and n must be multiples of 128 bits")
         self.r0, self.rows = row_block(m, self.world, self.rank)
-        self.s0, self.srows = row_block(k, self.world, self.rank)  # this rank's k-slab of B
+        self.s0, self.srows = exchange_slab(k, self.world, self.rank, src)  # this rank's k-slab of B
         ws, kws = n // 64, k // 64
         dev = torch.device("cuda", torch.cuda.current_device())
         self.tB = symm_mem.empty((k, ws), dtype=torch.int64, device=dev)    # valid on src only

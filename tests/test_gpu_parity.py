@@ -197,6 +197,33 @@ def test_transpose_add_device_and_host(gpu, m4, orc):
         L.mzd_free(s2)
 
 
+@pytest.mark.parametrize("variant", ["narrow", "wide"])
+def test_transpose_kernels_and_scatter(gpu, m4, orc, monkeypatch, variant):
+    """Both transpose kernels (256 x 1024 tiles with 32-byte output segments, 1024 x 1024 tiles with
+    128-byte segments) on ragged shapes, a stale destination, and the multi-destination scatter
+    that the fused multi-GPU exchange uses (here: two buffers on one GPU)."""
+    import ctypes
+    L = m4.lib()
+    monkeypatch.setenv("M4RI_B200_TRANSPOSE", variant)
+    for (r, c) in [(1, 1), (65, 129), (300, 1000), (1000, 64), (1030, 2050), (2048, 4096), (5000, 1111),
+                   (1025, 8192), (4096, 130)]:
+        S = orc.random(r, c, 7)
+        want = orc.transpose(S, c)[:, : orc.width(r)]
+        s = host(m4, S, c)
+        dS = m4.DMat.from_host(s)
+        d1, d2 = m4.DMat.init(c, r).fill_random(9), m4.DMat.init(c, r).fill_random(10)  # stale contents
+        L.m4ri_b200_dtranspose(d1.h, dS.h)
+        w1 = d1.to_words()
+        assert (w1[:, : orc.width(r)] == want).all() and not w1[:, orc.width(r):].any(), (r, c)
+        d1.fill_random(11)
+        arr = (ctypes.c_void_p * 2)(d1.h, d2.h)
+        L.m4ri_b200_dtranspose_scatter(arr, 2, dS.h)
+        for d in (d1, d2):
+            w = d.to_words()
+            assert (w[:, : orc.width(r)] == want).all() and not w[:, orc.width(r):].any(), (r, c)
+        L.mzd_free(s)
+
+
 def test_matvec_shapes(gpu, m4, orc):
     L = m4.lib()
     for (m, n) in [(34, 128), (10, 10), (64, 1000), (1000, 64), (1, 1), (4097, 777), (300, 8192),

@@ -132,3 +132,19 @@ def test_k_chunks_ramp_and_sm_reservation(m4):
     sm.step()
     assert log == [("bcast", 8192), ("bcast", 24576), ("bcast", 32768),
                    ("reserve", 8), ("mul", 0, True), ("reserve", 8), ("mul", 1, False), ("reserve", 0), ("mul", 2, False)]
+
+
+def test_exchange_slabs_cover_k(m4):
+    """Slab plan of the fused exchange: disjoint, ordered, aligned, covering [0, k); from 3 ranks up
+    the root only serves reads."""
+    from m4ri_rust_b200 import sharded
+    for world in (1, 2, 3, 4, 8):
+        for src, serves in ((0, False), (0, True), (world - 1, True)):
+            for k in (1024, 65536, 70000, 5000, 100):
+                slabs = [sharded.exchange_slab(k, world, r, src, root_serves=serves) for r in range(world)]
+                if world >= 3 and serves:
+                    assert slabs[src] == (0, 0)
+                live = sorted(s for s in slabs if s[1] > 0)
+                assert live[0][0] == 0 and sum(s[1] for s in live) == k
+                assert all(a[0] + a[1] == b[0] for a, b in zip(live, live[1:]))
+                assert all(s[0] % 1024 == 0 for s in live)
