@@ -310,13 +310,16 @@ def main():
 
     for _ in range(args.warmup):
         step()
-    barrier()
-    L.m4ri_b200_timing_reset()
-    l0 = m4.launch_count()
+    # everything slow on the host (NVML init, event creation) happens BEFORE the barrier: the
+    # steps are coupled across ranks by device-side barriers, so host skew between the barrier
+    # and the first timed step would be charged to that step
     sampler = ClockSampler(local_rank)
     sampler.start()
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     e_all0, e_all1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    L.m4ri_b200_timing_reset()
+    l0 = m4.launch_count()
     e_all0.record(stream)
     for a, b in evs:
         if flush is not None:
