@@ -35,6 +35,7 @@ def lib():
             "oracle_checksum": (u64, [u64p, i, i, i]),
             "oracle_mul_naive": (None, [u64p, i, u64p, i, u64p, i, i, i, i, i]),
             "oracle_mul_m4rm": (None, [u64p, i, u64p, i, u64p, i, i, i, i, i, i]),
+            "oracle_mul_strassen": (None, [u64p, i, u64p, i, u64p, i, i, i, i, i, i, i]),
             "oracle_mul_abt": (None, [u64p, i, u64p, i, u64p, i, i, i, i, i]),
             "oracle_mul_va": (None, [u64p, i, u64p, i, u64p, i, i, i, i, i]),
             "oracle_mul_v": (None, [u64p, u64p, i, u64p, i, i, i]),
@@ -91,6 +92,17 @@ def mul_m4rm(A, B, k, n, C=None, threads=1):
     clear = C is None
     C = zeros(m, n) if C is None else C
     lib().oracle_mul_m4rm(_p(C), C.shape[1], _p(A), A.shape[1], _p(B), B.shape[1], m, k, n, int(clear), threads)
+    return C
+
+
+def mul_strassen(A, B, k, n, C=None, cutoff=0, threads=0):
+    """Strassen-Winograd above `cutoff` (0 = 2048) with Four-Russians leaves: the strategy behind
+    the reference's default mzd_mul (m4ri-sys/src/strassen.rs:5-18)."""
+    m = A.shape[0]
+    clear = C is None
+    C = zeros(m, n) if C is None else C
+    lib().oracle_mul_strassen(_p(C), C.shape[1], _p(A), A.shape[1], _p(B), B.shape[1], m, k, n, int(clear),
+                              int(cutoff), threads)
     return C
 
 

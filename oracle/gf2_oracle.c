@@ -175,6 +175,117 @@ void oracle_mul_m4rm(word *C, int cs, const word *A, int as, const word *B, int 
   }
 }
 
+/* ---- Strassen-Winograd above a cutoff, Four Russians at the leaves ------------
+ * What mzd_mul (the reference's default strategy, m4ri-rust/src/friendly/
+ * binary_matrix.rs:63-74 -> m4ri-sys/src/strassen.rs:5-18) is documented to do:
+ * "Strassen-Winograd ... cutoff: minimal dimension for Strassen recursion". Seven
+ * half-size products and fifteen half-size XORs per level (over GF(2) every
+ * subtraction is an XOR):
+ *   S1=A21+A22 S2=S1+A11 S3=A11+A21 S4=A12+S2   T1=B12+B11 T2=B22+T1 T3=B22+B12 T4=T2+B21
+ *   P1=A11*B11 P2=A12*B21 P3=S4*B22 P4=A22*T4 P5=S1*T1 P6=S2*T2 P7=S3*T3
+ *   C11=P1+P2  U2=P1+P6  U3=U2+P7  U4=U2+P5  C12=U4+P3  C21=U3+P4  C22=U3+P5
+ * Halves are multiples of 64 columns (whole words); what does not fit the even core
+ * (odd tails) is peeled off and multiplied by the Four-Russians routine. The seven
+ * products of a level are OpenMP tasks; leaves run single-threaded.               */
+static void xor_rows(word *D, int ds, const word *X, int xs, const word *Y, int ys, int rows, int words) {
+  for (int i = 0; i < rows; i++) {
+    word *d = D + (size_t)i * ds;
+    const word *x = X + (size_t)i * xs, *y = Y + (size_t)i * ys;
+    for (int w = 0; w < words; w++) d[w] = x[w] ^ y[w];
+  }
+}
+
+/* C = A*B, every dimension a multiple of 64; C is overwritten */
+static void strassen_rec(word *C, int cs, const word *A, int as, const word *B, int bs, int m, int k,
+                         int n, int cutoff) {
+  if (m < 2 * cutoff || k < 2 * cutoff || n < 2 * cutoff || (m % 128) || (k % 128) || (n % 128)) {
+    oracle_mul_m4rm(C, cs, A, as, B, bs, m, k, n, 1, 1);
+    return;
+  }
+  const int m2 = m / 2, k2 = k / 2, n2 = n / 2, kw = k2 / 64, nw = n2 / 64;
+  const word *A11 = A, *A12 = A + kw, *A21 = A + (size_t)m2 * as, *A22 = A21 + kw;
+  const word *B11 = B, *B12 = B + nw, *B21 = B + (size_t)k2 * bs, *B22 = B21 + nw;
+  word *C11 = C, *C12 = C + nw, *C21 = C + (size_t)m2 * cs, *C22 = C21 + nw;
+  word *S = malloc(sizeof(word) * 4 * (size_t)m2 * kw), *T = malloc(sizeof(word) * 4 * (size_t)k2 * nw),
+       *P = malloc(sizeof(word) * 5 * (size_t)m2 * nw);
+  if (!S || !T || !P) abort();
+  word *S1 = S, *S2 = S1 + (size_t)m2 * kw, *S3 = S2 + (size_t)m2 * kw, *S4 = S3 + (size_t)m2 * kw;
+  word *T1 = T, *T2 = T1 + (size_t)k2 * nw, *T3 = T2 + (size_t)k2 * nw, *T4 = T3 + (size_t)k2 * nw;
+  word *P3 = P, *P4 = P3 + (size_t)m2 * nw, *P5 = P4 + (size_t)m2 * nw, *P6 = P5 + (size_t)m2 * nw,
+       *P7 = P6 + (size_t)m2 * nw;
+  xor_rows(S1, kw, A21, as, A22, as, m2, kw);
+  xor_rows(S2, kw, S1, kw, A11, as, m2, kw);
+  xor_rows(S3, kw, A11, as, A21, as, m2, kw);
+  xor_rows(S4, kw, A12, as, S2, kw, m2, kw);
+  xor_rows(T1, nw, B12, bs, B11, bs, k2, nw);
+  xor_rows(T2, nw, B22, bs, T1, nw, k2, nw);
+  xor_rows(T3, nw, B22, bs, B12, bs, k2, nw);
+  xor_rows(T4, nw, T2, nw, B21, bs, k2, nw);
+  /* P1 -> C11, P2 -> C12 (scratch until C12 is assembled), the rest into P */
+#pragma omp task
+  strassen_rec(C11, cs, A11, as, B11, bs, m2, k2, n2, cutoff);
+#pragma omp task
+  strassen_rec(C12, cs, A12, as, B21, bs, m2, k2, n2, cutoff);
+#pragma omp task
+  strassen_rec(P3, nw, S4, kw, B22, bs, m2, k2, n2, cutoff);
+#pragma omp task
+  strassen_rec(P4, nw, A22, as, T4, nw, m2, k2, n2, cutoff);
+#pragma omp task
+  strassen_rec(P5, nw, S1, kw, T1, nw, m2, k2, n2, cutoff);
+#pragma omp task
+  strassen_rec(P6, nw, S2, kw, T2, nw, m2, k2, n2, cutoff);
+#pragma omp task
+  strassen_rec(P7, nw, S3, kw, T3, nw, m2, k2, n2, cutoff);
+#pragma omp taskwait
+  xor_rows(P6, nw, P6, nw, C11, cs, m2, nw);  /* U2 = P1 + P6 */
+  xor_rows(C11, cs, C11, cs, C12, cs, m2, nw); /* C11 = P1 + P2 */
+  xor_rows(P7, nw, P7, nw, P6, nw, m2, nw);   /* U3 = U2 + P7 */
+  xor_rows(P6, nw, P6, nw, P5, nw, m2, nw);   /* U4 = U2 + P5 */
+  xor_rows(C12, cs, P6, nw, P3, nw, m2, nw);  /* C12 = U4 + P3 */
+  xor_rows(C21, cs, P7, nw, P4, nw, m2, nw);  /* C21 = U3 + P4 */
+  xor_rows(C22, cs, P7, nw, P5, nw, m2, nw);  /* C22 = U3 + P5 */
+  free(S);
+  free(T);
+  free(P);
+}
+
+void oracle_mul_strassen(word *C, int cs, const word *A, int as, const word *B, int bs, int m, int k,
+                         int n, int clear, int cutoff, int nthreads) {
+  if (cutoff <= 0) cutoff = 2048; /* fastest leaf size measured on the build host (1024-4096 within 10 %) */
+  if (cutoff < 64) cutoff = 64;
+#ifdef _OPENMP
+  if (nthreads <= 0) nthreads = omp_get_max_threads();
+#else
+  nthreads = 1;
+#endif
+  /* even core: the largest multiples of 128 that fit; tails go to the Four Russians */
+  const int mc = m / 128 * 128, kc = k / 128 * 128, nc = n / 128 * 128;
+  if (mc < 2 * cutoff || kc < 2 * cutoff || nc < 2 * cutoff) {
+    oracle_mul_m4rm(C, cs, A, as, B, bs, m, k, n, clear, nthreads);
+    return;
+  }
+  const int ncw = nc / 64;
+  word *D = C;
+  int ds = cs;
+  if (!clear) { /* C ^= A*B: core product into a temporary, XORed in afterwards */
+    D = malloc(sizeof(word) * (size_t)mc * ncw);
+    if (!D) abort();
+    ds = ncw;
+  }
+#pragma omp parallel num_threads(nthreads)
+#pragma omp single
+  strassen_rec(D, ds, A, as, B, bs, mc, kc, nc, cutoff);
+  if (!clear) {
+    xor_rows(C, cs, C, cs, D, ds, mc, ncw);
+    free(D);
+  }
+  /* peel: k tail into the core block, then the column tail (all rows, all of k) and the
+   * row tail (core columns only); column windows start on whole words */
+  if (k > kc) oracle_mul_m4rm(C, cs, A + kc / 64, as, B + (size_t)kc * bs, bs, mc, k - kc, nc, 0, nthreads);
+  if (n > nc) oracle_mul_m4rm(C + ncw, cs, A, as, B + ncw, bs, m, k, n - nc, clear, nthreads);
+  if (m > mc) oracle_mul_m4rm(C + (size_t)mc * cs, cs, A + (size_t)mc * as, as, B, bs, m - mc, k, nc, clear, nthreads);
+}
+
 /* ---- C (^)= A * Bt^T, both operands k-contiguous (mzd.rs:154-168) ------------ */
 void oracle_mul_abt(word *C, int cs, const word *A, int as, const word *Bt, int bts, int m, int k,
                     int n, int clear) {

@@ -74,6 +74,7 @@ def test_golden_products(orc):
         assert (orc.mul_naive(A, B, k, n) == C).all()
         assert (orc.mul_m4rm(A, B, k, n) == C).all()
         assert (orc.mul_m4rm(A, B, k, n, threads=2) == C).all()
+        assert (orc.mul_strassen(A, B, k, n, cutoff=64, threads=2) == C).all()
         assert orc.checksum(C, n) == int(chk[2])
         Bt = orc.transpose(B, n)
         assert (orc.mul_abt(A, Bt, k) == C).all()
@@ -149,3 +150,24 @@ def test_medium_threaded(orc):
     C1 = orc.mul_m4rm(A, B, n, n, threads=1)
     C4 = orc.mul_m4rm(A, B, n, n, threads=4)
     assert (C1 == C4).all() and orc.freivalds(C1, A, B, n, n)
+
+
+@pytest.mark.parametrize("m,k,n,cutoff", [(256, 256, 256, 64), (300, 500, 260, 64), (257, 129, 131, 64),
+                                          (640, 384, 512, 64), (1000, 777, 1300, 128), (129, 128, 128, 64),
+                                          (1024, 1024, 1024, 256), (100, 100, 100, 64)])
+def test_strassen_strategy_matches_definition(orc, m, k, n, cutoff):
+    """The Strassen-Winograd strategy (the reference's default mzd_mul, strassen.rs:5-18) against
+    the definition: even cores of one and two levels, odd tails in every dimension (peeled to the
+    Four Russians), accumulate, excess bits."""
+    A, B = orc.random(m, k, 300 + m), orc.random(k, n, 400 + n)
+    want = orc.mul_naive(A, B, k, n) if m * k * n <= 300 * 500 * 260 else orc.mul_m4rm(A, B, k, n)
+    got = orc.mul_strassen(A, B, k, n, cutoff=cutoff, threads=3)
+    assert (got == want).all()
+    C0 = orc.random(m, n, 7)
+    C = C0.copy()
+    orc.mul_strassen(A, B, k, n, C=C, cutoff=cutoff, threads=2)
+    assert (C == (C0 ^ want)).all()
+    w = orc.width(n)
+    if n % 64:
+        assert not (got[:, w - 1] >> np.uint64(n % 64)).any()
+    assert not got[:, w:].any()
