@@ -18,7 +18,9 @@
  * the published Method of the Four Russians (oracle_mul_m4rm: Gray-code tables
  * of 2^8 row combinations per 8-row slab of B, one table lookup + XOR per row of
  * A; mechanism documented at m4ri-sys/src/brilliantrussian.rs:17-193) — and the
- * tests prove the two agree.
+ * tests prove the two agree. oracle_mul_strassen adds the strategy of the
+ * reference's default entry point (Strassen-Winograd above a cutoff, Four Russians
+ * at the leaves; m4ri-sys/src/strassen.rs:5-18), checked against both.
  *
  * Semantics followed (all file:line relative to /root/reference):
  *   bit order  (r,c) = (row[c/64] >> (c%64)) & 1      m4ri-sys/src/mzd.rs:263-269
