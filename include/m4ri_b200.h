@@ -103,7 +103,7 @@ mzd_t *mzd_mul_v(mzd_t *y, const mzd_t *A, const mzd_t *x);
 enum m4ri_b200_algo {
   M4RI_B200_ALGO_AUTO = 0,  /* library picks (shape based)                        */
   M4RI_B200_ALGO_M4RM = 1,  /* path (a): shared-memory Four-Russians, LOP3 gather  */
-  M4RI_B200_ALGO_MMA = 2,   /* path (b): bits -> int8, tcgen05 MMA, parity of i32  */
+  M4RI_B200_ALGO_MMA = 2,   /* path (b): tcgen05 MMA (FP4 default, int8 variants)  */
   M4RI_B200_ALGO_SIMPLE = 3 /* AND+popc row.row kernel (what *_naive maps to)      */
 };
 /* Force an algorithm for mzd_mul/mzd_addmul (AUTO restores the default). Also

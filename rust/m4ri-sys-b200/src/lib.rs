@@ -1,0 +1,148 @@
+//! `extern "C"` surface of `libm4ri_b200.so` for the multiplication path of m4ri-rust.
+//!
+//! The names, argument order and the 64-byte matrix descriptor are the ones `m4ri-sys`
+//! declares for the M4RI C library (`include/m4ri_b200.h` cites the `m4ri-sys` line next to
+//! every prototype), so `m4ri-rust`'s `BinMatrix`/`BinVector` operators run unchanged on top
+//! of this crate: `&a * &b` still expands to one `mzd_mul(NULL, a, b, 0)` call.
+//!
+//! SOURCE ONLY — never compiled in the build image (no `cargo`/`rustc` there).
+#![allow(non_camel_case_types, non_snake_case)]
+
+use libc::{c_char, c_double, c_int, c_uint, c_ulonglong, c_void, size_t};
+
+pub type Rci = c_int;
+pub type Wi = c_int;
+pub type Word = u64;
+
+/// One block of matrix words (pinned host memory in this implementation).
+#[repr(C)]
+pub struct MzdBlock {
+    pub size: size_t,
+    pub begin: *mut Word,
+    pub end: *mut Word,
+}
+
+/// The 64-byte descriptor. Offsets: nrows 0, ncols 4, width 8, rowstride 12, offset_vector 16,
+/// row_offset 20, flags 24, blockrows_log 25, padding 26..40, high_bitmask 40, blocks 48, rows 56.
+#[repr(C)]
+pub struct Mzd {
+    pub nrows: Rci,
+    pub ncols: Rci,
+    pub width: Wi,
+    pub rowstride: Wi,
+    pub offset_vector: Wi,
+    pub row_offset: Wi,
+    pub flags: u8,
+    pub blockrows_log: u8,
+    pub padding: [u8; 14],
+    pub high_bitmask: Word,
+    pub blocks: *mut MzdBlock,
+    pub rows: *mut *mut Word,
+}
+
+/// Opaque device-resident matrix (same packing, even row stride, lives in HBM).
+#[repr(C)]
+pub struct DMat {
+    _private: [u8; 0],
+}
+
+pub const ALGO_AUTO: c_int = 0;
+pub const ALGO_M4RM: c_int = 1;
+pub const ALGO_MMA: c_int = 2;
+pub const ALGO_SIMPLE: c_int = 3;
+
+extern "C" {
+    // ---- allocator set: one allocator owns every matrix the path touches ----
+    pub fn mzd_init(r: Rci, c: Rci) -> *mut Mzd;
+    pub fn mzd_free(a: *mut Mzd);
+    pub fn mzd_init_window(m: *mut Mzd, lowr: Rci, lowc: Rci, highr: Rci, highc: Rci) -> *mut Mzd;
+    pub fn mzd_copy(dst: *mut Mzd, a: *const Mzd) -> *mut Mzd;
+    pub fn mzd_equal(a: *const Mzd, b: *const Mzd) -> c_int;
+    pub fn mzd_set_ui(a: *mut Mzd, value: c_uint);
+    pub fn mzd_randomize(a: *mut Mzd);
+    pub fn mzd_transpose(dst: *mut Mzd, a: *const Mzd) -> *mut Mzd;
+    pub fn mzd_add(c: *mut Mzd, a: *const Mzd, b: *const Mzd) -> *mut Mzd;
+    pub fn mzd_sub(c: *mut Mzd, a: *const Mzd, b: *const Mzd) -> *mut Mzd;
+
+    // ---- products (C == NULL: the library allocates, the caller frees with mzd_free) ----
+    pub fn mzd_mul(c: *mut Mzd, a: *const Mzd, b: *const Mzd, cutoff: c_int) -> *mut Mzd;
+    pub fn mzd_addmul(c: *mut Mzd, a: *const Mzd, b: *const Mzd, cutoff: c_int) -> *mut Mzd;
+    pub fn mzd_mul_m4rm(c: *mut Mzd, a: *const Mzd, b: *const Mzd, k: c_int) -> *mut Mzd;
+    pub fn mzd_addmul_m4rm(c: *mut Mzd, a: *const Mzd, b: *const Mzd, k: c_int) -> *mut Mzd;
+    pub fn _mzd_mul_m4rm(c: *mut Mzd, a: *const Mzd, b: *const Mzd, k: c_int, clear: c_int) -> *mut Mzd;
+    pub fn mzd_mul_naive(c: *mut Mzd, a: *const Mzd, b: *const Mzd) -> *mut Mzd;
+    pub fn mzd_addmul_naive(c: *mut Mzd, a: *const Mzd, b: *const Mzd) -> *mut Mzd;
+    pub fn _mzd_mul_naive(c: *mut Mzd, a: *const Mzd, bt: *const Mzd, clear: c_int) -> *mut Mzd;
+    pub fn _mzd_mul_va(c: *mut Mzd, v: *const Mzd, a: *const Mzd, clear: c_int) -> *mut Mzd;
+    /// y = A*x with x (ncols x 1) and y (nrows x 1): the shape `BinMatrix::mul_slice` builds.
+    pub fn mzd_mul_v(y: *mut Mzd, a: *const Mzd, x: *const Mzd) -> *mut Mzd;
+
+    // ---- engine control ----
+    pub fn m4ri_b200_set_algo(algo: c_int);
+    pub fn m4ri_b200_get_algo() -> c_int;
+    pub fn m4ri_b200_set_strassen_levels(levels: c_int);
+    pub fn m4ri_b200_device_count() -> c_int;
+    pub fn m4ri_b200_device_info(name: *mut c_char, name_len: c_int, sm_count: *mut c_int,
+                                 cc_major: *mut c_int, cc_minor: *mut c_int) -> c_int;
+    pub fn m4ri_b200_set_stream(stream: *mut c_void);
+    pub fn m4ri_b200_synchronize();
+    pub fn m4ri_b200_launch_count() -> c_ulonglong;
+    pub fn m4ri_b200_version() -> *const c_char;
+    pub fn m4ri_b200_pipeline_plan(m: c_int, k: c_int, n: c_int, clear: c_int,
+                                   row_chunks: *mut c_int, col_blocks: *mut c_int);
+
+    // ---- device-resident matrices: chained products without the PCIe round trip ----
+    pub fn m4ri_b200_dmat_init(nrows: Rci, ncols: Rci) -> *mut DMat;
+    pub fn m4ri_b200_dmat_wrap(dptr: *mut c_void, nrows: Rci, ncols: Rci, rowstride: Wi) -> *mut DMat;
+    pub fn m4ri_b200_dmat_free(m: *mut DMat);
+    pub fn m4ri_b200_dmat_nrows(m: *const DMat) -> Rci;
+    pub fn m4ri_b200_dmat_ncols(m: *const DMat) -> Rci;
+    pub fn m4ri_b200_dmat_rowstride(m: *const DMat) -> Wi;
+    pub fn m4ri_b200_dmat_ptr(m: *const DMat) -> *mut c_void;
+    pub fn m4ri_b200_upload(d: *mut DMat, h: *const Mzd);
+    pub fn m4ri_b200_download(h: *mut Mzd, d: *const DMat);
+    pub fn m4ri_b200_dmul(c: *mut DMat, a: *const DMat, b: *const DMat, clear: c_int, algo: c_int);
+    pub fn m4ri_b200_dmul_abt(c: *mut DMat, a: *const DMat, bt: *const DMat, clear: c_int, algo: c_int);
+    pub fn m4ri_b200_dmul_v(y: *mut DMat, a: *const DMat, x: *const DMat, clear: c_int);
+    pub fn m4ri_b200_dmul_va(c: *mut DMat, v: *const DMat, a: *const DMat, clear: c_int);
+    pub fn m4ri_b200_dtranspose(dst: *mut DMat, a: *const DMat);
+    pub fn m4ri_b200_dadd(c: *mut DMat, a: *const DMat, b: *const DMat);
+    pub fn m4ri_b200_dcopy(dst: *mut DMat, a: *const DMat);
+    pub fn m4ri_b200_dchecksum(m: *const DMat) -> u64;
+    pub fn m4ri_b200_timing_ms() -> c_double;
+}
+
+/// Bit (row, col) of a host matrix: bit `col % 64` of word `col / 64` of `rows[row]`, LSB first.
+///
+/// # Safety
+/// `m` must come from this library and `row`/`col` must be in range.
+#[inline]
+pub unsafe fn mzd_read_bit(m: *const Mzd, row: Rci, col: Rci) -> c_int {
+    let words = *(*m).rows.offset(row as isize);
+    ((*words.offset((col / 64) as isize) >> (col % 64)) & 1) as c_int
+}
+
+#[cfg(test)]
+mod tests {
+    use super::*;
+    use std::mem::size_of;
+    use std::ptr;
+
+    #[test]
+    fn descriptor_is_64_bytes() {
+        assert_eq!(size_of::<Mzd>(), 64);
+    }
+
+    #[test]
+    fn identity_times_identity() {
+        unsafe {
+            let a = mzd_init(8, 8);
+            mzd_set_ui(a, 1);
+            let c = mzd_mul(ptr::null_mut(), a, a, 0);
+            assert!(!c.is_null());
+            assert_eq!(mzd_equal(a, c), 1);
+            mzd_free(c);
+            mzd_free(a);
+        }
+    }
+}
