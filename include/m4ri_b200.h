@@ -141,6 +141,12 @@ int m4ri_b200_device_count(void);
 int m4ri_b200_device_info(char *name, int name_len, int *sm_count, int *cc_major, int *cc_minor);
 /* Use `stream` (a cudaStream_t) for all device-API work issued by this thread;
  * NULL selects the library's own stream. */
+/* mzd_free keeps blocks of 256 KiB or more (pinned host memory is expensive to allocate) for the
+ * next mzd_init of about the same size, up to M4RI_B200_HOST_CACHE_MB (default 4096) in total.
+ * trim returns them to the system; stats reports hits, misses and the bytes currently held. */
+void m4ri_b200_host_cache_trim(void);
+void m4ri_b200_host_cache_stats(unsigned long long *hits, unsigned long long *misses,
+                                unsigned long long *bytes_held);
 void m4ri_b200_set_stream(void *stream);
 void m4ri_b200_synchronize(void);
 /* Count of kernels the library launched since process start (bench: gpu_launches). */

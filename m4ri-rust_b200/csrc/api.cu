@@ -581,7 +581,7 @@ static mzd_t *host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int clear, 
   if (k != kb) die("m4ri_b200: %s: A ncols (%d) need to match B nrows (%d)\n", who, k, kb);
   if (!C) {
     if (!clear) die("m4ri_b200: %s: C must not be NULL when accumulating\n", who);
-    C = mzd_init(m, n);
+    C = mzd_init_impl(m, n, 0);  // every valid word is downloaded over
   } else if (C->nrows != m || C->ncols != n) {
     die("m4ri_b200: %s: C (%d x %d) has wrong dimensions, expected (%d x %d)\n", who, C->nrows,
         C->ncols, m, n);
@@ -658,7 +658,7 @@ mzd_t *mzd_mul_v(mzd_t *y, const mzd_t *A, const mzd_t *x) {
   rci_t m = A->nrows, n = A->ncols;
   if (x->nrows != n || x->ncols != 1)
     die("m4ri_b200: mzd_mul_v: x must be %d x 1 (got %d x %d)\n", n, x->nrows, x->ncols);
-  if (!y) y = mzd_init(m, 1);
+  if (!y) y = mzd_init_impl(m, 1, 0);
   else if (y->nrows != m || y->ncols != 1)
     die("m4ri_b200: mzd_mul_v: y must be %d x 1\n", m);
   cudaStream_t s = current_stream();
@@ -685,7 +685,7 @@ mzd_t *mzd_mul_v(mzd_t *y, const mzd_t *A, const mzd_t *x) {
 mzd_t *mzd_add(mzd_t *C, const mzd_t *A, const mzd_t *B) {
   if (A->nrows != B->nrows || A->ncols != B->ncols)
     die("m4ri_b200: mzd_add: rows and columns must match\n");
-  if (!C) C = mzd_init(A->nrows, A->ncols);
+  if (!C) C = mzd_init_impl(A->nrows, A->ncols, 0);
   else if (C->nrows != A->nrows || C->ncols != A->ncols)
     die("m4ri_b200: mzd_add: rows and columns of returned matrix must match\n");
   if (A->nrows == 0 || A->width == 0) return C;
@@ -705,7 +705,7 @@ mzd_t *mzd_sub(mzd_t *C, const mzd_t *A, const mzd_t *B) { return mzd_add(C, A, 
 // DST = A^T on the GPU (reference mzd_transpose mzd.rs:148; on the mat-vec path
 // twice per call, binary_matrix.rs:272-279,335,426).
 mzd_t *mzd_transpose(mzd_t *DST, const mzd_t *A) {
-  if (!DST) DST = mzd_init(A->ncols, A->nrows);
+  if (!DST) DST = mzd_init_impl(A->ncols, A->nrows, 0);
   else if (DST->nrows != A->ncols || DST->ncols != A->nrows)
     die("m4ri_b200: mzd_transpose: wrong size for return matrix\n");
   if (DST == A) die("m4ri_b200: mzd_transpose: in-place transpose is not supported\n");

@@ -39,6 +39,9 @@ bool has_tcgen05();  // compute capability 10.x
 
 // Event pair around the dominant product kernel (api.cu; no-ops until enabled).
 // `ops` = the 2*m*n*k bit-operations of this launch (summed for the roofline).
+// mzd_init without the O(size) zeroing for results whose every valid word is about to be
+// downloaded over (mzd_host.cpp)
+mzd_t *mzd_init_impl(rci_t r, rci_t c, int zero);
 void timing_begin(const char *kernel_name, cudaStream_t s, double ops);
 void timing_end(cudaStream_t s);
 

@@ -15,6 +15,7 @@
 
 #include <atomic>
 #include <mutex>
+#include <vector>
 
 #include "common.cuh"
 
@@ -30,13 +31,98 @@ enum : uint8_t { ALLOC_NONE = 0, ALLOC_MALLOC = 0xA1, ALLOC_PINNED = 0xA2 };
 // product run at full PCIe rate; small ones (the reference's tests create
 // thousands of 10x10 matrices) stay in ordinary memory.
 constexpr size_t PINNED_MIN_BYTES = 256 * 1024;
+
+// ---- cache of freed blocks ---------------------------------------------------------
+// m4ri-rust allocates the result of every product (`mzd_mul(NULL, a, b, 0)`,
+// binary_matrix.rs:465) and frees it on drop: for a 128 MiB result cudaHostAlloc + cudaFreeHost
+// cost several times the product itself. Freed blocks of PINNED_MIN_BYTES or more are kept
+// (up to M4RI_B200_HOST_CACHE_MB, default 4096) and handed out again to requests of the same
+// or a slightly smaller size. Applies to both kinds of block so that the logic is exercised on
+// a CPU-only box as well.
+struct CachedBlock {
+  word *p;
+  size_t cap;
+  uint8_t kind;
+};
+static std::mutex g_cache_mu;
+static std::vector<CachedBlock> g_cache;
+static size_t g_cache_bytes = 0;
+static std::atomic<unsigned long long> g_cache_hits{0}, g_cache_misses{0};
+
+static size_t cache_limit() {
+  static const size_t lim = [] {
+    const char *e = getenv("M4RI_B200_HOST_CACHE_MB");
+    long long mb = e ? atoll(e) : 4096;
+    return (size_t)(mb < 0 ? 0 : mb) << 20;
+  }();
+  return lim;
+}
+
+static void release_block(word *p, uint8_t kind) {
+  if (kind == ALLOC_PINNED) cudaFreeHost(p);
+  else free(p);
+}
+
+// smallest cached block of `kind` with bytes <= cap <= bytes * 5/4, or nullptr
+static word *cache_take(size_t bytes, uint8_t kind, size_t *cap) {
+  std::lock_guard<std::mutex> g(g_cache_mu);
+  int best = -1;
+  for (int i = 0; i < (int)g_cache.size(); i++) {
+    const CachedBlock &b = g_cache[i];
+    if (b.kind == kind && b.cap >= bytes && b.cap <= bytes + bytes / 4 &&
+        (best < 0 || b.cap < g_cache[best].cap))
+      best = i;
+  }
+  if (best < 0) return nullptr;
+  word *p = g_cache[best].p;
+  *cap = g_cache[best].cap;
+  g_cache_bytes -= g_cache[best].cap;
+  g_cache[best] = g_cache.back();
+  g_cache.pop_back();
+  return p;
+}
+
+static bool cache_put(word *p, size_t cap, uint8_t kind) {
+  if (cap < PINNED_MIN_BYTES) return false;
+  std::lock_guard<std::mutex> g(g_cache_mu);
+  if (g_cache_bytes + cap > cache_limit()) return false;
+  g_cache.push_back({p, cap, kind});
+  g_cache_bytes += cap;
+  return true;
+}
+
+// zero == 0: the caller overwrites every valid word (a product's result); only the padding
+// word of each row (rowstride > width) is cleared.
+mzd_t *mzd_init_impl(rci_t r, rci_t c, int zero);
 }  // namespace m4b
 
 using namespace m4b;
 
 extern "C" {
 
-mzd_t *mzd_init(rci_t r, rci_t c) {
+mzd_t *mzd_init(rci_t r, rci_t c) { return m4b::mzd_init_impl(r, c, 1); }
+
+void m4ri_b200_host_cache_trim(void) {
+  std::vector<CachedBlock> drop;
+  {
+    std::lock_guard<std::mutex> g(g_cache_mu);
+    drop.swap(g_cache);
+    g_cache_bytes = 0;
+  }
+  for (auto &b : drop) release_block(b.p, b.kind);
+}
+
+void m4ri_b200_host_cache_stats(unsigned long long *hits, unsigned long long *misses,
+                                unsigned long long *bytes_held) {
+  if (hits) *hits = g_cache_hits.load();
+  if (misses) *misses = g_cache_misses.load();
+  std::lock_guard<std::mutex> g(g_cache_mu);
+  if (bytes_held) *bytes_held = g_cache_bytes;
+}
+
+}  // extern "C"
+
+mzd_t *m4b::mzd_init_impl(rci_t r, rci_t c, int zero) {
   if (r < 0 || c < 0) die("m4ri_b200: mzd_init(%d, %d): negative dimension\n", r, c);
   mzd_t *A = (mzd_t *)calloc(1, sizeof(mzd_t));
   if (!A) die("m4ri_b200: out of memory\n");
@@ -59,22 +145,38 @@ mzd_t *mzd_init(rci_t r, rci_t c) {
   if (!A->blocks || !A->rows) die("m4ri_b200: out of memory\n");
   word *data = nullptr;
   uint8_t kind = ALLOC_MALLOC;
-  if (bytes >= PINNED_MIN_BYTES && m4ri_b200_device_count() > 0) {
-    if (cudaHostAlloc((void **)&data, bytes, cudaHostAllocPortable) == cudaSuccess) {
+  size_t cap = bytes ? ((bytes + 63) & ~(size_t)63) : 64;  // capacity of the block actually held
+  bool fresh = true;
+  const bool big = bytes >= PINNED_MIN_BYTES;
+  if (big && m4ri_b200_device_count() > 0) {
+    size_t got = 0;
+    if ((data = cache_take(bytes, ALLOC_PINNED, &got))) {
+      kind = ALLOC_PINNED, cap = got, fresh = false;
+    } else if (cudaHostAlloc((void **)&data, cap, cudaHostAllocPortable) == cudaSuccess) {
       kind = ALLOC_PINNED;
-      memset(data, 0, bytes);
     } else {
       (void)cudaGetLastError();
       data = nullptr;
     }
   }
   if (!data) {
-    size_t alloc = bytes ? ((bytes + 63) & ~(size_t)63) : 64;
-    data = (word *)aligned_alloc(64, alloc);
-    if (!data) die("m4ri_b200: out of memory (%zu bytes)\n", bytes);
-    memset(data, 0, alloc);
+    size_t got = 0;
+    if (big && (data = cache_take(bytes, ALLOC_MALLOC, &got))) {
+      cap = got, fresh = false;
+    } else {
+      data = (word *)aligned_alloc(64, cap);
+      if (!data) die("m4ri_b200: out of memory (%zu bytes)\n", bytes);
+    }
+  }
+  if (big) (fresh ? g_cache_misses : g_cache_hits).fetch_add(1);
+  if (zero) {
+    memset(data, 0, bytes ? bytes : cap);
+  } else if (A->rowstride > A->width) {
+    for (rci_t i = 0; i < r; i++) data[(size_t)i * A->rowstride + A->width] = 0;
   }
   A->padding[0] = kind;
+  // capacity of the block (>= the bytes in use) in padding[1..8]: mzd_free returns it to the cache
+  memcpy(&A->padding[1], &cap, sizeof(cap));
   A->blocks[0].size = bytes;
   A->blocks[0].begin = data;
   A->blocks[0].end = data + words;
@@ -82,11 +184,14 @@ mzd_t *mzd_init(rci_t r, rci_t c) {
   return A;
 }
 
+extern "C" {
+
 void mzd_free(mzd_t *A) {
   if (!A) return;
   if (A->blocks && A->padding[0] != ALLOC_NONE) {
-    if (A->padding[0] == ALLOC_PINNED) cudaFreeHost(A->blocks[0].begin);
-    else free(A->blocks[0].begin);
+    size_t cap = 0;
+    memcpy(&cap, &A->padding[1], sizeof(cap));
+    if (!cache_put(A->blocks[0].begin, cap, A->padding[0])) release_block(A->blocks[0].begin, A->padding[0]);
     free(A->blocks);
   }
   free(A->rows);

@@ -147,3 +147,46 @@ def test_pipeline_plan_is_host_arithmetic():
         assert 1 <= a <= 16 and 1 <= b <= 16
         a, b = plan(*shape, clear=0)
         assert 1 <= a <= 16 and 1 <= b <= 16
+
+
+def test_host_block_cache_reuses_and_zeroes():
+    """mzd_free keeps big blocks for the next mzd_init of about the same size (m4ri-rust allocates
+    and drops a result per product): the block comes back zeroed, a slightly smaller request
+    takes it too, a much smaller one does not, and trim empties the cache."""
+    import ctypes
+    import numpy as np
+    import m4ri_rust_b200 as m4
+    L = m4.lib()
+    def stats():
+        h, m_, b = ctypes.c_ulonglong(), ctypes.c_ulonglong(), ctypes.c_ulonglong()
+        L.m4ri_b200_host_cache_stats(ctypes.byref(h), ctypes.byref(m_), ctypes.byref(b))
+        return h.value, m_.value, b.value
+    L.m4ri_b200_host_cache_trim()
+    h0, m0, b0 = stats()
+    assert b0 == 0
+    a = L.mzd_init(2048, 4096)  # 1 MiB
+    first = a.contents.blocks[0].begin
+    addr = ctypes.cast(first, ctypes.c_void_p).value
+    L.mzd_randomize(a)
+    assert m4.mzd_words(a).any()
+    L.mzd_free(a)
+    assert stats()[2] == 2048 * 64 * 8
+    b = L.mzd_init(2048, 4096)
+    assert ctypes.cast(b.contents.blocks[0].begin, ctypes.c_void_p).value == addr
+    assert not m4.mzd_words(b).any(), "a recycled block must come back zeroed"
+    assert stats()[0] == h0 + 1 and stats()[2] == 0
+    L.mzd_free(b)
+    c = L.mzd_init(2000, 4096)  # 2.3 % smaller: same block
+    assert ctypes.cast(c.contents.blocks[0].begin, ctypes.c_void_p).value == addr
+    assert c.contents.blocks[0].size == 2000 * 64 * 8 and not m4.mzd_words(c).any()
+    L.mzd_free(c)
+    d = L.mzd_init(1024, 4096)  # half the size: a block of its own
+    assert ctypes.cast(d.contents.blocks[0].begin, ctypes.c_void_p).value != addr
+    L.mzd_free(d)
+    assert stats()[2] == (2048 + 1024) * 64 * 8
+    L.m4ri_b200_host_cache_trim()
+    assert stats()[2] == 0
+    # small matrices never enter the cache
+    e = L.mzd_init(10, 10)
+    L.mzd_free(e)
+    assert stats()[2] == 0
