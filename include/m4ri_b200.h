@@ -117,6 +117,13 @@ void m4ri_b200_set_strassen_levels(int levels);
  * product (the NCCL broadcast of the next k-chunk of B, sharded.py) needs a few SMs of its own:
  * sms > 0 caps the SMs the product kernels launched after this call use (0 = all). */
 void m4ri_b200_set_sm_limit(int sms);
+/* GPUs one host-ABI product may use (default 1; also M4RI_B200_DEVICES). With n > 1 a large
+ * mzd_mul/mzd_addmul/_mzd_mul_naive on host operands is cut into n row-blocks of A and C, one per
+ * GPU of this process (devices 0..n-1), each running the copy/compute pipeline on its block over
+ * its own PCIe link; the blocks are independent (no collective). get returns the effective count
+ * (clamped to the devices present). */
+void m4ri_b200_set_devices(int n);
+int m4ri_b200_get_devices(void);
 /* Block plan the host-ABI products use to overlap PCIe copies with the kernels on an
  * m x k x n product: row-chunks of A and column blocks of B (pure host arithmetic, no device
  * needed; M4RI_B200_PIPE_ROWS / M4RI_B200_PIPE_COLS override it). */

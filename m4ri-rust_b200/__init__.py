@@ -99,7 +99,7 @@ def lib():
         "m4ri_b200_dis_zero": (i, [vp]), "m4ri_b200_dflip_bit": (None, [vp, i, i]),
         "m4ri_b200_algo_available": (i, [i]),
         "m4ri_b200_dfill_random_at": (None, [vp, u64, u64]),
-        "m4ri_b200_set_sm_limit": (None, [i]), "m4ri_b200_host_cache_trim": (None, []), "m4ri_b200_host_cache_stats": (None, [ctypes.POINTER(ctypes.c_ulonglong)] * 3), "m4ri_b200_pipeline_plan": (None, [i, i, i, i, ctypes.POINTER(i), ctypes.POINTER(i)]), "m4ri_b200_dtranspose_scatter": (None, [ctypes.POINTER(vp), i, vp]), "m4ri_b200_timing_reset": (None, []), "m4ri_b200_timing_ms": (ctypes.c_double, []),
+        "m4ri_b200_set_sm_limit": (None, [i]), "m4ri_b200_set_devices": (None, [i]), "m4ri_b200_get_devices": (i, []), "m4ri_b200_host_cache_trim": (None, []), "m4ri_b200_host_cache_stats": (None, [ctypes.POINTER(ctypes.c_ulonglong)] * 3), "m4ri_b200_pipeline_plan": (None, [i, i, i, i, ctypes.POINTER(i), ctypes.POINTER(i)]), "m4ri_b200_dtranspose_scatter": (None, [ctypes.POINTER(vp), i, vp]), "m4ri_b200_timing_reset": (None, []), "m4ri_b200_timing_ms": (ctypes.c_double, []),
         "m4ri_b200_timing_count": (i, []), "m4ri_b200_timing_ops": (ctypes.c_double, []), "m4ri_b200_timing_name": (ctypes.c_char_p, []),
     }
     for name, (res, args) in sig.items():

@@ -8,7 +8,10 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <condition_variable>
+#include <functional>
 #include <mutex>
+#include <thread>
 #include <utility>
 #include <vector>
 
@@ -572,6 +575,91 @@ static void pipelined_host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int
   for (auto &e : ev) M4B_CUDA(cudaEventDestroy(e));
 }
 
+// ---- several GPUs behind one host-ABI call ("single process ... what a library
+// behind a C ABI should do; no launcher") ---------------------------------------------------
+// m4ri_b200_set_devices(G) / M4RI_B200_DEVICES=G: a large host product is cut into G row-blocks
+// of A and C; a resident worker thread per GPU runs the copy/compute pipeline above on its
+// block — its rows of A, all of B, over its own PCIe link — and writes its rows of C. No
+// collective and no peer access: the blocks are independent. One multi-GPU call at a time.
+static std::atomic<int> g_devices{-1};  // -1: not decided yet (environment)
+
+static int multi_devices() {
+  int g = g_devices.load();
+  if (g < 0) {
+    const char *e = getenv("M4RI_B200_DEVICES");
+    g = e ? atoi(e) : 1;
+    if (g < 1) g = 1;
+    g_devices.store(g);
+  }
+  std::call_once(g_once, probe);
+  return g < g_ndev ? g : (g_ndev > 0 ? g_ndev : 1);
+}
+
+struct DeviceWorker {
+  std::thread th;
+  std::mutex mu;
+  std::condition_variable cv;
+  std::function<void()> job;
+  bool pending = false;
+  int dev = 0;
+  void loop() {
+    M4B_CUDA(cudaSetDevice(dev));
+    std::unique_lock<std::mutex> lk(mu);
+    for (;;) {
+      cv.wait(lk, [&] { return pending; });
+      std::function<void()> j = std::move(job);
+      lk.unlock();
+      j();  // dies loudly on any CUDA error, like every other entry point
+      lk.lock();
+      pending = false;
+      cv.notify_all();
+    }
+  }
+};
+static std::mutex g_workers_mu;  // also serialises multi-GPU calls
+static std::vector<DeviceWorker *> g_workers;
+
+static void multi_device_host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int clear, int form, int G) {
+  std::lock_guard<std::mutex> g(g_workers_mu);
+  while ((int)g_workers.size() < G) {  // workers live for the rest of the process
+    DeviceWorker *w = new DeviceWorker;
+    w->dev = (int)g_workers.size();
+    w->th = std::thread([w] { w->loop(); });
+    w->th.detach();
+    g_workers.push_back(w);
+  }
+  const rci_t m = A->nrows;
+  const rci_t per = ((m + G - 1) / G + 255) / 256 * 256;
+  // shallow views of the callers' matrices: rows [r0, r1) through the same rows[] array
+  std::vector<mzd_t> Av(G), Cv(G);
+  int used = 0;
+  for (int i = 0; i < G; i++) {
+    const rci_t r0 = (rci_t)i * per, r1 = r0 + per < m ? r0 + per : m;
+    if (r0 >= m) break;
+    Av[i] = *A;
+    Av[i].nrows = r1 - r0;
+    Av[i].rows = A->rows + r0;
+    Cv[i] = *C;
+    Cv[i].nrows = r1 - r0;
+    Cv[i].rows = C->rows + r0;
+    DeviceWorker *w = g_workers[i];
+    mzd_t *Ci = &Cv[i];
+    const mzd_t *Ai = &Av[i];
+    {
+      std::lock_guard<std::mutex> lk(w->mu);
+      w->job = [=] { pipelined_host_product(Ci, Ai, B, clear, form, current_stream()); };
+      w->pending = true;
+    }
+    w->cv.notify_all();
+    used++;
+  }
+  for (int i = 0; i < used; i++) {
+    DeviceWorker *w = g_workers[i];
+    std::unique_lock<std::mutex> lk(w->mu);
+    w->cv.wait(lk, [&] { return !w->pending; });
+  }
+}
+
 // Shared body of the host-ABI products. form: 0 = A*B, 1 = A*Bt^T, 2 = v*A.
 static mzd_t *host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int clear, int algo, int form,
                            const char *who, int cutoff = 0) {
@@ -589,11 +677,17 @@ static mzd_t *host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int clear, 
   if (C == A || C == B) die("m4ri_b200: %s: C must not alias an input\n", who);
   cudaStream_t s = current_stream();
   if (form != 2 && m > 0 && n > 0 && k > 0 && resolve_algo(algo, m, k, n) == M4RI_B200_ALGO_MMA &&
-      ((size_t)m * A->width + (size_t)B->nrows * B->width) * 8 >= PIPELINE_MIN_BYTES &&
-      strassen_levels(m, k, n, M4RI_B200_ALGO_MMA, cutoff) <= 1) {
-    // (deeper recursions only pay beyond n = 65536, where the 7/8 per level outweighs the copies)
-    pipelined_host_product(C, A, B, clear, form, s);
-    return C;
+      ((size_t)m * A->width + (size_t)B->nrows * B->width) * 8 >= PIPELINE_MIN_BYTES) {
+    const int G = multi_devices();
+    if (G > 1 && m >= 512) {  // row-blocks of A and C over the GPUs of this process
+      multi_device_host_product(C, A, B, clear, form, G);
+      return C;
+    }
+    if (strassen_levels(m, k, n, M4RI_B200_ALGO_MMA, cutoff) <= 1) {
+      // (deeper recursions only pay beyond n = 65536, where the 7/8 per level outweighs the copies)
+      pipelined_host_product(C, A, B, clear, form, s);
+      return C;
+    }
   }
   DMat *dA = dmat_new(A->nrows, A->ncols, s), *dB = dmat_new(B->nrows, B->ncols, s),
        *dC = dmat_new(m, n, s);
@@ -735,6 +829,8 @@ void m4ri_b200_set_strassen_levels(int levels) { g_strassen.store(levels); }
 void m4ri_b200_pipeline_plan(int m, int k, int n, int clear, int *row_chunks, int *col_blocks) {
   plan_pipeline(m, k, n, clear, row_chunks, col_blocks);
 }
+void m4ri_b200_set_devices(int n) { g_devices.store(n < 1 ? 1 : n); }
+int m4ri_b200_get_devices(void) { return multi_devices(); }
 void m4ri_b200_set_sm_limit(int sms) { g_sm_limit.store(sms < 0 ? 0 : (sms & ~1)); }
 void m4ri_b200_set_mma_variant(int variant) {
   if (variant < 0 || variant > 7) die("m4ri_b200: unknown MMA variant %d\n", variant);

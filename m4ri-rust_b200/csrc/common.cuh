@@ -37,6 +37,15 @@ void require_device();
 int sm_count();
 bool has_tcgen05();  // compute capability 10.x
 
+// Function attributes (opt-in dynamic shared memory) are per device: true the first time the
+// calling site is reached with this device current (a process may drive several GPUs).
+static inline bool first_use_on_this_device(std::atomic<unsigned long long> &seen) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return true;
+  const unsigned long long bit = 1ull << dev;
+  return !(seen.fetch_or(bit) & bit);
+}
+
 // Event pair around the dominant product kernel (api.cu; no-ops until enabled).
 // `ops` = the 2*m*n*k bit-operations of this launch (summed for the roofline).
 // mzd_init without the O(size) zeroing for results whose every valid word is about to be

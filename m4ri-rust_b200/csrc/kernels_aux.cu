@@ -239,10 +239,9 @@ static bool transpose_wide_ok(const uint32_t *const *dst, int ndst, int ds32) {
 }
 
 static void launch_transpose_wide(const TransposeDsts &dsts, const DMat *A, int ds32, int dw32, cudaStream_t s) {
-  static std::once_flag once;
-  std::call_once(once, [] {
+  static std::atomic<unsigned long long> attr_seen{0};
+  if (first_use_on_this_device(attr_seen))
     M4B_CUDA(cudaFuncSetAttribute(transpose_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TW_SMEM));
-  });
   const int sw32 = A->width * 2;
   dim3 grid(cdiv(sw32, 32), cdiv(dw32, 32));
   transpose_wide_kernel<<<grid, 512, TW_SMEM, s>>>(dsts, (const uint32_t *)A->d, A->nrows, A->ncols, sw32,

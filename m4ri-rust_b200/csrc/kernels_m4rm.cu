@@ -199,11 +199,10 @@ void k_mul_m4rm(DMat *C, const DMat *A, const DMat *B, int clear, cudaStream_t s
   }
   if (((uintptr_t)C->d & 15) || (C->rowstride & 1) || ((uintptr_t)A->d & 15) || (A->rowstride & 1))
     die("m4ri_b200: m4rm kernel needs 16-byte aligned rows of A and C\n");
-  static bool attr_set = false;
-  if (!attr_set) {
+  static std::atomic<unsigned long long> attr_seen{0};
+  if (first_use_on_this_device(attr_seen)) {
     M4B_CUDA(cudaFuncSetAttribute(m4rm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   M4RM_SMEM));
-    attr_set = true;
   }
   dim3 grid((C->width * 2 + TNW - 1) / TNW, (C->nrows + TM - 1) / TM);
   timing_begin("m4rm_kernel", s, 2.0 * C->nrows * C->ncols * A->ncols);

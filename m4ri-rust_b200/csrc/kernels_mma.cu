@@ -279,10 +279,9 @@ void k_mul_abt_mma1(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStrea
   }
   if (!has_tcgen05()) die("m4ri_b200: the tcgen05 MMA path needs an sm_100 device\n");
   if (!mma_shape_ok(C, A, Bt)) die("m4ri_b200: mma kernel needs 16-byte aligned rows\n");
-  static bool attr_set = false;
-  if (!attr_set) {
+  static std::atomic<unsigned long long> attr_seen{0};
+  if (first_use_on_this_device(attr_seen)) {
     M4B_CUDA(cudaFuncSetAttribute(mma_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    attr_set = true;
   }
   const int tiles_m = (C->nrows + BM - 1) / BM, tiles_n = (C->ncols + BN - 1) / BN;
   timing_begin("mma_i8_kernel", s, 2.0 * C->nrows * C->ncols * A->ncols);

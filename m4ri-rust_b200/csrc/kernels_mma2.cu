@@ -327,10 +327,9 @@ CUtensorMap packed_rows_map(const word *d, int nrows, int width, int rowstride) 
 
 template <int CG>
 static void launch_mma2(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static std::atomic<unsigned long long> attr_seen{0};
+  if (first_use_on_this_device(attr_seen)) {
     M4B_CUDA(cudaFuncSetAttribute(mma2_kernel<CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_V2));
-    attr_set = true;
   }
   const int tile = 128 * CG;
   const int tiles_m = (C->nrows + tile - 1) / tile, tiles_n = (C->ncols + tile - 1) / tile;

@@ -332,10 +332,9 @@ mma4_kernel(uint32_t *__restrict__ C, const __grid_constant__ CUtensorMap tmA,
 template <int CG>
 static void launch_mma4(DMat *C, const DMat *A, const DMat *Bt, int clear, float *raw_acc,
                         cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static std::atomic<unsigned long long> attr_seen{0};
+  if (first_use_on_this_device(attr_seen)) {
     M4B_CUDA(cudaFuncSetAttribute(mma4_kernel<CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_V4));
-    attr_set = true;
   }
   const int tile = 128 * CG;
   const int tiles_m = (C->nrows + tile - 1) / tile, tiles_n = (C->ncols + tile - 1) / tile;

@@ -345,10 +345,9 @@ mma5_kernel(uint32_t *__restrict__ C, const uint8_t *__restrict__ Ab, const uint
 // ---- host side -------------------------------------------------------------------
 template <int CG, bool WIDE>
 static void launch_mma5(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static std::atomic<unsigned long long> attr_seen{0};
+  if (first_use_on_this_device(attr_seen)) {
     M4B_CUDA(cudaFuncSetAttribute(mma5_kernel<CG, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_V5));
-    attr_set = true;
   }
   const int tile = 128 * CG;
   const int tiles_m = (C->nrows + tile - 1) / tile, tiles_n = (C->ncols + tile - 1) / tile;

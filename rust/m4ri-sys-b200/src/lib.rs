@@ -81,6 +81,9 @@ extern "C" {
     pub fn m4ri_b200_set_algo(algo: c_int);
     pub fn m4ri_b200_get_algo() -> c_int;
     pub fn m4ri_b200_set_strassen_levels(levels: c_int);
+    pub fn m4ri_b200_set_devices(n: c_int);
+    pub fn m4ri_b200_get_devices() -> c_int;
+    pub fn m4ri_b200_host_cache_trim();
     pub fn m4ri_b200_device_count() -> c_int;
     pub fn m4ri_b200_device_info(name: *mut c_char, name_len: c_int, sm_count: *mut c_int,
                                  cc_major: *mut c_int, cc_minor: *mut c_int) -> c_int;
