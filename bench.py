@@ -119,7 +119,7 @@ def cpu_arm(n, m_total, steps, warmup, target_s=12.0):
     m4rm = {"value": 2.0 * rows * n * n / t / 1e12, "ms_per_step": t * 1e3,
             "sample": f"first {rows} of {m_total} rows of A times the full {n}x{n} B, per step"}
     # Strassen strategy: a square product on the same seeded operands — the full workload when
-    # (steps + warmup) of them fit ~90 s of CPU time (estimated from an 8192-cube), else the
+    # (steps + warmup) of them fit ~60 s of CPU time (estimated from an 8192-cube), else the
     # largest leading ns x ns x ns sub-square that does (throughput is nearly size-independent)
     ns = n
     if n > 8192:
@@ -128,7 +128,7 @@ def cpu_arm(n, m_total, steps, warmup, target_s=12.0):
         t0 = time.perf_counter()
         oracle.mul_strassen(Ap, Bp, 8192, 8192, threads=0)
         rate = 2.0 * 8192 ** 3 / (time.perf_counter() - t0)
-        while ns > 8192 and (steps + warmup) * 2.0 * ns ** 3 / rate > 90.0:
+        while ns > 8192 and (steps + warmup) * 2.0 * ns ** 3 / rate > 60.0:
             ns //= 2
         del Ap, Bp
     if ns == n:
@@ -276,7 +276,7 @@ def main():
         if rank != 0:
             return
         steps, warmup = args.steps, args.warmup
-        r = cpu_arm(n, n, steps, warmup, target_s=60.0)
+        r = cpu_arm(n, n, steps, warmup, target_s=30.0)
         line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": "Tbit-op/s",
                 "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": r["ms_per_step"],
                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u64",

@@ -475,3 +475,33 @@ def test_fp4_accumulators_are_exact(gpu, m4, orc):
             assert (acc.cpu().numpy() == want).all(), (cg, m, k, n)
             L.mzd_free(a)
             L.mzd_free(b)
+
+
+def test_multi_device_host_products(gpu, m4, orc):
+    """m4ri_b200_set_devices(G): one host-ABI call spread over the GPUs of the process (row-blocks
+    of A and C on per-GPU worker threads). Needs two visible GPUs; the result must be the
+    single-GPU words, for the plain, accumulate and pre-transposed forms on a ragged shape."""
+    L = m4.lib()
+    if L.m4ri_b200_device_count() < 2:
+        pytest.skip("one GPU visible")
+    m, k, n = 5000, 20000, 9000
+    A, B, C0 = orc.random(m, k, 21), orc.random(k, n, 22), orc.random(m, n, 23)
+    want = orc.mul_m4rm(A, B, k, n, threads=0)[:, : orc.width(n)]
+    a, b = host(m4, A, k), host(m4, B, n)
+    try:
+        L.m4ri_b200_set_devices(2)
+        assert L.m4ri_b200_get_devices() == 2
+        assert (result_words(m4, L.mzd_mul(None, a, b, 0)) == want).all()
+        c = host(m4, C0, n)
+        L.mzd_addmul(c, a, b, 0)
+        assert (result_words(m4, c) == (C0[:, : orc.width(n)] ^ want)).all()
+        bt = L.mzd_transpose(None, b)
+        L.m4ri_b200_set_algo(m4.ALGO_MMA)
+        got = result_words(m4, L._mzd_mul_naive(None, a, bt, 1))
+        assert (got == want).all()
+        L.mzd_free(bt)
+    finally:
+        L.m4ri_b200_set_algo(m4.ALGO_AUTO)
+        L.m4ri_b200_set_devices(1)
+    for p in (a, b):
+        L.mzd_free(p)
