@@ -6,18 +6,20 @@
 
 A step is one product C = A*B over GF(2) on synthetic uniform random bits.
   N = 1 : square n = 32768 (BASELINE configs[2], the size the metric is quoted on).
-  N > 1 : square n = 65536 (configs[3]): C/A row-blocks sharded over the ranks, B
-          broadcast from rank 0 by NCCL inside every timed step (the path's one
-          exchange step), one process per GPU under torchrun.
+  N > 1 : square n = 65536 (configs[3]): C/A row-blocks sharded over the ranks, B of
+          rank 0 distributed inside every timed step (the path's one exchange step;
+          default: fused into the transpose with NVLink peer stores, --exchange nccl:
+          NCCL broadcast in overlapped k-chunks), one process per GPU under torchrun.
 `value` = effective bit-ops 2*m*k*n of the whole job / device time (operands
 resident in HBM); `e2e` = the same through the reference-facing C-ABI call
 mzd_mul(NULL, A, B, 0) on HOST mzd_t operands (H2D + kernels + D2H inside the
 timed region). Prints ONE JSON line on rank 0.
 
 --impl reference times the CPU arm: M4RI itself is an absent submodule of the
-reference (DESIGN.md "Oracle"), so the arm is the repo's C restatement of the
-Method of the Four Russians (oracle/, kind "port") on all host threads, on a
-bounded row sample of the same workload.
+reference (DESIGN.md "Oracle"), so the arm is the repo's C restatement (oracle/,
+kind "port") of both strategies of the reference's mul_impl! on all host threads —
+Strassen-Winograd over Four-Russians leaves (the default mzd_mul; the full product
+per step) and the Four Russians alone (bounded row sample); value = the faster.
 """
 import argparse
 import ctypes

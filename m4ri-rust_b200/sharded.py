@@ -146,7 +146,7 @@ class FusedBroadcastMul:
     The tensor path consumes B transposed (Bt, n x k, k-contiguous). Instead of "NCCL
     broadcast of B, then every rank transposes all of it", rank g transposes ONE k-slab of
     B — read straight from the root's memory over NVLink — and the same kernel stores the
-    slab of Bt into every rank's Bt buffer with peer stores (transpose_scatter_kernel). Root
+    slab of Bt into every rank's Bt buffer with 128-byte peer stores (transpose_wide_kernel). Root
     egress is |B| instead of (G-1)|B|, every link carries (G-1)/G |B| in parallel, no SM is
     held by a collective while the product runs, and the product is one launch over the full
     k. Buffers are torch symmetric memory (NVLink-mapped into every process of the node);

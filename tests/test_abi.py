@@ -190,3 +190,35 @@ def test_host_block_cache_reuses_and_zeroes():
     e = L.mzd_init(10, 10)
     L.mzd_free(e)
     assert stats()[2] == 0
+
+
+def test_allocator_is_thread_safe():
+    """BinMatrix is Send + Sync (binary_matrix.rs:38-39): mzd_init / mzd_free from several host
+    threads at once, through the block cache, never hand one block to two owners."""
+    import ctypes
+    import threading
+    import m4ri_rust_b200 as m4
+    L = m4.lib()
+    errors = []
+
+    def worker(tag):
+        try:
+            for it in range(40):
+                a = L.mzd_init(1024 + 64 * (it % 3), 4096)  # 512-576 KiB: cached sizes
+                w = m4.mzd_words(a)
+                if w.any():
+                    errors.append("block not zeroed")
+                w[:] = tag  # every word of the block carries the owner's tag
+                if not (m4.mzd_words(a) == tag).all():
+                    errors.append("block shared between owners")
+                L.mzd_free(a)
+        except Exception as e:  # pragma: no cover
+            errors.append(repr(e))
+
+    threads = [threading.Thread(target=worker, args=(t + 1,)) for t in range(6)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors[:3]
+    L.m4ri_b200_host_cache_trim()
