@@ -90,22 +90,33 @@ class ClockSampler(threading.Thread):
                 "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
-def cpu_arm(n, m_total, steps, warmup, target_s=12.0):
+def host_threads():
+    """Host threads the CPU arm uses: the cores this process may run on. Passed to the oracle
+    explicitly — torchrun exports OMP_NUM_THREADS=1, which would otherwise silently turn the
+    N > 1 reference arm into a one-thread run."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+def cpu_arm(n, m_total, steps, warmup, target_s=12.0, budget_s=600.0, strassen_n=None):
     """CPU arm on the box's host cores, both strategies of the reference's `mul_impl!`
     (m4ri-rust/src/friendly/binary_matrix.rs:53-95), all host threads:
     - "strassen": Strassen-Winograd over Four-Russians leaves (the default, mzd_mul) on the
-      full n x n x n workload — the recursion needs the whole square, so the sample is bounded
-      by the step count instead;
+      full n x n x n workload — the recursion needs the whole square, so when (steps + warmup)
+      products do not fit `budget_s` the number of STEPS shrinks (recorded), never the size;
+      `strassen_n` (the cpu_baseline leg of an N > 1 line only) asks for a smaller, labelled cube;
     - "m4rm": Four Russians alone (mzd_mul_m4rm) on a bounded row sample, the first `rows` rows
       of A against the full k x n B.
     `value` is the faster of the two."""
     import oracle
-    threads = oracle.max_threads()
+    threads = host_threads()
     B = oracle.random(n, n, SEED_B)
     probe_rows = 256
     A = oracle.random(probe_rows, n, SEED_A)
     t0 = time.perf_counter()
-    oracle.mul_m4rm(A, B, n, n, threads=0)
+    oracle.mul_m4rm(A, B, n, n, threads=threads)
     t_probe = time.perf_counter() - t0
     per_step = target_s / max(1, steps + warmup)
     rows = int(min(m_total, max(256, probe_rows * per_step / max(t_probe, 1e-6))))
@@ -114,24 +125,27 @@ def cpu_arm(n, m_total, steps, warmup, target_s=12.0):
     times = []
     for i in range(warmup + steps):
         t0 = time.perf_counter()
-        oracle.mul_m4rm(A, B, n, n, threads=0)
+        oracle.mul_m4rm(A, B, n, n, threads=threads)
         if i >= warmup:
             times.append(time.perf_counter() - t0)
     t = sum(times) / len(times)
     m4rm = {"value": 2.0 * rows * n * n / t / 1e12, "ms_per_step": t * 1e3,
             "sample": f"first {rows} of {m_total} rows of A times the full {n}x{n} B, per step"}
-    # Strassen strategy: a square product on the same seeded operands — the full workload when
-    # (steps + warmup) of them fit ~60 s of CPU time (estimated from an 8192-cube), else the
-    # largest leading ns x ns x ns sub-square that does (throughput is nearly size-independent)
-    ns = n
-    if n > 8192:
+    # Strassen strategy: the full square product on the same seeded operands. The step count is
+    # bounded by the time budget (estimated from an 8192-cube); the size is not reduced.
+    ns = strassen_n or n
+    s_steps, s_warm = steps, warmup
+    if ns > 8192:
         Ap, Bp = oracle.random(8192, 8192, SEED_A), oracle.random(8192, 8192, SEED_B)
-        oracle.mul_strassen(Ap, Bp, 8192, 8192, threads=0)
+        oracle.mul_strassen(Ap, Bp, 8192, 8192, threads=threads)
         t0 = time.perf_counter()
-        oracle.mul_strassen(Ap, Bp, 8192, 8192, threads=0)
+        oracle.mul_strassen(Ap, Bp, 8192, 8192, threads=threads)
         rate = 2.0 * 8192 ** 3 / (time.perf_counter() - t0)
-        while ns > 8192 and (steps + warmup) * 2.0 * ns ** 3 / rate > 60.0:
-            ns //= 2
+        est = 2.0 * ns ** 3 / rate
+        while s_warm > 1 and (s_steps + s_warm) * est > budget_s:
+            s_warm -= 1
+        while s_steps > 1 and (s_steps + s_warm) * est > budget_s:
+            s_steps -= 1
         del Ap, Bp
     if ns == n:
         A = oracle.random(n, n, SEED_A)
@@ -139,19 +153,20 @@ def cpu_arm(n, m_total, steps, warmup, target_s=12.0):
     else:
         A, Bs = oracle.random(ns, ns, SEED_A), oracle.random(ns, ns, SEED_B)
     times = []
-    for i in range(warmup + steps):
+    for i in range(s_warm + s_steps):
         t0 = time.perf_counter()
-        C = oracle.mul_strassen(A, Bs, ns, ns, threads=0)
-        if i >= warmup:
+        C = oracle.mul_strassen(A, Bs, ns, ns, threads=threads)
+        if i >= s_warm:
             times.append(time.perf_counter() - t0)
     t = sum(times) / len(times)
     strassen = {"value": 2.0 * ns * ns * ns / t / 1e12, "ms_per_step": t * 1e3,
+                "steps_timed": s_steps, "warmup_run": s_warm,
                 "sample": (f"the full {n}x{n}x{n} product, per step" if ns == n else
-                           f"a {ns}x{ns}x{ns} product per step (the {n}-cube does not fit the time bound)"),
+                           f"a {ns}x{ns}x{ns} product per step (bounded sample of the {n}-cube)"),
                 "checksum": f"{oracle.checksum(C, ns):016x}" if ns == n else None}
     best, name = (strassen, "strassen") if strassen["value"] >= m4rm["value"] else (m4rm, "m4rm")
     return {"value": best["value"], "unit": "Tbit-op/s", "cores": threads, "kind": "port",
-            "sample": f"{name}: {best['sample']}; CPU restatement (oracle/gf2_oracle.c, OpenMP) of the "
+            "sample": f"{name}: {best['sample']}; CPU restatement (oracle/gf2_oracle.c, OpenMP, {threads} threads) of the "
                       f"reference's two strategies, not M4RI itself (absent submodule, none on the box)",
             "ms_per_step": best["ms_per_step"], "rows": rows if name == "m4rm" else ns,
             "strategies": {"strassen": strassen, "m4rm": m4rm}}
@@ -200,40 +215,91 @@ def run_lpn(args):
                       "gbs_compulsory": (2 * m * 64 + k * 64) / ms / 1e6}
     out["product"] = prod
     out["value"], out["unit"], out["ms_per_step"] = prod["auto"]["tbitops"], "Tbit-op/s", prod["auto"]["ms"]
-    # mat-vec
+    # ---- mat-vec on the resident A: HBM bound ------------------------------------------
+    pk = peaks()
+    w = k // 64
+    # Every launch must read its A from HBM, not from the 126 MB L2: the launches rotate over
+    # four resident copies of A (4 x 64 MiB = 256 MiB > L2), timed back to back with one event
+    # pair around the batch — the launch latency of a ~12 us kernel is then amortised instead of
+    # being charged to a 64 MiB read. The L2-flushed single-launch time is kept beside it.
+    copies = [dA] + [m4.DMat.init(m, k).fill_random(21) for _ in range(3)]
+
+    def rotating(fn_of_A, reps=24):
+        for i in range(8):
+            fn_of_A(copies[i % 4])
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        for i in range(reps):
+            fn_of_A(copies[i % 4])
+        b.record(stream)
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps
+
+    def roof(bytes_alg, ms, kernel):
+        return {"bound": "hbm", "achieved": bytes_alg / ms / 1e6, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                "frac": bytes_alg / ms / 1e6 / pk["hbm_gbs"], "traffic": None, "kernel": kernel,
+                "algorithmic_bytes": bytes_alg}
+
     dx = m4.DMat.init(1, k).fill_random(23)
     dy = m4.DMat.init(1, m)
-    ms = timed(lambda: L.m4ri_b200_dmul_v(dy.h, dA.h, dx.h, 1), args.steps, args.warmup)
-    bytes_alg = 8 * (m * (k // 64) + k // 64) + (m // 64) * 8
-    pk = peaks()
-    out["matvec"] = {"ms": ms, "tbitops": 2.0 * m * k / ms / 1e9,
-                     "roofline": {"bound": "hbm", "achieved": bytes_alg / ms / 1e6, "peak": pk["hbm_gbs"],
-                                  "unit": "GB/s", "frac": bytes_alg / ms / 1e6 / pk["hbm_gbs"], "traffic": None,
-                                  "kernel": "mul_v_coal_kernel<4>", "algorithmic_bytes": bytes_alg}}
+    ms_single = timed(lambda: L.m4ri_b200_dmul_v(dy.h, dA.h, dx.h, 1), args.steps, args.warmup)
+    ms = rotating(lambda A_: L.m4ri_b200_dmul_v(dy.h, A_.h, dx.h, 1))
+    bytes_alg = 8 * (m * w + w) + (m // 64) * 8
+    out["matvec"] = {"ms": ms, "ms_flushed_single_launch": ms_single, "tbitops": 2.0 * m * k / ms / 1e9,
+                     "timing": "24 launches back to back over 4 resident copies of A (256 MiB > L2), one event pair",
+                     "roofline": roof(bytes_alg, ms, "mul_v_coal_kernel<4,2>")}
+    # batched: b vectors against the resident A in one pass (m4ri_b200_dmul_v_batched)
+    for bvec in (8, 32):
+        dX = m4.DMat.init(bvec, k).fill_random(24)
+        dY = m4.DMat.init(bvec, m)
+        msb = rotating(lambda A_: L.m4ri_b200_dmul_v_batched(dY.h, A_.h, dX.h, 1))
+        passes = (bvec + 7) // 8
+        bb = passes * 8 * m * w + 8 * bvec * w + bvec * (m // 64) * 8
+        out[f"matvec_batched_{bvec}"] = {"ms": msb, "tbitops": 2.0 * m * k * bvec / msb / 1e9, "vectors": bvec,
+                                        "passes_over_A": passes,
+                                        "roofline": roof(bb, msb, "mul_vb_coal_kernel<4,1,8>")}
+    # the reference's own call: BinMatrix::mul_slice = mzd_mul_naive(NULL, A, x_column) on HOST
+    # operands (binary_matrix.rs:416-431): 64 MiB of A cross PCIe per call, then the same kernel
+    hA = L.mzd_init(m, k)
+    L.m4ri_b200_download(hA, dA.h)
+    L.m4ri_b200_synchronize()
+    M = m4.BinMatrix(hA)
+    xw = m4.mzd_words(dx.to_host())[0, :w].copy()
+    for _ in range(2):
+        M.mul_slice(xw)
+    L.m4ri_b200_timing_reset()
+    t0 = time.perf_counter()
+    reps = 5
+    for _ in range(reps):
+        col = M.mul_slice(xw)
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / reps
+    out["matvec_via_mul_slice"] = {"ms": e2e_ms, "kernel": L.m4ri_b200_timing_name().decode(),
+                                   "h2d_bytes_per_call": m * w * 8, "d2h_bytes_per_call": (m // 64) * 8,
+                                   "api": "BinMatrix.mul_slice -> mzd_transpose + mzd_mul_naive(NULL, A, x) on host mzd_t (binary_matrix.rs:416-431)",
+                                   "pcie_gbs": m * w * 8 / e2e_ms / 1e6}
+    del M
     # the same kernel on a 4x taller A (256 MiB > L2): launch latency amortised, no flush needed
     m2 = 1 << 22
     dA2 = m4.DMat.init(m2, k).fill_random(31)
     dy2 = m4.DMat.init(1, m2)
     ms2 = timed(lambda: L.m4ri_b200_dmul_v(dy2.h, dA2.h, dx.h, 1), args.steps, args.warmup)
-    b2 = 8 * (m2 * (k // 64) + k // 64) + (m2 // 64) * 8
-    out["matvec_2^22_rows"] = {"ms": ms2, "tbitops": 2.0 * m2 * k / ms2 / 1e9,
-                               "roofline": {"bound": "hbm", "achieved": b2 / ms2 / 1e6, "peak": pk["hbm_gbs"],
-                                            "unit": "GB/s", "frac": b2 / ms2 / 1e6 / pk["hbm_gbs"],
-                                            "traffic": None, "kernel": "mul_v_coal_kernel<4>",
-                                            "algorithmic_bytes": b2}}
+    b2 = 8 * (m2 * w + w) + (m2 // 64) * 8
+    out["matvec_2^22_rows"] = {"ms": ms2, "tbitops": 2.0 * m2 * k / ms2 / 1e9, "roofline": roof(b2, ms2, "mul_v_coal_kernel<4,2>")}
     del dA2, dy2
-    # long rows: square 32768 x 32768 A (128 MiB), one warp per row
+    # long rows: square 32768 x 32768 A (128 MiB > L2), one CTA per 32 rows
     m3 = n3 = 32768
     dA3 = m4.DMat.init(m3, n3).fill_random(41)
     dx3 = m4.DMat.init(1, n3).fill_random(42)
     dy3 = m4.DMat.init(1, m3)
     ms3 = timed(lambda: L.m4ri_b200_dmul_v(dy3.h, dA3.h, dx3.h, 1), args.steps, args.warmup)
     b3 = 8 * (m3 * (n3 // 64) + n3 // 64) + (m3 // 64) * 8
-    out["matvec_32768x32768"] = {"ms": ms3, "tbitops": 2.0 * m3 * n3 / ms3 / 1e9,
-                                 "roofline": {"bound": "hbm", "achieved": b3 / ms3 / 1e6, "peak": pk["hbm_gbs"],
-                                              "unit": "GB/s", "frac": b3 / ms3 / 1e6 / pk["hbm_gbs"],
-                                              "traffic": None, "kernel": "mul_v_long_kernel",
-                                              "algorithmic_bytes": b3}}
+    out["matvec_32768x32768"] = {"ms": ms3, "tbitops": 2.0 * m3 * n3 / ms3 / 1e9, "roofline": roof(b3, ms3, "mul_v_long_kernel")}
+    dX3 = m4.DMat.init(8, n3).fill_random(43)
+    dY3 = m4.DMat.init(8, m3)
+    ms3b = timed(lambda: L.m4ri_b200_dmul_v_batched(dY3.h, dA3.h, dX3.h, 1), args.steps, args.warmup)
+    out["matvec_batched_8_32768x32768"] = {"ms": ms3b, "tbitops": 2.0 * m3 * n3 * 8 / ms3b / 1e9,
+                                           "roofline": roof(b3 + 7 * (n3 // 8 + m3 // 8), ms3b, "mul_vb_long_kernel<8>")}
     print(json.dumps(out))
 
 
@@ -279,6 +345,7 @@ def main():
             return
         steps, warmup = args.steps, args.warmup
         r = cpu_arm(n, n, steps, warmup, target_s=30.0)
+        config = dict(config, cpu_threads=r["cores"], cpu_sample=r["sample"])
         line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": "Tbit-op/s",
                 "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": r["ms_per_step"],
                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u64",
@@ -437,7 +504,7 @@ def main():
         # strictest denominator); the fraction of 2 x the driver-measured cuBLAS bf16 burst
         # (power-capped at ~1.3 GHz) is reported beside it.
         sm_max = (clocks.get("sm_max_mhz") or 1965) * 1e6
-        fp4 = "mma4" in kern_name or "mma5" in kern_name  # kind::mxf4: 64 elements per row per MMA, twice kind::i8
+        fp4 = any(v in kern_name for v in ("mma4", "mma5", "mma6"))  # kind::mxf4: 64 elements per row per MMA, twice kind::i8
         per_clk = 32768.0 if fp4 else 16384.0
         peak = per_clk * 148 * sm_max / 1e12
         meas = (4.0 if fp4 else 2.0) * pk["bf16_tflops"]
@@ -487,6 +554,10 @@ def main():
                        "ms_per_step": e2e_max, "h2d_bytes_per_step": bytes_in,
                        "d2h_bytes_per_step": rows * ws * 8,
                        "api": "C = mzd_mul(NULL, A, B, 0) on host mzd_t operands (pinned), result allocated by the library and freed by the caller as m4ri-rust does; per rank on its row-block"}
+    if world > 1 and not args.no_cpu_baseline:
+        # N > 1 lines: a bounded, labelled sample (the full arm is `--impl reference`)
+        r = cpu_arm(n, n, 1, 1, target_s=6.0, strassen_n=16384)
+        line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample", "strategies")}
     if world == 1 and not args.no_cpu_baseline:
         r = cpu_arm(n, n, 2, 1, target_s=12.0)
         line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample", "strategies")}

@@ -79,6 +79,10 @@ void mzd_randomize(mzd_t *A);                            /* mzd.rs:184 */
 mzd_t *mzd_transpose(mzd_t *DST, const mzd_t *A);        /* mzd.rs:148 */
 mzd_t *mzd_add(mzd_t *C, const mzd_t *A, const mzd_t *B);/* mzd.rs:223 (C may alias A) */
 mzd_t *mzd_sub(mzd_t *C, const mzd_t *A, const mzd_t *B);/* mzd.rs:230 (alias of add)  */
+/* [A B] and [A; B] (BinMatrix::augmented / stacked, binary_matrix.rs:221-244): host copies, so that
+ * an unmodified m4ri-rust links against this library alone. */
+mzd_t *mzd_concat(mzd_t *C, const mzd_t *A, const mzd_t *B); /* mzd.rs:195 */
+mzd_t *mzd_stack(mzd_t *C, const mzd_t *A, const mzd_t *B);  /* mzd.rs:201 */
 
 /* ---- the hot path: every one of these runs on the GPU ----------------------- */
 /* C = A*B. C == NULL: allocate. cutoff is a hint (the result does not depend on it). */
@@ -129,7 +133,7 @@ int m4ri_b200_get_devices(void);
  * needed; M4RI_B200_PIPE_ROWS / M4RI_B200_PIPE_COLS override it). */
 void m4ri_b200_pipeline_plan(int m, int k, int n, int clear, int *row_chunks, int *col_blocks);
 /* Kernel variant behind M4RI_B200_ALGO_MMA (0 restores the default; also
- * settable with M4RI_B200_MMA=v1|v2cg1|v2|fp4cg1|fp4|fp4tma): benchmarking knob. */
+ * settable with M4RI_B200_MMA=v1|v2cg1|v2|fp4cg1|fp4|fp4ldgcg1|fp4ldg|fp4s256cg1|fp4s256): benchmarking knob. */
 enum m4ri_b200_mma_variant {
   M4RI_B200_MMA_DEFAULT = 0,
   M4RI_B200_MMA_V1 = 1,        /* one CTA per 128x128 tile, operands expanded into shared memory */
@@ -138,7 +142,9 @@ enum m4ri_b200_mma_variant {
   M4RI_B200_MMA_FP4_SINGLE = 4,/* bits -> E2M1 nibbles, kind::mxf4 (2x the int8 rate), cta_group::1 */
   M4RI_B200_MMA_FP4_PAIR = 5,  /* the same on CTA pairs, 256x256 tiles                           */
   M4RI_B200_MMA_FP4_LDG_SINGLE = 6, /* FP4, packed bits by direct 256-bit global loads (no TMA)  */
-  M4RI_B200_MMA_FP4_LDG_PAIR = 7    /* the same on CTA pairs (default)                           */
+  M4RI_B200_MMA_FP4_LDG_PAIR = 7,   /* the same on CTA pairs (round 1's default)                 */
+  M4RI_B200_MMA_FP4_S256_SINGLE = 8,/* FP4, 256-bit stages x 6, 16 expander + 8 epilogue warps   */
+  M4RI_B200_MMA_FP4_S256_PAIR = 9   /* the same on CTA pairs (default)                           */
 };
 void m4ri_b200_set_mma_variant(int variant);
 
@@ -184,6 +190,13 @@ void m4ri_b200_dmul_abt(m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *A,
  * (packed words in, packed words out: SURVEY 8f.2). */
 void m4ri_b200_dmul_v(m4ri_b200_dmat_t *y, const m4ri_b200_dmat_t *A, const m4ri_b200_dmat_t *x,
                       int clear);
+/* Batched mat-vec (BASELINE configs[4] "batched mzd_mul_v"): row q of Y (1 x nrows(A), packed) (^)=
+ * A * x_q for the b packed vectors x_q = rows of X (b x ncols(A)); Y is b x nrows(A). One pass over A
+ * per 8 vectors (HBM-bound); more than 32 vectors go to the tensor path as Y = X * A^T. The
+ * reference's mat-vec surface is mul_slice / Mul<&BinVector> (binary_matrix.rs:416-431,528-550),
+ * one vector per call. */
+void m4ri_b200_dmul_v_batched(m4ri_b200_dmat_t *Y, const m4ri_b200_dmat_t *A, const m4ri_b200_dmat_t *X,
+                              int clear);
 /* C (^)= v*A, v is r x nrows(A) with small r. */
 void m4ri_b200_dmul_va(m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *v, const m4ri_b200_dmat_t *A,
                        int clear);

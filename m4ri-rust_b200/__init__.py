@@ -19,12 +19,13 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libm4ri_b200.so")
+# M4RI_B200_LIB selects another build of the same library (the perf-hook build of build.py --perf)
+LIB_PATH = os.environ.get("M4RI_B200_LIB") or os.path.join(_HERE, "lib", "libm4ri_b200.so")
 HEADER_PATH = os.path.join(_HERE, "..", "include", "m4ri_b200.h")
 
 ALGO_AUTO, ALGO_M4RM, ALGO_MMA, ALGO_SIMPLE = 0, 1, 2, 3
 ALGO_NAMES = {"auto": 0, "m4rm": 1, "mma": 2, "simple": 3}
-MMA_VARIANTS = {"default": 0, "v1": 1, "v2cg1": 2, "v2": 3, "fp4cg1": 4, "fp4": 5, "fp4ldgcg1": 6, "fp4ldg": 7}
+MMA_VARIANTS = {"default": 0, "v1": 1, "v2cg1": 2, "v2": 3, "fp4cg1": 4, "fp4": 5, "fp4ldgcg1": 6, "fp4ldg": 7, "fp4s256cg1": 8, "fp4s256": 9}
 
 
 class MzdBlock(ctypes.Structure):
@@ -64,6 +65,7 @@ def lib():
         "mzd_set_ui": (None, [MzdP, u]), "mzd_randomize": (None, [MzdP]),
         "mzd_transpose": (MzdP, [MzdP, MzdP]),
         "mzd_add": (MzdP, [MzdP, MzdP, MzdP]), "mzd_sub": (MzdP, [MzdP, MzdP, MzdP]),
+        "mzd_concat": (MzdP, [MzdP, MzdP, MzdP]), "mzd_stack": (MzdP, [MzdP, MzdP, MzdP]),
         "mzd_mul": (MzdP, [MzdP, MzdP, MzdP, i]), "mzd_addmul": (MzdP, [MzdP, MzdP, MzdP, i]),
         "mzd_mul_m4rm": (MzdP, [MzdP, MzdP, MzdP, i]),
         "mzd_addmul_m4rm": (MzdP, [MzdP, MzdP, MzdP, i]),
@@ -91,6 +93,7 @@ def lib():
         "m4ri_b200_dmul_abt_fp4_debug": (None, [vp, vp, vp, vp, i]),
         "m4ri_b200_dmul_v": (None, [vp, vp, vp, i]),
         "m4ri_b200_dmul_va": (None, [vp, vp, vp, i]),
+        "m4ri_b200_dmul_v_batched": (None, [vp, vp, vp, i]),
         "m4ri_b200_dtranspose": (None, [vp, vp]), "m4ri_b200_dadd": (None, [vp, vp, vp]),
         "m4ri_b200_dcopy": (None, [vp, vp]),
         "m4ri_b200_dfill_random": (None, [vp, u64]),

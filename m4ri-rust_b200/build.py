@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libm4ri_b200.so")
-SOURCES = ["api.cu", "kernels_aux.cu", "kernels_m4rm.cu", "kernels_mma.cu", "kernels_mma2.cu", "kernels_mma4.cu", "kernels_mma5.cu", "mzd_host.cpp"]
+SOURCES = ["api.cu", "kernels_aux.cu", "kernels_m4rm.cu", "kernels_mma.cu", "kernels_mma2.cu", "kernels_mma4.cu", "kernels_mma5.cu", "kernels_mma6.cu", "mzd_host.cpp"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",
@@ -33,16 +33,29 @@ def _stale():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False):
+PERF_LIB = os.path.join(LIBDIR, "libm4ri_b200_perf.so")
+
+
+def build(force=False, verbose=False, perf=False):
+    """perf=True builds libm4ri_b200_perf.so with -DM4RI_B200_PERF_HOOKS: the tensor kernels then
+    honour M4RI_B200_DBG (bit 0: no operand expansion, bit 2: no accumulator drain) for the
+    isolation experiments of tools/gpu_dbg.sh. The shipped library has no such switch; select the
+    perf build with M4RI_B200_LIB=<path>."""
+    if perf:
+        return _build(PERF_LIB, os.path.join(LIBDIR, "perf"), ["-DM4RI_B200_PERF_HOOKS"], verbose)
     if not force and not _stale():
         return LIB
-    os.makedirs(LIBDIR, exist_ok=True)
+    return _build(LIB, LIBDIR, [], verbose)
+
+
+def _build(LIB, OBJDIR, extra, verbose):
+    os.makedirs(OBJDIR, exist_ok=True)
     objs = []
     procs = []
     for src in SOURCES:
-        obj = os.path.join(LIBDIR, os.path.splitext(src)[0] + ".o")
+        obj = os.path.join(OBJDIR, os.path.splitext(src)[0] + ".o")
         objs.append(obj)
-        cmd = ["nvcc"] + NVCC_FLAGS + ["-c", "-o", obj, os.path.join(CSRC, src)]
+        cmd = ["nvcc"] + NVCC_FLAGS + extra + ["-c", "-o", obj, os.path.join(CSRC, src)]
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     log = []
     failed = False
@@ -50,7 +63,7 @@ def build(force=False, verbose=False):
         out, _ = p.communicate()
         log.append(f"==== {src}\n{out}")
         failed |= p.returncode != 0
-    with open(os.path.join(LIBDIR, "build.log"), "w") as f:
+    with open(os.path.join(OBJDIR, "build.log"), "w") as f:
         f.write("\n".join(log))
     if failed or verbose:
         sys.stderr.write("\n".join(log))
@@ -58,6 +71,21 @@ def build(force=False, verbose=False):
         raise RuntimeError("nvcc failed, see m4ri-rust_b200/lib/build.log")
     subprocess.check_call(["nvcc", "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"])
     return LIB
+
+
+def build_variant(name, defs, source="kernels_mma6.cu"):
+    """A/B builds of one kernel file: lib/exp/<name>.so = the current objects of the library with
+    `source` recompiled under the given -D definitions (tools/mma6_explore.sh)."""
+    build()
+    d = os.path.join(LIBDIR, "exp")
+    os.makedirs(d, exist_ok=True)
+    obj = os.path.join(d, name + ".o")
+    subprocess.check_call(["nvcc"] + [f for f in NVCC_FLAGS if f not in ("-Xptxas", "-v")] + ["-D" + x for x in defs] +
+                          ["-c", "-o", obj, os.path.join(CSRC, source)])
+    objs = [os.path.join(LIBDIR, os.path.splitext(src)[0] + ".o") for src in SOURCES if src != source] + [obj]
+    out = os.path.join(d, name + ".so")
+    subprocess.check_call(["nvcc", "-shared", "-o", out] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"])
+    return out
 
 
 MICROBENCH = os.path.join(LIBDIR, "microbench")
@@ -93,6 +121,9 @@ def build_cpp_tests(force=False):
 
 
 if __name__ == "__main__":
+    if "--perf" in sys.argv:
+        print(build(perf=True, verbose="--verbose" in sys.argv))
+        sys.exit(0)
     build_microbench(force="--force" in sys.argv)
     print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))
     build_cpp_tests(force="--force" in sys.argv)

@@ -133,16 +133,19 @@ void k_mul_abt_mma(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream
   int v = g_mma_variant.load();
   if (v == 0) {
     const char *e = getenv("M4RI_B200_MMA");
-    v = !e ? M4RI_B200_MMA_FP4_LDG_PAIR
+    v = !e ? M4RI_B200_MMA_FP4_S256_PAIR
         : !strcmp(e, "v1") ? M4RI_B200_MMA_V1
         : !strcmp(e, "v2cg1") ? M4RI_B200_MMA_V2_SINGLE
         : !strcmp(e, "fp4cg1") ? M4RI_B200_MMA_FP4_SINGLE
         : !strcmp(e, "v2") ? M4RI_B200_MMA_V2_PAIR
         : !strcmp(e, "fp4ldg") ? M4RI_B200_MMA_FP4_LDG_PAIR
         : !strcmp(e, "fp4ldgcg1") ? M4RI_B200_MMA_FP4_LDG_SINGLE
-        : !strcmp(e, "fp4") ? M4RI_B200_MMA_FP4_PAIR : M4RI_B200_MMA_FP4_LDG_PAIR;
+        : !strcmp(e, "fp4s256cg1") ? M4RI_B200_MMA_FP4_S256_SINGLE
+        : !strcmp(e, "fp4") ? M4RI_B200_MMA_FP4_PAIR : M4RI_B200_MMA_FP4_S256_PAIR;
   }
   if (v == M4RI_B200_MMA_V1) k_mul_abt_mma1(C, A, Bt, clear, s);
+  else if (v == M4RI_B200_MMA_FP4_S256_SINGLE || v == M4RI_B200_MMA_FP4_S256_PAIR)
+    k_mul_abt_mma6(C, A, Bt, clear, v == M4RI_B200_MMA_FP4_S256_SINGLE ? 1 : 2, s);
   else if (v == M4RI_B200_MMA_FP4_LDG_SINGLE || v == M4RI_B200_MMA_FP4_LDG_PAIR)
     k_mul_abt_mma5(C, A, Bt, clear, v == M4RI_B200_MMA_FP4_LDG_SINGLE ? 1 : 2, s);
   else if (v == M4RI_B200_MMA_FP4_SINGLE || v == M4RI_B200_MMA_FP4_PAIR)
@@ -195,6 +198,15 @@ static void dmat_delete(DMat *M, cudaStream_t s) {
 // Rows [r0, r1) of H -> the same rows of D. rows[] is the only thing the reference
 // guarantees ("multi-block"): maximal runs of evenly strided rows go as one
 // 2-D copy each.
+// One run of evenly strided rows between host and device. When the rows are back to back on both
+// sides (stride == width) it is ONE linear copy: a 2-D copy of 64-byte rows runs at a quarter of
+// the PCIe rate (2^20 x 512 bits: 5.6 ms as 2-D, 1.3 ms linear).
+static void copy_rows(void *dst, size_t dpitch, const void *src, size_t spitch, size_t wbytes, size_t nrows,
+                      cudaMemcpyKind kind, cudaStream_t s) {
+  if (dpitch == wbytes && spitch == wbytes) M4B_CUDA(cudaMemcpyAsync(dst, src, wbytes * nrows, kind, s));
+  else M4B_CUDA(cudaMemcpy2DAsync(dst, dpitch, src, spitch, wbytes, nrows, kind, s));
+}
+
 static void upload_rows(DMat *D, const mzd_t *H, rci_t r0, rci_t r1, cudaStream_t s) {
   if (D->nrows != H->nrows || D->ncols != H->ncols)
     die("m4ri_b200: upload: shape mismatch (%d x %d vs %d x %d)\n", D->nrows, D->ncols, H->nrows,
@@ -204,9 +216,8 @@ static void upload_rows(DMat *D, const mzd_t *H, rci_t r0, rci_t r1, cudaStream_
   while (i < r1) {
     rci_t j = i + 1;
     while (j < r1 && H->rows[j] == H->rows[i] + (size_t)(j - i) * H->rowstride) j++;
-    M4B_CUDA(cudaMemcpy2DAsync(D->d + (size_t)i * D->rowstride, (size_t)D->rowstride * 8,
-                               H->rows[i], (size_t)H->rowstride * 8, (size_t)H->width * 8, j - i,
-                               cudaMemcpyHostToDevice, s));
+    copy_rows(D->d + (size_t)i * D->rowstride, (size_t)D->rowstride * 8, H->rows[i], (size_t)H->rowstride * 8,
+              (size_t)H->width * 8, j - i, cudaMemcpyHostToDevice, s);
     i = j;
   }
   if (D->ncols % 64) {  // never trust excess bits of a caller's matrix
@@ -219,17 +230,41 @@ static void upload_rows(DMat *D, const mzd_t *H, rci_t r0, rci_t r1, cudaStream_
 }
 static void upload(DMat *D, const mzd_t *H, cudaStream_t s) { upload_rows(D, H, 0, H->nrows, s); }
 
-static void download_rows(mzd_t *H, const DMat *D, rci_t r0, rci_t r1, cudaStream_t s) {
-  if (D->nrows != H->nrows || D->ncols != H->ncols)
-    die("m4ri_b200: download: shape mismatch\n");
-  if (r1 <= r0 || H->width == 0) return;
+// A result written into a WINDOW whose last word is shared with the parent's other columns
+// (ncols % 64 != 0): the bits beyond ncols in that word belong to the parent and must survive
+// the download. The host's last-word column of rows [r0, r1) is fetched and merged into the
+// device copy before the rows travel back (all on the stream: no extra synchronize).
+static bool shares_last_word(const mzd_t *H) {
+  return (H->ncols % 64) && (H->flags & (mzd_flag_windowed_zerooffset | mzd_flag_windowed_zeroexcess));
+}
+static void merge_foreign_excess(const mzd_t *H, const DMat *D, rci_t r0, rci_t r1, cudaStream_t s) {
+  if (r1 <= r0 || !H->width) return;
+  word *col;
+  M4B_CUDA(cudaMallocAsync(&col, (size_t)(r1 - r0) * 8, s));
   rci_t i = r0;
   while (i < r1) {
     rci_t j = i + 1;
     while (j < r1 && H->rows[j] == H->rows[i] + (size_t)(j - i) * H->rowstride) j++;
-    M4B_CUDA(cudaMemcpy2DAsync(H->rows[i], (size_t)H->rowstride * 8,
-                               D->d + (size_t)i * D->rowstride, (size_t)D->rowstride * 8,
-                               (size_t)H->width * 8, j - i, cudaMemcpyDeviceToHost, s));
+    M4B_CUDA(cudaMemcpy2DAsync(col + (i - r0), 8, H->rows[i] + H->width - 1, (size_t)H->rowstride * 8, 8,
+                               j - i, cudaMemcpyHostToDevice, s));
+    i = j;
+  }
+  k_merge_excess(D->d + (size_t)r0 * D->rowstride + D->width - 1, D->rowstride, col, r1 - r0,
+                 high_mask(H->ncols), s);
+  M4B_CUDA(cudaFreeAsync(col, s));
+}
+
+static void download_rows(mzd_t *H, const DMat *D, rci_t r0, rci_t r1, cudaStream_t s) {
+  if (D->nrows != H->nrows || D->ncols != H->ncols)
+    die("m4ri_b200: download: shape mismatch\n");
+  if (r1 <= r0 || H->width == 0) return;
+  if (shares_last_word(H)) merge_foreign_excess(H, D, r0, r1, s);
+  rci_t i = r0;
+  while (i < r1) {
+    rci_t j = i + 1;
+    while (j < r1 && H->rows[j] == H->rows[i] + (size_t)(j - i) * H->rowstride) j++;
+    copy_rows(H->rows[i], (size_t)H->rowstride * 8, D->d + (size_t)i * D->rowstride, (size_t)D->rowstride * 8,
+              (size_t)H->width * 8, j - i, cudaMemcpyDeviceToHost, s);
     i = j;
   }
 }
@@ -372,12 +407,44 @@ static void product_with_strassen(DMat *C, const DMat *A, const DMat *B, int cle
   }
 }
 
+// true when neither the call nor the process-wide setting forces an algorithm: the thin
+// (HBM-bound) shapes may then skip the product kernels
+static bool thin_shape_auto(int algo) {
+  std::call_once(g_once, probe);
+  return algo == M4RI_B200_ALGO_AUTO && g_algo.load() == M4RI_B200_ALGO_AUTO;
+}
+static bool aligned16(const DMat *M) { return !((uintptr_t)M->d & 15) && !(M->rowstride & 1); }
+
 // C (^)= A*B on device
 static void dmul(DMat *C, const DMat *A, const DMat *B, int clear, int algo, cudaStream_t s,
                  int cutoff = 0) {
   if (A->ncols != B->nrows || C->nrows != A->nrows || C->ncols != B->ncols)
     die("m4ri_b200: mul: shapes (%d x %d) * (%d x %d) -> (%d x %d) do not match\n", A->nrows,
         A->ncols, B->nrows, B->ncols, C->nrows, C->ncols);
+  if (thin_shape_auto(algo) && C->nrows > 0 && C->ncols > 0 && A->ncols > 0) {
+    // HBM-bound shapes (no product kernel): a few rows of A = v*B (mul_va); a few
+    // columns of B = a batched mat-vec over A (one pass), through two thin transposes
+    if (C->nrows <= 4) {
+      k_mul_va(C, A, B, clear, s);
+      return;
+    }
+    if (C->ncols <= 32 && C->nrows >= 256 && aligned16(A) && aligned16(C)) {
+      DMat *Bt = dmat_new(B->ncols, B->nrows, s), *Y = dmat_new(C->ncols, C->nrows, s);
+      k_transpose(Bt, B, s);
+      k_mul_v_batched(Y, A, Bt, 1, s);
+      if (clear) {
+        k_transpose(C, Y, s);
+      } else {
+        DMat *T = dmat_new(C->nrows, C->ncols, s);
+        k_transpose(T, Y, s);
+        k_add(C, C, T, s);
+        dmat_delete(T, s);
+      }
+      dmat_delete(Bt, s);
+      dmat_delete(Y, s);
+      return;
+    }
+  }
   algo = resolve_algo(algo, C->nrows, A->ncols, C->ncols);
   if (algo == M4RI_B200_ALGO_M4RM) {
     product_with_strassen(C, A, B, clear, algo, 0, cutoff, s);
@@ -395,6 +462,11 @@ static void dmul_abt(DMat *C, const DMat *A, const DMat *Bt, int clear, int algo
   if (A->ncols != Bt->ncols || C->nrows != A->nrows || C->ncols != Bt->nrows)
     die("m4ri_b200: mul (pre-transposed): shapes (%d x %d) * (%d x %d)^T -> (%d x %d) do not match\n",
         A->nrows, A->ncols, Bt->nrows, Bt->ncols, C->nrows, C->ncols);
+  if (thin_shape_auto(algo) && C->nrows > 0 && C->nrows <= 32 && C->ncols >= 256 && A->ncols > 0 &&
+      aligned16(A) && aligned16(Bt)) {
+    k_mul_v_batched(C, Bt, A, clear, s);  // rows of A are a few packed vectors against Bt: one pass over Bt
+    return;
+  }
   algo = resolve_algo(algo, C->nrows, A->ncols, C->ncols);
   if (algo == M4RI_B200_ALGO_MMA) {
     product_with_strassen(C, A, Bt, clear, algo, 1, 0, s);
@@ -479,6 +551,7 @@ static void upload_cols(DMat *D, const mzd_t *H, wi_t w0, wi_t w1, cudaStream_t 
 static void download_block(mzd_t *H, const DMat *D, rci_t r0, rci_t r1, wi_t w0, wi_t w1,
                            cudaStream_t s) {
   if (r1 <= r0 || w1 <= w0) return;
+  if (w1 == H->width && shares_last_word(H)) merge_foreign_excess(H, D, r0, r1, s);
   rci_t i = r0;
   while (i < r1) {
     rci_t j = i + 1;
@@ -660,6 +733,52 @@ static void multi_device_host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, 
   }
 }
 
+// y (^)= A*x for the shapes the reference's mat-vec calls have: BinMatrix::mul_slice passes x as an
+// n x 1 column matrix to mzd_mul_naive (m4ri-rust/src/friendly/binary_matrix.rs:426-427) and gets
+// an m x 1 column back (one word per row). The column is packed on the host (O(n)), A is read
+// once by the HBM-bound mat-vec kernels (kernels_aux.cu: mul_v_*), the packed y is spread over
+// the m one-word rows (O(m)) — no transpose, no 64x64 product tile for one useful column.
+// x_is_row: x is already a packed 1 x n row (the pre-transposed form, _mzd_mul_naive with a
+// one-row Bt).
+static mzd_t *host_matvec(mzd_t *y, const mzd_t *A, const mzd_t *x, int x_is_row, int clear) {
+  const rci_t m = A->nrows, n = A->ncols;
+  cudaStream_t s = current_stream();
+  DMat *dA = dmat_new(m, n, s), *dx = dmat_new(1, n, s), *dy = dmat_new(1, m, s);
+  upload(dA, A, s);
+  const int xw = width_of(n), yw = width_of(m);
+  word *hx = (word *)calloc((size_t)(xw > 0 ? xw : 1), 8), *hy = (word *)calloc((size_t)(yw > 0 ? yw : 1), 8);
+  if (!hx || !hy) die("m4ri_b200: out of memory\n");
+  if (x_is_row) {
+    memcpy(hx, x->rows[0], (size_t)xw * 8);
+    if (xw) hx[xw - 1] &= high_mask(n);
+  } else {
+    for (rci_t j = 0; j < n; j++) hx[j / 64] |= (x->rows[j][0] & 1) << (j % 64);
+  }
+  if (xw) M4B_CUDA(cudaMemcpyAsync(dx->d, hx, (size_t)xw * 8, cudaMemcpyHostToDevice, s));
+  k_mul_v(dy, dA, dx, 1, s);
+  if (yw) M4B_CUDA(cudaMemcpyAsync(hy, dy->d, (size_t)yw * 8, cudaMemcpyDeviceToHost, s));
+  dmat_delete(dA, s);
+  dmat_delete(dx, s);
+  dmat_delete(dy, s);
+  M4B_CUDA(cudaStreamSynchronize(s));
+  // (a window's word also holds the parent's other columns: keep them)
+  const word keep = shares_last_word(y) ? ~(word)1 : 0;
+  if (m > 0 && !keep && clear && y->rows[m - 1] == y->rows[0] + (size_t)(m - 1) * y->rowstride) {
+    // the usual case (a fresh m x 1 result of this library): evenly strided rows, no indirection
+    word *p = y->rows[0];
+    const size_t st = (size_t)y->rowstride;
+    for (rci_t i = 0; i < m; i++) p[i * st] = (hy[i >> 6] >> (i & 63)) & 1;
+  } else {
+    for (rci_t i = 0; i < m; i++) {
+      const word old = y->rows[i][0], bit = (hy[i / 64] >> (i % 64)) & 1;
+      y->rows[i][0] = (old & keep) | ((clear ? bit : (old ^ bit)) & 1);
+    }
+  }
+  free(hx);
+  free(hy);
+  return y;
+}
+
 // Shared body of the host-ABI products. form: 0 = A*B, 1 = A*Bt^T, 2 = v*A.
 static mzd_t *host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int clear, int algo, int form,
                            const char *who, int cutoff = 0) {
@@ -676,6 +795,12 @@ static mzd_t *host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int clear, 
   }
   if (C == A || C == B) die("m4ri_b200: %s: C must not alias an input\n", who);
   cudaStream_t s = current_stream();
+  // The reference's mat-vec shapes never need a product kernel (whatever algorithm the entry
+  // point names — over GF(2) the result is the same):
+  //   A * x, x an n x 1 column (mul_slice, binary_matrix.rs:426-427) or a one-row Bt  -> mul_v_*
+  //   v * A with a few rows of v (Mul<&BinMatrix> for &BinVector, binary_matrix.rs:552-563) -> mul_va
+  if (m > 0 && n == 1 && k > 0 && (form == 0 || form == 1)) return host_matvec(C, A, B, form == 1, clear);
+  if (form == 0 && m > 0 && m <= 4 && n > 0 && k > 0) form = 2;
   if (form != 2 && m > 0 && n > 0 && k > 0 && resolve_algo(algo, m, k, n) == M4RI_B200_ALGO_MMA &&
       ((size_t)m * A->width + (size_t)B->nrows * B->width) * 8 >= PIPELINE_MIN_BYTES) {
     const int G = multi_devices();
@@ -755,23 +880,7 @@ mzd_t *mzd_mul_v(mzd_t *y, const mzd_t *A, const mzd_t *x) {
   if (!y) y = mzd_init_impl(m, 1, 0);
   else if (y->nrows != m || y->ncols != 1)
     die("m4ri_b200: mzd_mul_v: y must be %d x 1\n", m);
-  cudaStream_t s = current_stream();
-  DMat *dA = dmat_new(m, n, s), *dx = dmat_new(1, n, s), *dy = dmat_new(1, m, s);
-  upload(dA, A, s);
-  int xw = width_of(n), yw = width_of(m);
-  word *hx = (word *)calloc((size_t)(xw > 0 ? xw : 1), 8), *hy = (word *)calloc((size_t)(yw > 0 ? yw : 1), 8);
-  for (rci_t j = 0; j < n; j++) hx[j / 64] |= (x->rows[j][0] & 1) << (j % 64);
-  if (xw) M4B_CUDA(cudaMemcpyAsync(dx->d, hx, (size_t)xw * 8, cudaMemcpyHostToDevice, s));
-  k_mul_v(dy, dA, dx, 1, s);
-  if (yw) M4B_CUDA(cudaMemcpyAsync(hy, dy->d, (size_t)yw * 8, cudaMemcpyDeviceToHost, s));
-  dmat_delete(dA, s);
-  dmat_delete(dx, s);
-  dmat_delete(dy, s);
-  M4B_CUDA(cudaStreamSynchronize(s));
-  for (rci_t i = 0; i < m; i++) y->rows[i][0] = (hy[i / 64] >> (i % 64)) & 1;
-  free(hx);
-  free(hy);
-  return y;
+  return host_matvec(y, A, x, 0, 1);
 }
 
 // C = A ^ B on the GPU (the Strassen / addmul "add"; reference mzd_add mzd.rs:223).
@@ -833,7 +942,7 @@ void m4ri_b200_set_devices(int n) { g_devices.store(n < 1 ? 1 : n); }
 int m4ri_b200_get_devices(void) { return multi_devices(); }
 void m4ri_b200_set_sm_limit(int sms) { g_sm_limit.store(sms < 0 ? 0 : (sms & ~1)); }
 void m4ri_b200_set_mma_variant(int variant) {
-  if (variant < 0 || variant > 7) die("m4ri_b200: unknown MMA variant %d\n", variant);
+  if (variant < 0 || variant > 9) die("m4ri_b200: unknown MMA variant %d\n", variant);
   g_mma_variant.store(variant);
 }
 
@@ -901,6 +1010,14 @@ void m4ri_b200_dmul_v(m4ri_b200_dmat_t *y, const m4ri_b200_dmat_t *A, const m4ri
   if (x->nrows != 1 || x->ncols != A->ncols || y->nrows != 1 || y->ncols != A->nrows)
     die("m4ri_b200: dmul_v: x must be 1 x %d and y 1 x %d\n", A->ncols, A->nrows);
   k_mul_v(y, A, x, clear, current_stream());
+}
+void m4ri_b200_dmul_v_batched(m4ri_b200_dmat_t *Y, const m4ri_b200_dmat_t *A, const m4ri_b200_dmat_t *X,
+                              int clear) {
+  if (X->ncols != A->ncols || Y->nrows != X->nrows || Y->ncols != A->nrows)
+    die("m4ri_b200: dmul_v_batched: X must be b x %d and Y b x %d\n", A->ncols, A->nrows);
+  // Y = X * A^T: beyond 32 vectors the contraction is a product for the tensor cores
+  if (X->nrows > 32) dmul_abt(Y, X, A, clear, M4RI_B200_ALGO_AUTO, current_stream());
+  else k_mul_v_batched(Y, A, X, clear, current_stream());
 }
 void m4ri_b200_dmul_va(m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *v, const m4ri_b200_dmat_t *A,
                        int clear) {

@@ -83,6 +83,8 @@ typedef m4ri_b200_dmat DMat;
 // ---- kernels_aux.cu ----------------------------------------------------------
 void k_zero(DMat *M, cudaStream_t s);
 void k_mask_excess(DMat *M, cudaStream_t s);
+// last[i*stride] = (last[i*stride] & keep) | (host_col[i] & ~keep) for i < nrows (window results)
+void k_merge_excess(word *last, int stride, const word *host_col, int nrows, word keep, cudaStream_t s);
 void k_add(DMat *C, const DMat *A, const DMat *B, cudaStream_t s);
 void k_copy(DMat *D, const DMat *A, cudaStream_t s);
 void k_transpose(DMat *D, const DMat *A, cudaStream_t s);
@@ -93,6 +95,8 @@ bool k_is_zero(const DMat *M, cudaStream_t s);
 void k_flip_bit(DMat *M, int r, int c, cudaStream_t s);
 // y (^)= A*x ; x, y packed rows
 void k_mul_v(DMat *y, const DMat *A, const DMat *x, int clear, cudaStream_t s);
+// Y (^)= X*A^T for a few packed vectors (rows of X): one pass over A per 8 vectors
+void k_mul_v_batched(DMat *Y, const DMat *A, const DMat *X, int clear, cudaStream_t s);
 // C (^)= v*A
 void k_mul_va(DMat *C, const DMat *v, const DMat *A, int clear, cudaStream_t s);
 // C (^)= A*Bt^T by AND + popcount parity
@@ -115,6 +119,8 @@ void k_mul_abt_mma4(DMat *C, const DMat *A, const DMat *Bt, int clear, int cg, f
                     cudaStream_t s);
 // ---- kernels_mma5.cu: the same contraction, packed bits by direct global loads
 void k_mul_abt_mma5(DMat *C, const DMat *A, const DMat *Bt, int clear, int cg, cudaStream_t s);
+// ---- kernels_mma6.cu: the same contraction, 256-bit stages x 6, 16 expander + 8 epilogue warps (default)
+void k_mul_abt_mma6(DMat *C, const DMat *A, const DMat *Bt, int clear, int cg, cudaStream_t s);
 bool mma_shape_ok(const DMat *C, const DMat *A, const DMat *Bt);
 bool mma_available();
 

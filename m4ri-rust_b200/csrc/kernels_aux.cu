@@ -12,6 +12,24 @@ namespace m4b {
 
 static inline unsigned cdiv(long long a, long long b) { return (unsigned)((a + b - 1) / b); }
 
+// CTAs of `kernel` (256 threads, no dynamic shared memory) that are resident on the device at
+// once: the grid of the persistent (grid-stride) kernels, so that there is no tail wave.
+template <typename K>
+static long long resident_ctas(K kernel) {
+  static std::atomic<int> cache[64];  // per kernel instantiation and device (0 = not asked yet)
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+  int per_sm = cache[dev].load(std::memory_order_relaxed);
+  if (per_sm == 0) {
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, 256, 0) != cudaSuccess || per_sm < 1) {
+      (void)cudaGetLastError();
+      per_sm = 1;
+    }
+    cache[dev].store(per_sm, std::memory_order_relaxed);
+  }
+  return (long long)sm_count() * per_sm;
+}
+
 // ---------------------------------------------------------------------------
 // zero / mask / copy / add
 // ---------------------------------------------------------------------------
@@ -29,6 +47,16 @@ void k_mask_excess(DMat *M, cudaStream_t s) {
   if (M->ncols % 64 == 0 || M->nrows == 0) return;
   mask_excess_kernel<<<cdiv(M->nrows, 256), 256, 0, s>>>(M->d, M->nrows, M->width, M->rowstride,
                                                           high_mask(M->ncols));
+  M4B_LAUNCHED();
+}
+
+__global__ void merge_excess_kernel(word *last, int stride, const word *col, int nrows, word keep) {
+  int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < nrows) last[(size_t)r * stride] = (last[(size_t)r * stride] & keep) | (col[r] & ~keep);
+}
+void k_merge_excess(word *last, int stride, const word *host_col, int nrows, word keep, cudaStream_t s) {
+  if (nrows <= 0) return;
+  merge_excess_kernel<<<cdiv(nrows, 256), 256, 0, s>>>(last, stride, host_col, nrows, keep);
   M4B_LAUNCHED();
 }
 
@@ -505,41 +533,243 @@ static bool mul_v_force_rows() {  // M4RI_B200_MULV=rows: keep the thread-per-ro
 // j*(32/WV) + l/WV, column l%WV — every 32-byte sector is fetched once, by one request).
 // Lane parities are folded over the WV lanes of a row with shuffles; one more shuffle and one
 // ballot put the 32 row parities in row order = one aligned 32-bit word of y.
-template <int WV, int U /* 32-row groups per warp: U*WV 16-byte loads in flight per lane */>
+template <int WV, int U /* 32-row groups per warp step: U*WV 16-byte loads in flight per lane */>
 __global__ void __launch_bounds__(256)
 mul_v_coal_kernel(uint32_t *__restrict__ y, const ulonglong2 *__restrict__ A,
                   const ulonglong2 *__restrict__ x, long long m, int clear) {
   constexpr int RPI = 32 / WV;  // rows per request
   const int lane = threadIdx.x & 31;
   const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
-  const long long row0 = warp * (32 * U), mpad = (m + 63) & ~63LL;  // y is written in whole 64-bit words
-  if (row0 >= mpad) return;
-  const long long nvec = m * WV, v0 = row0 * WV + lane;
-  ulonglong2 a[U * WV];
-#pragma unroll
-  for (int j = 0; j < U * WV; j++) {
-    a[j] = make_ulonglong2(0, 0);
-    if (v0 + j * 32 < nvec)
-      asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0,%1}, [%2];"
-                   : "=l"(a[j].x), "=l"(a[j].y) : "l"(A + v0 + j * 32));
-  }
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  const long long mpad = (m + 63) & ~63LL;  // y is written in whole 64-bit words
+  const long long nvec = m * WV;
   const ulonglong2 b = __ldg(&x[lane % WV]);
-  unsigned v = 0;  // bit j = parity of this lane's vector of request j
+  // persistent: the grid is one wave of resident CTAs (no tail wave), every warp strides over
+  // the 32*U-row steps
+  for (long long row0 = warp * (32 * U); row0 < mpad; row0 += nwarps * (32 * U)) {
+    const long long v0 = row0 * WV + lane;
+    ulonglong2 a[U * WV];
 #pragma unroll
-  for (int j = 0; j < U * WV; j++)
-    v |= (unsigned)(__popcll((a[j].x & b.x) ^ (a[j].y & b.y)) & 1) << j;
+    for (int j = 0; j < U * WV; j++) {
+      a[j] = make_ulonglong2(0, 0);
+      if (v0 + j * 32 < nvec)
+        asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0,%1}, [%2];"
+                     : "=l"(a[j].x), "=l"(a[j].y) : "l"(A + v0 + j * 32));
+    }
+    unsigned v = 0;  // bit j = parity of this lane's vector of request j
 #pragma unroll
-  for (int o = 1; o < WV; o <<= 1) v ^= __shfl_xor_sync(0xffffffffu, v, o);
-  // row r (0..31) of group u: request u*WV + r / RPI, lanes (r % RPI)*WV ...
-  const unsigned t = __shfl_sync(0xffffffffu, v, (lane % RPI) * WV) >> (lane / RPI);
+    for (int j = 0; j < U * WV; j++)
+      v |= (unsigned)(__popcll((a[j].x & b.x) ^ (a[j].y & b.y)) & 1) << j;
 #pragma unroll
-  for (int u = 0; u < U; u++) {
-    const unsigned bits = __ballot_sync(0xffffffffu, (t >> (u * WV)) & 1u);
-    if (lane == 0 && row0 + u * 32 < mpad) {
-      uint32_t *dst = y + ((row0 >> 5) + u);
-      *dst = clear ? bits : (*dst ^ bits);
+    for (int o = 1; o < WV; o <<= 1) v ^= __shfl_xor_sync(0xffffffffu, v, o);
+    // row r (0..31) of group u: request u*WV + r / RPI, lanes (r % RPI)*WV ...
+    const unsigned t = __shfl_sync(0xffffffffu, v, (lane % RPI) * WV) >> (lane / RPI);
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const unsigned bits = __ballot_sync(0xffffffffu, (t >> (u * WV)) & 1u);
+      if (lane == 0 && row0 + u * 32 < mpad) {
+        uint32_t *dst = y + ((row0 >> 5) + u);
+        *dst = clear ? bits : (*dst ^ bits);
+      }
     }
   }
+}
+
+// ---------------------------------------------------------------------------
+// batched mat-vec: Y (^)= X * A^T, i.e. row q of Y (packed, nrows(A) bits) = A * x_q for the
+// nb <= BB packed vectors x_q = rows of X — ONE pass over A for all of them (the LPN workload's
+// "batched mzd_mul_v", BASELINE configs[4]). HBM-bound like the single mat-vec: algorithmic
+// bytes = 8 * (m*width + nb*width) + nb * ceil(m/64)*8.
+// ---------------------------------------------------------------------------
+// acc ^= (a & b), folded to 32 bits: one LOP3 per 32-bit word
+__device__ __forceinline__ unsigned and_xor_fold(unsigned acc, const ulonglong2 &a, const ulonglong2 &b) {
+  acc ^= (unsigned)a.x & (unsigned)b.x;
+  acc ^= (unsigned)(a.x >> 32) & (unsigned)(b.x >> 32);
+  acc ^= (unsigned)a.y & (unsigned)b.y;
+  acc ^= (unsigned)(a.y >> 32) & (unsigned)(b.y >> 32);
+  return acc;
+}
+
+// Short rows stored back to back (row stride == row length = WV 16-byte vectors): one THREAD per
+// row. The row is read with 32-byte loads (whole sectors: no sector is fetched twice although
+// neighbouring threads are WV*16 bytes apart), the BB vectors sit in shared memory and are read
+// as broadcasts; per 32-bit word of the row and vector one LOP3 (acc ^= a & x) — the integer
+// pipe, not HBM, is what bounds eight vectors per pass (128 LOP3 per 64-byte row). BB ballots
+// turn the 32 rows x BB parities of a warp into one 32-bit word of every Y row.
+template <int WV, int BB>
+__global__ void __launch_bounds__(256)
+mul_vb_rows_kernel(uint32_t *__restrict__ y, long long ys32, const ulonglong2 *__restrict__ A,
+                   const ulonglong2 *__restrict__ X, int xs, long long m, int nb, int clear) {
+  constexpr int RPT = 2;  // rows per thread: a warp owns 64 rows (rows base + lane and base + 32 + lane);
+                          // every broadcast read of a vector word feeds two rows
+  __shared__ ulonglong2 xsm[BB][WV];
+  for (int i = threadIdx.x; i < BB * WV; i += 256) {
+    const int q = i / WV, w = i % WV;
+    xsm[q][w] = q < nb ? X[(size_t)q * xs + w] : make_ulonglong2(0, 0);
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  // (no grid-stride loop: with one the compiler hoists the BB*WV vector loads out of it into
+  // 128 registers and the occupancy collapses)
+  const long long base = (blockIdx.x * 8LL + (threadIdx.x >> 5)) * (32 * RPT);  // first row of the warp
+  if (base >= ((m + 63) & ~63LL)) return;
+  ulonglong2 a[RPT][WV];
+#pragma unroll
+  for (int j = 0; j < RPT; j++) {
+    const long long row = base + 32 * j + lane;
+    if (row < m) {
+      const ulonglong2 *ar = A + row * WV;
+      if constexpr (WV % 2 == 0) {
+#pragma unroll
+        for (int w = 0; w < WV; w += 2)
+          asm volatile("ld.global.nc.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];"
+                       : "=l"(a[j][w].x), "=l"(a[j][w].y), "=l"(a[j][w + 1].x), "=l"(a[j][w + 1].y) : "l"(ar + w));
+      } else {
+#pragma unroll
+        for (int w = 0; w < WV; w++)
+          asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0,%1}, [%2];" : "=l"(a[j][w].x), "=l"(a[j][w].y) : "l"(ar + w));
+      }
+    } else {
+#pragma unroll
+      for (int w = 0; w < WV; w++) a[j][w] = make_ulonglong2(0, 0);
+    }
+  }
+  unsigned mine[RPT];
+#pragma unroll
+  for (int j = 0; j < RPT; j++) mine[j] = 0;
+#pragma unroll
+  for (int q = 0; q < BB; q++) {
+    unsigned acc[RPT];
+#pragma unroll
+    for (int j = 0; j < RPT; j++) acc[j] = 0;
+#pragma unroll
+    for (int w = 0; w < WV; w++) {
+      const ulonglong2 xv = xsm[q][w];
+#pragma unroll
+      for (int j = 0; j < RPT; j++) acc[j] = and_xor_fold(acc[j], a[j][w], xv);
+    }
+#pragma unroll
+    for (int j = 0; j < RPT; j++) mine[j] |= (__popc(acc[j]) & 1u) << q;
+  }
+  // the warp's 64 rows are whole 64-bit words of y (m is padded to 64 for the store): lane q
+  // stores the two 32-bit words of Y row q
+#pragma unroll
+  for (int j = 0; j < RPT; j++) {
+    unsigned mybits = 0;
+#pragma unroll
+    for (int q = 0; q < BB; q++) {
+      const unsigned bits = __ballot_sync(0xffffffffu, (mine[j] >> q) & 1u);
+      if (lane == q) mybits = bits;
+    }
+    if (lane < nb) {
+      uint32_t *dst = y + (size_t)lane * ys32 + ((base >> 5) + j);
+      *dst = clear ? mybits : (*dst ^ mybits);
+    }
+  }
+}
+
+// Any row length and stride: a CTA of 4 warps owns 32 consecutive rows (one aligned 32-bit word of
+// every Y row), a warp walks its 8 rows together: per step nb 16-byte loads of the vectors (L1
+// resident) feed 8 independent 16-byte loads of A.
+template <int BB>
+__global__ void __launch_bounds__(128)
+mul_vb_long_kernel(uint32_t *__restrict__ y, long long ys32, const ulonglong2 *__restrict__ A,
+                   const ulonglong2 *__restrict__ X, int xs, int m, int wv, int as, int nb, int clear) {
+  constexpr int R = 8;
+  __shared__ unsigned sbits[4][BB];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const long long row0 = blockIdx.x * 32LL + w * R;
+  const ulonglong2 *ar[R];
+#pragma unroll
+  for (int r = 0; r < R; r++) {
+    const long long row = row0 + r < m ? row0 + r : m - 1;  // rows past m: read a valid row, drop the bits
+    ar[r] = A + (size_t)row * as;
+  }
+  unsigned acc[R][BB];
+#pragma unroll
+  for (int r = 0; r < R; r++)
+#pragma unroll
+    for (int q = 0; q < BB; q++) acc[r][q] = 0;
+  for (int v = lane; v < wv; v += 32) {
+    ulonglong2 a[R];
+#pragma unroll
+    for (int r = 0; r < R; r++)
+      asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0,%1}, [%2];" : "=l"(a[r].x), "=l"(a[r].y) : "l"(ar[r] + v));
+#pragma unroll
+    for (int q = 0; q < BB; q++) {
+      if (q < nb) {
+        const ulonglong2 b = __ldg(&X[(size_t)q * xs + v]);
+#pragma unroll
+        for (int r = 0; r < R; r++) acc[r][q] = and_xor_fold(acc[r][q], a[r], b);
+      }
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < BB; q++) {
+    unsigned bits = 0;
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      const unsigned ball = __ballot_sync(0xffffffffu, __popc(acc[r][q]) & 1);
+      if (row0 + r < m) bits |= (unsigned)(__popc(ball) & 1) << r;
+    }
+    if (lane == 0) sbits[w][q] = bits;
+  }
+  __syncthreads();
+  if (threadIdx.x < nb) {
+    unsigned word32 = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) word32 |= sbits[i][threadIdx.x] << (R * i);
+    uint32_t *dst = y + (size_t)threadIdx.x * ys32 + blockIdx.x;
+    *dst = clear ? word32 : (*dst ^ word32);
+  }
+}
+
+template <int BB>
+static void launch_mul_vb(uint32_t *yy, long long ys32, const DMat *A, const ulonglong2 *xx, int xs, int nb,
+                          int clear, cudaStream_t s) {
+  const int wv = (A->width + 1) / 2, as = A->rowstride / 2, mm = A->nrows;
+  const ulonglong2 *AA = (const ulonglong2 *)A->d;
+  if (wv <= 8 && as == wv && (wv & (wv - 1)) == 0 && (wv == 1 || !((uintptr_t)A->d & 31))) {
+    const unsigned grid = cdiv(((long long)mm + 63) / 64 * 64, 512);  // 8 warps x 64 rows
+    switch (wv) {
+      case 1: mul_vb_rows_kernel<1, BB><<<grid, 256, 0, s>>>(yy, ys32, AA, xx, xs, mm, nb, clear); break;
+      case 2: mul_vb_rows_kernel<2, BB><<<grid, 256, 0, s>>>(yy, ys32, AA, xx, xs, mm, nb, clear); break;
+      case 4: mul_vb_rows_kernel<4, BB><<<grid, 256, 0, s>>>(yy, ys32, AA, xx, xs, mm, nb, clear); break;
+      default: mul_vb_rows_kernel<8, BB><<<grid, 256, 0, s>>>(yy, ys32, AA, xx, xs, mm, nb, clear); break;
+    }
+  } else {
+    const unsigned grid = cdiv(((long long)mm + 63) / 64 * 64, 32);  // whole 64-bit words of y
+    mul_vb_long_kernel<BB><<<grid, 128, 0, s>>>(yy, ys32, AA, xx, xs, mm, wv, as, nb, clear);
+  }
+  M4B_LAUNCHED();
+}
+
+// Y (b x m) (^)= X (b x n) * A (m x n)^T, b small: passes of up to 8 vectors, each one read of A
+void k_mul_v_batched(DMat *Y, const DMat *A, const DMat *X, int clear, cudaStream_t s) {
+  const int b = X->nrows;
+  if (b == 0 || A->nrows == 0) return;
+  if (A->ncols == 0) {
+    if (clear) k_zero(Y, s);
+    return;
+  }
+  if (A->rowstride % 2 || ((uintptr_t)A->d % 16) || ((uintptr_t)X->d % 16) || X->rowstride % 2)
+    die("m4ri_b200: batched mul_v needs 16-byte aligned rows\n");
+  if (b == 1) {  // the single-vector kernels
+    DMat y1 = *Y, x1 = *X;
+    y1.base = x1.base = nullptr;
+    k_mul_v(&y1, A, &x1, clear, s);
+    return;
+  }
+  timing_begin("mul_vb_kernel", s, 2.0 * A->nrows * (double)A->ncols * b);
+  for (int q0 = 0; q0 < b; q0 += 8) {
+    const int nb = b - q0 < 8 ? b - q0 : 8;
+    uint32_t *yy = (uint32_t *)(Y->d + (size_t)q0 * Y->rowstride);
+    const ulonglong2 *xx = (const ulonglong2 *)(X->d + (size_t)q0 * X->rowstride);
+    if (nb <= 2) launch_mul_vb<2>(yy, Y->rowstride * 2LL, A, xx, X->rowstride / 2, nb, clear, s);
+    else if (nb <= 4) launch_mul_vb<4>(yy, Y->rowstride * 2LL, A, xx, X->rowstride / 2, nb, clear, s);
+    else launch_mul_vb<8>(yy, Y->rowstride * 2LL, A, xx, X->rowstride / 2, nb, clear, s);
+  }
+  timing_end(s);
 }
 
 void k_mul_v(DMat *y, const DMat *A, const DMat *x, int clear, cudaStream_t s) {
@@ -551,6 +781,7 @@ void k_mul_v(DMat *y, const DMat *A, const DMat *x, int clear, cudaStream_t s) {
     die("m4ri_b200: mul_v needs 16-byte aligned rows\n");
   // x is read in 16-byte vectors up to ceil(width/2): its row is padded to an even stride.
   int wv = (A->width + 1) / 2, as = A->rowstride / 2;
+  const double ops = 2.0 * A->nrows * (double)A->ncols;
   if (wv <= 8) {  // thread per row; the last 64-bit word of y (rows past m) is written whole
     unsigned grid = cdiv(((long long)A->nrows + 63) / 64 * 64, 256);
     uint32_t *yy = (uint32_t *)y->d;
@@ -558,15 +789,26 @@ void k_mul_v(DMat *y, const DMat *A, const DMat *x, int clear, cudaStream_t s) {
     const int mm = A->nrows;
     if (as == wv && (wv & (wv - 1)) == 0 && !mul_v_force_rows()) {  // rows back to back: coalesced warp-per-32-rows kernel
       const long long groups = ((long long)mm + 63) / 64 * 2;  // 32-row groups
+      // one wave of resident CTAs, grid-stride inside the kernel: no tail wave
+      // M4RI_B200_MULV_WAVES=w: cap the grid at w waves of resident CTAs (grid-stride loop inside the
+      // kernel); 0 = one CTA per 8 x 32U rows (every warp runs one step)
+      static const int waves = getenv("M4RI_B200_MULV_WAVES") ? atoi(getenv("M4RI_B200_MULV_WAVES")) : 0;
+      auto grid_of = [&](int U, long long cap) {
+        const long long all = cdiv(cdiv(groups, U), 8);
+        return (unsigned)(waves > 0 ? min(all, cap * waves) : all);
+      };
+      timing_begin("mul_v_coal_kernel", s, ops);
       switch (wv) {
-        case 1: mul_v_coal_kernel<1, 8><<<cdiv(cdiv(groups, 8), 8), 256, 0, s>>>(yy, AA, xx, mm, clear); break;
-        case 2: mul_v_coal_kernel<2, 4><<<cdiv(cdiv(groups, 4), 8), 256, 0, s>>>(yy, AA, xx, mm, clear); break;
-        case 4: mul_v_coal_kernel<4, 2><<<cdiv(cdiv(groups, 2), 8), 256, 0, s>>>(yy, AA, xx, mm, clear); break;
-        default: mul_v_coal_kernel<8, 1><<<cdiv(groups, 8), 256, 0, s>>>(yy, AA, xx, mm, clear); break;
+        case 1: mul_v_coal_kernel<1, 8><<<grid_of(8, resident_ctas(mul_v_coal_kernel<1, 8>)), 256, 0, s>>>(yy, AA, xx, mm, clear); break;
+        case 2: mul_v_coal_kernel<2, 4><<<grid_of(4, resident_ctas(mul_v_coal_kernel<2, 4>)), 256, 0, s>>>(yy, AA, xx, mm, clear); break;
+        case 4: mul_v_coal_kernel<4, 2><<<grid_of(2, resident_ctas(mul_v_coal_kernel<4, 2>)), 256, 0, s>>>(yy, AA, xx, mm, clear); break;
+        default: mul_v_coal_kernel<8, 1><<<grid_of(1, resident_ctas(mul_v_coal_kernel<8, 1>)), 256, 0, s>>>(yy, AA, xx, mm, clear); break;
       }
       M4B_LAUNCHED();
+      timing_end(s);
       return;
     }
+    timing_begin("mul_v_rows_kernel", s, ops);
     switch (wv) {
       case 1: mul_v_rows_kernel<1><<<grid, 256, 0, s>>>(yy, AA, xx, mm, as, clear); break;
       case 2: mul_v_rows_kernel<2><<<grid, 256, 0, s>>>(yy, AA, xx, mm, as, clear); break;
@@ -578,14 +820,17 @@ void k_mul_v(DMat *y, const DMat *A, const DMat *x, int clear, cudaStream_t s) {
       default: mul_v_rows_kernel<8><<<grid, 256, 0, s>>>(yy, AA, xx, mm, as, clear); break;
     }
     M4B_LAUNCHED();
+    timing_end(s);
     return;
   }
   if (wv >= 32 && A->nrows >= 2048 && !mul_v_force_rows()) {
     // whole 64-bit words of y: an even number of 32-row CTAs
     unsigned grid = cdiv(((long long)A->nrows + 63) / 64 * 64, 32);
+    timing_begin("mul_v_long_kernel", s, ops);
     mul_v_long_kernel<<<grid, 256, 0, s>>>((uint32_t *)y->d, (const ulonglong2 *)A->d,
                                            (const ulonglong2 *)x->d, A->nrows, wv, as, clear);
     M4B_LAUNCHED();
+    timing_end(s);
     return;
   }
   if (clear) k_zero(y, s);
@@ -594,6 +839,7 @@ void k_mul_v(DMat *y, const DMat *A, const DMat *x, int clear, cudaStream_t s) {
   unsigned grid = cdiv(warps * 32, 256);
   uint32_t *yy = (uint32_t *)y->d;
   const ulonglong2 *AA = (const ulonglong2 *)A->d, *xx = (const ulonglong2 *)x->d;
+  timing_begin("mul_v_kernel", s, ops);
   switch (G) {
     case 32: mul_v_kernel<32><<<grid, 256, 0, s>>>(yy, AA, xx, A->nrows, wv, as); break;
     case 16: mul_v_kernel<16><<<grid, 256, 0, s>>>(yy, AA, xx, A->nrows, wv, as); break;
@@ -603,6 +849,7 @@ void k_mul_v(DMat *y, const DMat *A, const DMat *x, int clear, cudaStream_t s) {
     default: mul_v_kernel<1><<<grid, 256, 0, s>>>(yy, AA, xx, A->nrows, wv, as); break;
   }
   M4B_LAUNCHED();
+  timing_end(s);
 }
 
 // ---------------------------------------------------------------------------
@@ -635,9 +882,11 @@ void k_mul_va(DMat *C, const DMat *v, const DMat *A, int clear, cudaStream_t s) 
   if (clear) k_zero(C, s);
   if (v->nrows == 0 || A->nrows == 0 || A->ncols == 0) return;
   dim3 grid(cdiv(A->width, 256), cdiv(A->nrows, VA_ROWS), v->nrows);
+  timing_begin("mul_va_kernel", s, 2.0 * v->nrows * (double)A->nrows * A->ncols);
   mul_va_kernel<<<grid, 256, 0, s>>>(C->d, v->d, A->d, A->nrows, A->width, C->rowstride,
                                      v->rowstride, A->rowstride);
   M4B_LAUNCHED();
+  timing_end(s);
 }
 
 // ---------------------------------------------------------------------------

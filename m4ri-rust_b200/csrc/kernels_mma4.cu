@@ -341,7 +341,11 @@ static void launch_mma4(DMat *C, const DMat *A, const DMat *Bt, int clear, float
   const int ntiles = tiles_m * tiles_n;
   int nclusters = sm_count() / CG;
   if (nclusters > ntiles) nclusters = ntiles;
-  static const int dbg = getenv("M4RI_B200_DBG") ? atoi(getenv("M4RI_B200_DBG")) : 0;  // perf experiments only
+#ifdef M4RI_B200_PERF_HOOKS
+  static const int dbg = getenv("M4RI_B200_DBG") ? atoi(getenv("M4RI_B200_DBG")) : 0;  // perf-hook builds only (build.py --perf)
+#else
+  const int dbg = 0;  // the shipped library never lets the environment alter results
+#endif
   for (int k0 = 0; k0 < A->ncols; k0 += K_CHUNK_MAX) {
     const int kc = A->ncols - k0 < K_CHUNK_MAX ? A->ncols - k0 : K_CHUNK_MAX;
     const CUtensorMap tmA = packed_rows_map(A->d + k0 / 64, A->nrows, width_of(kc), A->rowstride);

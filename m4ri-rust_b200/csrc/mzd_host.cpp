@@ -27,6 +27,10 @@ static_assert(offsetof(mzd_t, high_bitmask) == 40 && offsetof(mzd_t, blocks) == 
 namespace m4b {
 // how a matrix's words were allocated, kept in mzd_t::padding[0]
 enum : uint8_t { ALLOC_NONE = 0, ALLOC_MALLOC = 0xA1, ALLOC_PINNED = 0xA2 };
+// padding[9] of every descriptor this library creates: mzd_free refuses anything else (a matrix
+// allocated by another M4RI in the same process must be freed by that library — mixing
+// allocators is unsupported)
+constexpr uint8_t DESC_MAGIC = 0x5B;
 // Matrices at least this large get page-locked memory so the H2D/D2H copies of a
 // product run at full PCIe rate; small ones (the reference's tests create
 // thousands of 10x10 matrices) stay in ordinary memory.
@@ -177,6 +181,7 @@ mzd_t *m4b::mzd_init_impl(rci_t r, rci_t c, int zero) {
   A->padding[0] = kind;
   // capacity of the block (>= the bytes in use) in padding[1..8]: mzd_free returns it to the cache
   memcpy(&A->padding[1], &cap, sizeof(cap));
+  A->padding[9] = DESC_MAGIC;
   A->blocks[0].size = bytes;
   A->blocks[0].begin = data;
   A->blocks[0].end = data + words;
@@ -188,6 +193,10 @@ extern "C" {
 
 void mzd_free(mzd_t *A) {
   if (!A) return;
+  if (A->padding[9] != DESC_MAGIC ||
+      (A->padding[0] != ALLOC_NONE && A->padding[0] != ALLOC_MALLOC && A->padding[0] != ALLOC_PINNED))
+    die("m4ri_b200: mzd_free: this mzd_t was not created by libm4ri_b200 (mixing M4RI allocators in "
+        "one process is unsupported)\n");
   if (A->blocks && A->padding[0] != ALLOC_NONE) {
     size_t cap = 0;
     memcpy(&cap, &A->padding[1], sizeof(cap));
@@ -217,10 +226,57 @@ mzd_t *mzd_init_window(mzd_t *M, rci_t lowr, rci_t lowc, rci_t highr, rci_t high
   W->offset_vector = M->offset_vector + lowr * M->rowstride + lowc / 64;
   W->blocks = M->blocks;  // shared, not owned
   W->padding[0] = ALLOC_NONE;
+  W->padding[9] = DESC_MAGIC;
   W->rows = (word **)calloc((size_t)(W->nrows > 0 ? W->nrows : 1), sizeof(word *));
   if (!W->rows) die("m4ri_b200: out of memory\n");
   for (rci_t i = 0; i < W->nrows; i++) W->rows[i] = M->rows[lowr + i] + lowc / 64;
   return W;
+}
+
+// bits [0, ncols) of src appended to dst starting at bit column c0 (dst bits there are zero)
+static void append_bits(word *dst, rci_t c0, const word *src, rci_t ncols, word src_mask) {
+  const wi_t sw = (ncols + 63) / 64;
+  const int sh = c0 % 64;
+  word *d = dst + c0 / 64;
+  for (wi_t w = 0; w < sw; w++) {
+    const word v = (w == sw - 1) ? (src[w] & src_mask) : src[w];
+    d[w] |= v << sh;
+    if (sh && (w < sw - 1 || (ncols - 1) % 64 + sh >= 64)) d[w + 1] |= v >> (64 - sh);
+  }
+}
+
+// C = [A B] (mzd.rs:195; BinMatrix::augmented, binary_matrix.rs:221-231). O(size) host copy.
+mzd_t *mzd_concat(mzd_t *C, const mzd_t *A, const mzd_t *B) {
+  if (A->nrows != B->nrows) die("m4ri_b200: mzd_concat: bad arguments to concat\n");
+  if (!C) C = mzd_init(A->nrows, A->ncols + B->ncols);
+  else if (C->nrows != A->nrows || C->ncols != A->ncols + B->ncols)
+    die("m4ri_b200: mzd_concat: C has wrong dimension\n");
+  for (rci_t i = 0; i < A->nrows; i++) {
+    word *dst = C->rows[i];
+    memset(dst, 0, sizeof(word) * (size_t)C->width);
+    if (A->width) {
+      memcpy(dst, A->rows[i], sizeof(word) * (size_t)A->width);
+      dst[A->width - 1] &= A->high_bitmask;
+    }
+    if (B->width) append_bits(dst, A->ncols, B->rows[i], B->ncols, B->high_bitmask);
+  }
+  return C;
+}
+
+// C = [A; B] (mzd.rs:201; BinMatrix::stacked, binary_matrix.rs:234-244). O(size) host copy.
+mzd_t *mzd_stack(mzd_t *C, const mzd_t *A, const mzd_t *B) {
+  if (A->ncols != B->ncols) die("m4ri_b200: mzd_stack: A->ncols != B->ncols!\n");
+  if (!C) C = mzd_init(A->nrows + B->nrows, A->ncols);
+  else if (C->nrows != A->nrows + B->nrows || C->ncols != A->ncols)
+    die("m4ri_b200: mzd_stack: C has wrong dimension!\n");
+  for (rci_t i = 0; i < C->nrows; i++) {
+    const mzd_t *S = i < A->nrows ? A : B;
+    const word *src = S->rows[i < A->nrows ? i : i - A->nrows];
+    if (!C->width) continue;
+    memcpy(C->rows[i], src, sizeof(word) * (size_t)C->width);
+    C->rows[i][C->width - 1] &= C->high_bitmask;
+  }
+  return C;
 }
 
 mzd_t *mzd_copy(mzd_t *N, const mzd_t *P) {

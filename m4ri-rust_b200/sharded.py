@@ -111,6 +111,9 @@ def gpu_chunk_product(m4, tA, tB, tC, rows, k, n, algo=0):
     cache = {}
 
     def product(i, k0, k1, clear):
+        # works[i].wait() orders NCCL's stream before torch's current stream: issue the product there
+        import ctypes
+        m4.lib().m4ri_b200_set_stream(ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
         if i not in cache:
             if k0 % 128:
                 raise ValueError("k-chunk boundaries must be multiples of 128 bits")
@@ -186,6 +189,10 @@ class FusedBroadcastMul:
             self.dst_arr = (ctypes.c_void_p * self.world)(*[d.h for d in self.dDst])
 
     def step(self, algo=0):
+        # the symmetric-memory barriers run on torch's current stream: the library must issue the
+        # scatter and the product on that same stream or the barriers order nothing
+        import ctypes
+        self.L.m4ri_b200_set_stream(ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
         self.hBt.barrier(channel=0)  # every rank is done reading its Bt of the previous step
         if self.srows > 0:
             self.L.m4ri_b200_dtranspose_scatter(self.dst_arr, self.world, self.dSlab.h)

@@ -222,3 +222,51 @@ def test_allocator_is_thread_safe():
         t.join()
     assert not errors, errors[:3]
     L.m4ri_b200_host_cache_trim()
+
+
+def _bits(m4, p):
+    m = p.contents
+    return np.array([[(int(m.rows[r][c // 64]) >> (c % 64)) & 1 for c in range(m.ncols)] for r in range(m.nrows)],
+                    dtype=np.uint8).reshape(m.nrows, m.ncols)
+
+
+def test_concat_and_stack(m4):
+    """mzd_concat / mzd_stack (mzd.rs:195,201; BinMatrix::augmented / stacked,
+    binary_matrix.rs:221-244): host copies at arbitrary bit offsets, NULL and preallocated C."""
+    L = m4.lib()
+    for (r, ca, cb) in [(5, 3, 4), (7, 64, 64), (9, 70, 130), (4, 1, 200), (3, 127, 1), (6, 128, 65), (2, 200, 300)]:
+        a, b = L.mzd_init(r, ca), L.mzd_init(r, cb)
+        L.mzd_randomize(a)
+        L.mzd_randomize(b)
+        c = L.mzd_concat(None, a, b)
+        assert (c.contents.nrows, c.contents.ncols) == (r, ca + cb)
+        want = np.concatenate([_bits(m4, a), _bits(m4, b)], axis=1)
+        assert (_bits(m4, c) == want).all(), (r, ca, cb)
+        w = m4.mzd_words(c)
+        assert not (w[:, c.contents.width - 1] & ~np.uint64(c.contents.high_bitmask)).any()
+        assert not w[:, c.contents.width:].any()
+        c2 = L.mzd_init(r, ca + cb)
+        L.mzd_randomize(c2)  # stale contents are overwritten
+        assert ctypes.addressof(L.mzd_concat(c2, a, b).contents) == ctypes.addressof(c2.contents)
+        assert L.mzd_equal(c, c2) == 1
+        for p in (a, b, c, c2):
+            L.mzd_free(p)
+    for (ra, rb, c_) in [(3, 4, 5), (1, 1, 64), (10, 20, 130), (7, 2, 200)]:
+        a, b = L.mzd_init(ra, c_), L.mzd_init(rb, c_)
+        L.mzd_randomize(a)
+        L.mzd_randomize(b)
+        s = L.mzd_stack(None, a, b)
+        assert (s.contents.nrows, s.contents.ncols) == (ra + rb, c_)
+        assert (_bits(m4, s) == np.concatenate([_bits(m4, a), _bits(m4, b)], axis=0)).all()
+        for p in (a, b, s):
+            L.mzd_free(p)
+
+
+def test_free_rejects_foreign_descriptors(m4):
+    """A descriptor this library did not create (e.g. from another M4RI in the process) must not
+    reach free()/cudaFreeHost: mzd_free dies loudly instead."""
+    code = ("import sys; sys.path.insert(0, %r); import ctypes, m4ri_rust_b200 as m4; L = m4.lib();"
+            "p = L.mzd_init(4, 4); q = m4.Mzd(); ctypes.memmove(ctypes.byref(q), p, 64);"
+            "q.padding[9] = 0; L.mzd_free(ctypes.pointer(q))") % ROOT
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True)
+    assert r.returncode != 0 and "not created by libm4ri_b200" in r.stderr

@@ -34,3 +34,18 @@ def test_reference_arm_line():
 
 def test_reference_arm_other_ranks_are_silent():
     assert run({"RANK": "1", "LOCAL_RANK": "1", "WORLD_SIZE": "2"}) == ""
+
+
+def test_reference_arm_ignores_torchrun_thread_cap():
+    """torchrun exports OMP_NUM_THREADS=1: the arm must still use every core it may run on and
+    the same sample (round 1's N > 1 reference lines were one-thread runs on a smaller cube)."""
+    import ast
+    free = json.loads(run().splitlines()[-1])
+    capped = json.loads(run({"OMP_NUM_THREADS": "1", "RANK": "0", "LOCAL_RANK": "0", "WORLD_SIZE": "2"}).splitlines()[-1])
+    cores = len(os.sched_getaffinity(0))
+    assert free["cpu_baseline"]["cores"] == capped["cpu_baseline"]["cores"] == cores
+    assert capped["config"]["cpu_threads"] == cores
+    for k in ("strassen", "m4rm"):
+        assert free["cpu_baseline"]["strategies"][k]["sample"] == capped["cpu_baseline"]["strategies"][k]["sample"]
+    if cores > 1:  # a one-thread run would be several times slower
+        assert capped["value"] > 0.4 * free["value"]

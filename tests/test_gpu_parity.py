@@ -414,7 +414,7 @@ VARIANT_SWEEP = [(1, 1, 1), (2, 63, 65), (65, 64, 64), (191, 193, 129), (200, 25
                  (1030, 40, 1030), (257, 2050, 1500), (256, 4096, 128), (300, 512, 300), (129, 1536, 257)]
 
 
-@pytest.mark.parametrize("variant", ["v1", "v2cg1", "v2", "fp4cg1", "fp4", "fp4ldgcg1", "fp4ldg"])
+@pytest.mark.parametrize("variant", ["v1", "v2cg1", "v2", "fp4cg1", "fp4", "fp4ldgcg1", "fp4ldg", "fp4s256cg1", "fp4s256"])
 def test_every_tensor_kernel_variant(gpu, m4, orc, variant):
     """Each kernel behind ALGO_MMA (int8 SS, int8 TS single/pair, FP4 with TMA staging
     single/pair, FP4 with direct global loads single/pair) is bit-exact on ragged shapes,
@@ -505,3 +505,111 @@ def test_multi_device_host_products(gpu, m4, orc):
         L.m4ri_b200_set_devices(1)
     for p in (a, b):
         L.mzd_free(p)
+
+
+def test_fp4_accumulators_exact_on_dense_operands(gpu, m4, orc):
+    """the FP4 path is only correct if fp32 accumulation of 0.25-steps is exact up to
+    the largest sum the wrapper allows (k = 65536 -> 16384.0, 17 significant bits). All-ones
+    operands only ever add 16.0 per MMA and 50 % random ones stay below 4200: here near-dense
+    operands (all ones with random holes at densities 0.9 ... 0.999, and rows whose per-word
+    popcounts are odd) put the accumulators between 4197 and 16384 with odd quarter increments.
+    Both the raw fp32 accumulators (mma4 debug entry) and the parities of the default kernel are
+    compared with exact integer arithmetic."""
+    import torch
+    L = m4.lib()
+    k = 65536
+    kw = k // 64
+    rng = np.random.default_rng(7)
+    ones = np.uint64(0xFFFFFFFFFFFFFFFF)
+
+    def dense(rows, density, seed):
+        r = np.random.default_rng(seed)
+        bits = (r.random((rows, k)) < density).astype(np.uint8)
+        return np.packbits(bits, axis=1, bitorder="little").view(np.uint64).reshape(rows, kw).copy()
+
+    def odd_words(rows, seed):
+        # every 64-bit word has an odd popcount: all ones with one hole at a random position
+        r = np.random.default_rng(seed)
+        return ones ^ (np.uint64(1) << r.integers(0, 64, size=(rows, kw)).astype(np.uint64))
+
+    cases = [(dense(256, 0.9, 1), dense(256, 0.95, 2)), (dense(256, 0.99, 3), dense(256, 0.999, 4)),
+             (odd_words(256, 5), odd_words(256, 6)), (dense(256, 0.999, 8), np.full((256, kw), ones))]
+    for ci, (A, B) in enumerate(cases):
+        a8 = np.unpackbits(A.view(np.uint8), axis=1, bitorder="little").astype(np.float64)
+        b8 = np.unpackbits(B.view(np.uint8), axis=1, bitorder="little").astype(np.float64)
+        pc = (a8 @ b8.T)  # exact in float64 (<= 65536)
+        assert pc.max() > 4197 * 4, "the case must exercise accumulators beyond the 50 %-random range"
+        a, b = host(m4, A, k), host(m4, B, k)
+        dA, dB, dC = m4.DMat.from_host(a), m4.DMat.from_host(b), m4.DMat.init(256, 256)
+        for cg in (1, 2):
+            acc = torch.full((256, 256), -1.0, dtype=torch.float32, device="cuda")
+            torch.cuda.synchronize()
+            L.m4ri_b200_dmul_abt_fp4_debug(dC.h, dA.h, dB.h, acc.data_ptr(), cg)
+            L.m4ri_b200_synchronize()
+            assert (acc.cpu().numpy().astype(np.float64) * 4 == pc).all(), (ci, cg)
+        want = np.packbits((pc.astype(np.int64) & 1).astype(np.uint8), axis=1, bitorder="little").view(np.uint64)
+        for variant in ("fp4s256", "fp4s256cg1", "fp4ldg", "fp4", "fp4ldgcg1"):
+            L.m4ri_b200_set_mma_variant(m4.MMA_VARIANTS[variant])
+            try:
+                m4.dmul_abt(dC, dA, dB, clear=True, algo=m4.ALGO_MMA)
+                assert (dC.to_words()[:, :4] == want).all(), (ci, variant)
+            finally:
+                L.m4ri_b200_set_mma_variant(0)
+        L.mzd_free(a)
+        L.mzd_free(b)
+
+
+def test_n65536_single_gpu(gpu, m4):
+    """configs[3] on ONE GPU: n = 65536 through m4ri_b200_dmul AUTO — the plan with TWO Strassen
+    levels (api.cu strassen_levels: leaves of 16384) — checked with Freivalds (2^-64), against the
+    Four-Russians kernel's checksum, and a row-block product (the 8-GPU job's 8192 x 65536 x 65536
+    shard, one level) against the same rows of the full result."""
+    n = 65536
+    L = m4.lib()
+    dA = m4.DMat.init(n, n).fill_random(61)
+    dB = m4.DMat.init(n, n).fill_random(62)
+    dC = m4.DMat.init(n, n)
+    L.m4ri_b200_timing_reset()
+    m4.dmul(dC, dA, dB, algo=m4.ALGO_AUTO)
+    L.m4ri_b200_synchronize()
+    assert L.m4ri_b200_timing_count() == 49, "AUTO at n = 65536 runs 7^2 leaf products (two levels)"
+    assert L.m4ri_b200_dfreivalds(dC.h, dA.h, dB.h, 0xF5E1) == 1
+    chk = dC.checksum()
+    # row-block of the sharded job: rows [16384, 24576)
+    r0, rows = 16384, 8192
+    ws = n // 64
+    dAb = m4.DMat.wrap(dA.ptr + r0 * ws * 8, rows, n, ws, keepalive=dA)
+    dCb = m4.DMat.init(rows, n)
+    m4.dmul(dCb, dAb, dB, algo=m4.ALGO_AUTO)
+    dCref = m4.DMat.wrap(dC.ptr + r0 * ws * 8, rows, n, ws, keepalive=dC)
+    L.m4ri_b200_dadd(dCb.h, dCb.h, dCref.h)
+    assert L.m4ri_b200_dis_zero(dCb.h) == 1
+    del dCb
+    # independent algorithm, same checksum
+    m4.dmul(dC, dA, dB, algo=m4.ALGO_M4RM)
+    assert dC.checksum() == chk
+
+
+def test_result_into_window_keeps_the_parents_bits(gpu, m4, orc):
+    """C is a window whose last word is shared with other columns of its parent (ncols % 64 != 0):
+    the product must not touch the parent's bits beyond the window."""
+    L = m4.lib()
+    P0 = orc.random(300, 640, 4)
+    for (m, k, n, lowc) in [(200, 320, 100, 128), (200, 5000, 70, 0), (64, 64, 1, 64)]:
+        p = host(m4, P0, 640)
+        w = L.mzd_init_window(p, 10, lowc, 10 + m, lowc + n)
+        A, B = orc.random(m, k, 5), orc.random(k, n, 6)
+        a, b = host(m4, A, k), host(m4, B, n)
+        want = orc.mul_m4rm(A, B, k, n)[:, : orc.width(n)]
+        for f in (lambda: L.mzd_mul(w, a, b, 0), lambda: L.mzd_mul_m4rm(w, a, b, 0), lambda: L.mzd_mul_naive(w, a, b)):
+            f()
+            now = m4.mzd_words(p)[:, :10]
+            exp = P0[:, :10].copy()
+            mask = np.uint64((1 << (n % 64)) - 1) if n % 64 else np.uint64(0xFFFFFFFFFFFFFFFF)
+            wd = orc.width(n)
+            blk = exp[10:10 + m, lowc // 64: lowc // 64 + wd]
+            blk[:, : wd - 1] = want[:, : wd - 1]
+            blk[:, wd - 1] = (blk[:, wd - 1] & ~mask) | (want[:, wd - 1] & mask)
+            assert (now == exp).all(), (m, k, n, lowc)
+        for q in (w, p, a, b):
+            L.mzd_free(q)

@@ -37,7 +37,8 @@ print(f"{variant}: {len(SWEEP) - bad}/{len(SWEEP)} shapes bit-exact", flush=True
 if ("--time" in sys.argv or "--time-only" in sys.argv) and bad == 0:
     import ctypes
     L.m4ri_b200_set_strassen_levels(int(os.environ.get("LEVELS", "0")))  # time the kernel itself
-    for n in ((32768,) if '--time-only' in sys.argv else (4096, 8192, 16384, 32768)):
+    sizes = [int(x) for x in os.environ["SIZES"].split(",")] if os.environ.get("SIZES") else None
+    for n in (sizes or ((32768,) if '--time-only' in sys.argv else (4096, 8192, 16384, 32768))):
         dA, dB, dBt, dC = (m4.DMat.init(n, n) for _ in range(4))
         dA.fill_random(1); dB.fill_random(2)
         L.m4ri_b200_dtranspose(dBt.h, dB.h)
