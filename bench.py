@@ -456,31 +456,53 @@ def main():
     chk = dC.checksum()
 
     # ---- e2e: the reference-facing call, host operands ---------------------------
+    # ONE call C = mzd_mul(NULL, A, B, 0) on the FULL host operands, as m4ri-rust makes it for
+    # `&a * &b` (binary_matrix.rs:465): C == NULL, the library allocates the result, the caller
+    # drops it (mzd_free) — allocation and free are timed. At N > 1 rank 0 makes that one call
+    # with m4ri_b200_set_devices(N): the library spreads it over the N GPUs of the box (B uploaded
+    # once, slab g over GPU g's PCIe link, exchanged over NVLink); the other ranks wait on the
+    # host (a store key, not an NCCL kernel that would sit on their SMs).
     e2e_ms = None
+    e2e_bytes = (0, 0)
     if not args.no_e2e:
-        hA, hB = L.mzd_init(rows, n), L.mzd_init(n, n)
-        L.m4ri_b200_download(hA, dA.h)
-        L.m4ri_b200_download(hB, dB.h)
-        L.m4ri_b200_synchronize()
-        L.m4ri_b200_set_algo(algo)
-        # the call m4ri-rust makes for `&a * &b` (binary_matrix.rs:465): C == NULL, the library
-        # allocates the result, the caller drops it (mzd_free) — allocation and free are timed
-        e2e_steps = max(3, min(args.steps, 5))
-        for i in range(2):
-            L.mzd_free(L.mzd_mul(None, hA, hB, 0))
+        store = dist.distributed_c10d._get_default_store() if dist is not None else None
         barrier()
-        t0 = time.perf_counter()
-        for i in range(e2e_steps - 1):
-            L.mzd_free(L.mzd_mul(None, hA, hB, 0))  # synchronous: result words valid on return
-        hC = L.mzd_mul(None, hA, hB, 0)
-        torch.cuda.synchronize()
-        e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
-        L.m4ri_b200_set_algo(0)
-        host_chk_ok = bool((m4.mzd_words(hC)[:4] == dC.to_words()[:4]).all())
-        if not host_chk_ok:
-            raise SystemExit("bench.py: host-ABI result differs from the device-resident result")
-        for p in (hA, hB, hC):
-            L.mzd_free(p)
+        if rank == 0:
+            if world > 1:
+                dAf = m4.DMat.init(n, n).fill_random(SEED_A)
+                hA, hB = L.mzd_init(n, n), L.mzd_init(n, n)
+                L.m4ri_b200_download(hA, dAf.h)
+                del dAf
+            else:
+                hA, hB = L.mzd_init(rows, n), L.mzd_init(n, n)
+                L.m4ri_b200_download(hA, dA.h)
+            L.m4ri_b200_download(hB, dB.h)
+            L.m4ri_b200_synchronize()
+            L.m4ri_b200_set_algo(algo)
+            L.m4ri_b200_set_devices(world)
+            e2e_steps = max(3, min(args.steps, 5))
+            for i in range(2):
+                L.mzd_free(L.mzd_mul(None, hA, hB, 0))
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for i in range(e2e_steps - 1):
+                L.mzd_free(L.mzd_mul(None, hA, hB, 0))  # synchronous: result words valid on return
+            hC = L.mzd_mul(None, hA, hB, 0)
+            e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
+            L.m4ri_b200_set_devices(1)
+            L.m4ri_b200_set_algo(0)
+            # the rows this rank also computed device-resident must be the same words
+            mine = m4.mzd_words(hC)[r0:r0 + rows]
+            step_ = max(1, rows // 64)
+            if not bool((mine[::step_] == dC.to_words()[::step_]).all()):
+                raise SystemExit("bench.py: host-ABI result differs from the device-resident result")
+            e2e_bytes = (2 * n * ws * 8 if world > 1 else (rows * ws + n * ws) * 8, (n if world > 1 else rows) * ws * 8)
+            for p in (hA, hB, hC):
+                L.mzd_free(p)
+            if store is not None:
+                store.set("m4ri_b200_e2e_done", "1")
+        elif store is not None:
+            store.wait(["m4ri_b200_e2e_done"])
 
     # ---- reduce over ranks: max time ------------------------------------------------
     t = torch.tensor([ms, e2e_ms or 0.0, kern_ms], dtype=torch.float64, device="cuda")
@@ -549,11 +571,11 @@ def main():
             "parity": {"freivalds_2^-64": True, "checksum_rank0": f"{chk:016x}"},
             "step_ms_rank0": [round(x, 3) for x in step_ms]}
     if e2e_ms is not None:
-        bytes_in = (rows * ws + n * ws) * 8
         line["e2e"] = {"value": total_ops / (e2e_max * 1e-3) / 1e12, "unit": "Tbit-op/s",
-                       "ms_per_step": e2e_max, "h2d_bytes_per_step": bytes_in,
-                       "d2h_bytes_per_step": rows * ws * 8,
-                       "api": "C = mzd_mul(NULL, A, B, 0) on host mzd_t operands (pinned), result allocated by the library and freed by the caller as m4ri-rust does; per rank on its row-block"}
+                       "ms_per_step": e2e_max, "h2d_bytes_per_step": e2e_bytes[0],
+                       "d2h_bytes_per_step": e2e_bytes[1],
+                       "api": "ONE call C = mzd_mul(NULL, A, B, 0) on the full host mzd_t operands (pinned), result allocated by the library and freed by the caller as m4ri-rust does"
+                              + ("" if world == 1 else f"; made by rank 0 with m4ri_b200_set_devices({world}): B crosses PCIe once (slab g over GPU g's link) and is exchanged over NVLink inside the library")}
     if world > 1 and not args.no_cpu_baseline:
         # N > 1 lines: a bounded, labelled sample (the full arm is `--impl reference`)
         r = cpu_arm(n, n, 1, 1, target_s=6.0, strassen_n=16384)

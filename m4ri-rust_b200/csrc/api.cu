@@ -34,12 +34,13 @@ void die(const char *fmt, ...) {
 static std::mutex g_tmu;
 static std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_tev;
 static bool g_timing_on = false;
+static std::thread::id g_timing_thread;  // only launches of the thread that called timing_reset are recorded
 static const char *g_tname = "";
 static double g_tops = 0;
 void timing_begin(const char *kernel_name, cudaStream_t s, double ops) {
   if (!g_timing_on) return;
   std::lock_guard<std::mutex> g(g_tmu);
-  if (g_tev.size() >= 4096) return;
+  if (std::this_thread::get_id() != g_timing_thread || g_tev.size() >= 4096) return;
   cudaEvent_t a, b;
   M4B_CUDA(cudaEventCreate(&a));
   M4B_CUDA(cudaEventCreate(&b));
@@ -51,7 +52,7 @@ void timing_begin(const char *kernel_name, cudaStream_t s, double ops) {
 void timing_end(cudaStream_t s) {
   if (!g_timing_on) return;
   std::lock_guard<std::mutex> g(g_tmu);
-  if (g_tev.empty()) return;
+  if (std::this_thread::get_id() != g_timing_thread || g_tev.empty()) return;
   M4B_CUDA(cudaEventRecord(g_tev.back().second, s));
 }
 
@@ -631,7 +632,7 @@ static void pipelined_host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int
       const rci_t r0 = i * per, r1 = r0 + per < m ? r0 + per : m;
       DMat Ai = dwin(dA, r0, 0, r1 - r0, k), Cij = dwin(dC, r0, c0, r1 - r0, c1 - c0);
       if (j == 0) M4B_CUDA(cudaStreamWaitEvent(s, ev_a[i], 0));
-      k_mul_abt_mma(&Cij, &Ai, &Btj, clear, s);
+      product_with_strassen(&Cij, &Ai, &Btj, clear, M4RI_B200_ALGO_MMA, 1, 0, s);  // a level where the block is big enough
       cudaEvent_t e = ev_c[j * na + i];
       M4B_CUDA(cudaEventRecord(e, s));
       M4B_CUDA(cudaStreamWaitEvent(t_d2h, e, 0));
@@ -692,6 +693,198 @@ struct DeviceWorker {
 static std::mutex g_workers_mu;  // also serialises multi-GPU calls
 static std::vector<DeviceWorker *> g_workers;
 
+// ---- one product over the G GPUs of the process, B travelling ONCE over PCIe -----------------
+// GPU g uploads only ITS k-slab of B (|B|/G over its own link), bit-transposes it and stores the
+// slab of Bt into every GPU's Bt buffer with peer stores over NVLink (transpose_wide_kernel, the
+// exchange of the torchrun path, sharded.py) — the pre-transposed form peer-copies row slabs of Bt
+// instead. Its rows of A go up in chunks behind the slab; every chunk is multiplied as soon as it
+// and the whole Bt have landed, and its rows of C go home while the next chunk is multiplied.
+// Host traffic: |A| + |B| up, |C| down in total (round 1: |A| + G |B| up).
+// Cross-device ordering is by events; an event must have been RECORDED (on the host timeline)
+// before another thread makes a stream wait for it, hence the two host barriers.
+struct HostBarrier {
+  std::mutex mu;
+  std::condition_variable cv;
+  int n = 0, waiting = 0;
+  unsigned long long gen = 0;
+  void wait() {
+    std::unique_lock<std::mutex> lk(mu);
+    const unsigned long long g = gen;
+    if (++waiting == n) {
+      waiting = 0;
+      gen++;
+      cv.notify_all();
+    } else {
+      cv.wait(lk, [&] { return gen != g; });
+    }
+  }
+};
+struct MultiJob {
+  int G = 0, used = 0, clear = 0, form = 0;
+  mzd_t *C = nullptr;
+  const mzd_t *A = nullptr, *B = nullptr;
+  rci_t per = 0, slab = 0;  // rows of A/C per GPU; rows of B (form 0) or of Bt (form 1) per GPU
+  DMat *dBt[8] = {};
+  cudaEvent_t e_alloc[8] = {}, e_xchg[8] = {};
+  HostBarrier bar;
+};
+
+static std::atomic<int> g_peer_ok{-1};  // -1 unknown, 0 no, 1 every pair of the first G devices is peer-capable
+static int g_peer_G = 0;
+static bool peers_ready(int G) {  // under g_workers_mu
+  if (g_peer_ok.load() >= 0 && g_peer_G >= G) return g_peer_ok.load() == 1;
+  bool ok = true;
+  for (int a = 0; a < G && ok; a++)
+    for (int b = 0; b < G && ok; b++) {
+      int can = 0;
+      if (a != b && (cudaDeviceCanAccessPeer(&can, a, b) != cudaSuccess || !can)) ok = false;
+    }
+  (void)cudaGetLastError();
+  if (getenv("M4RI_B200_NO_PEER")) ok = false;  // experiment/test hook: the independent-upload plan
+  g_peer_ok.store(ok ? 1 : 0);
+  g_peer_G = G;
+  return ok;
+}
+// called by worker `dev` (its device current): peers may read/write this device's pool memory
+static void open_pool_to_peers(int dev, int G) {
+  static std::atomic<unsigned long long> done{0};
+  const unsigned long long bit = 1ull << dev;
+  if (done.load() & bit) return;
+  cudaMemPool_t pool;
+  M4B_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
+  for (int p = 0; p < G; p++) {
+    if (p == dev) continue;
+    cudaMemAccessDesc d = {};
+    d.location.type = cudaMemLocationTypeDevice;
+    d.location.id = p;
+    d.flags = cudaMemAccessFlagsProtReadWrite;
+    M4B_CUDA(cudaMemPoolSetAccess(pool, &d, 1));
+    cudaError_t e = cudaDeviceEnablePeerAccess(p, 0);  // kernels of this device may address p's memory
+    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) M4B_CUDA(e);
+    (void)cudaGetLastError();
+  }
+  done.fetch_or(bit);
+}
+
+static void multi_worker(MultiJob *J, int g) {
+  if (!t_h2d) M4B_CUDA(cudaStreamCreateWithFlags(&t_h2d, cudaStreamNonBlocking));
+  if (!t_d2h) M4B_CUDA(cudaStreamCreateWithFlags(&t_d2h, cudaStreamNonBlocking));
+  cudaStream_t s = current_stream();
+  open_pool_to_peers(g, J->G);
+  const mzd_t *A = J->A, *B = J->B;
+  mzd_t *C = J->C;
+  const int clear = J->clear, form = J->form;
+  const rci_t M = A->nrows, k = A->ncols, n = C->ncols;
+  const rci_t r0 = (rci_t)g * J->per < M ? (rci_t)g * J->per : M, r1 = r0 + J->per < M ? r0 + J->per : M, m = r1 - r0;
+  const rci_t slab_total = form == 0 ? k : n;  // rows of the operand B as the caller holds it
+  const rci_t s0 = (rci_t)g * J->slab < slab_total ? (rci_t)g * J->slab : slab_total,
+              s1 = s0 + J->slab < slab_total ? s0 + J->slab : slab_total;
+  // shallow views: rows [r0, r1) of A and C, rows [s0, s1) of B, through the callers' rows[]
+  mzd_t Av = *A, Cv = *C, Bv = *B;
+  Av.nrows = Cv.nrows = m;
+  Av.rows = A->rows + r0;
+  Cv.rows = C->rows + r0;
+  Bv.nrows = s1 - s0;
+  Bv.rows = B->rows + s0;
+  DMat *dA = dmat_new_overwritten(m, k, s), *dC = dmat_new_overwritten(m, n, s);
+  DMat *dBt = dmat_new_overwritten(n, k, s);
+  DMat *dBs = form == 0 ? dmat_new_overwritten(s1 - s0, n, s) : nullptr;
+  J->dBt[g] = dBt;
+  M4B_CUDA(cudaEventCreateWithFlags(&J->e_alloc[g], cudaEventDisableTiming));
+  M4B_CUDA(cudaEventCreateWithFlags(&J->e_xchg[g], cudaEventDisableTiming));
+  M4B_CUDA(cudaEventRecord(J->e_alloc[g], s));
+  M4B_CUDA(cudaStreamWaitEvent(t_h2d, J->e_alloc[g], 0));
+  // ---- uploads: this GPU's slab of B first, then its rows of A in chunks ----
+  cudaEvent_t e_slab;
+  M4B_CUDA(cudaEventCreateWithFlags(&e_slab, cudaEventDisableTiming));
+  if (s1 > s0) {
+    if (form == 0) {
+      upload_rows(dBs, &Bv, 0, s1 - s0, t_h2d);
+    } else {  // rows [s0, s1) of Bt go straight into place
+      DMat W = dwin(dBt, s0, 0, s1 - s0, k);
+      upload_rows(&W, &Bv, 0, s1 - s0, t_h2d);
+    }
+  }
+  M4B_CUDA(cudaEventRecord(e_slab, t_h2d));
+  int na = 1, nb_unused = 1;
+  if (m > 0) plan_pipeline(m, k, n, clear, &na, &nb_unused);
+  na = pipeline_parts("M4RI_B200_PIPE_ROWS", na);
+  rci_t per = m > 0 ? ((m + na - 1) / na + 255) / 256 * 256 : 256;
+  na = m > 0 ? (m + per - 1) / per : 0;
+  std::vector<cudaEvent_t> ev(2 * na + 1);
+  for (auto &e : ev) M4B_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  for (int i = 0; i < na; i++) {
+    const rci_t a0 = i * per, a1 = a0 + per < m ? a0 + per : m;
+    upload_rows(dA, &Av, a0, a1, t_h2d);
+    if (!clear) upload_rows(dC, &Cv, a0, a1, t_h2d);
+    M4B_CUDA(cudaEventRecord(ev[i], t_h2d));
+  }
+  J->bar.wait();  // every GPU's Bt buffer exists and its e_alloc is recorded
+  // ---- exchange: my slab -> every GPU's Bt ----
+  M4B_CUDA(cudaStreamWaitEvent(s, e_slab, 0));
+  for (int d = 0; d < J->used; d++)
+    if (d != g) M4B_CUDA(cudaStreamWaitEvent(s, J->e_alloc[d], 0));
+  if (s1 > s0) {
+    if (form == 0) {
+      DMat wins[8];
+      DMat *dst[8];
+      for (int d = 0; d < J->used; d++) {
+        wins[d] = dwin(J->dBt[d], 0, s0, n, s1 - s0);  // columns [s0, s1) of Bt: 128-byte aligned (slabs of 1024 rows)
+        dst[d] = &wins[d];
+      }
+      k_transpose_scatter(dst, J->used, dBs, s);
+    } else {
+      for (int d = 0; d < J->used; d++)
+        if (d != g)
+          M4B_CUDA(cudaMemcpyPeerAsync(J->dBt[d]->d + (size_t)s0 * J->dBt[d]->rowstride, d,
+                                       dBt->d + (size_t)s0 * dBt->rowstride, g,
+                                       (size_t)(s1 - s0) * dBt->rowstride * 8, s));
+    }
+  }
+  M4B_CUDA(cudaEventRecord(J->e_xchg[g], s));
+  J->bar.wait();  // every exchange is recorded
+  for (int d = 0; d < J->used; d++)
+    if (d != g) M4B_CUDA(cudaStreamWaitEvent(s, J->e_xchg[d], 0));
+  // ---- products, chunk by chunk, rows of C going home behind them ----
+  for (int i = 0; i < na; i++) {
+    const rci_t a0 = i * per, a1 = a0 + per < m ? a0 + per : m;
+    DMat Ai = dwin(dA, a0, 0, a1 - a0, k), Ci = dwin(dC, a0, 0, a1 - a0, n);
+    M4B_CUDA(cudaStreamWaitEvent(s, ev[i], 0));
+    product_with_strassen(&Ci, &Ai, dBt, clear, M4RI_B200_ALGO_MMA, 1, 0, s);
+    M4B_CUDA(cudaEventRecord(ev[na + i], s));
+    M4B_CUDA(cudaStreamWaitEvent(t_d2h, ev[na + i], 0));
+    download_rows(&Cv, dC, a0, a1, t_d2h);
+  }
+  M4B_CUDA(cudaEventRecord(ev[2 * na], t_d2h));
+  M4B_CUDA(cudaStreamWaitEvent(s, ev[2 * na], 0));
+  M4B_CUDA(cudaStreamSynchronize(s));
+  J->bar.wait();  // nobody frees a Bt buffer a peer may still be writing or reading
+  dmat_delete(dA, s);
+  dmat_delete(dC, s);
+  dmat_delete(dBt, s);
+  if (dBs) dmat_delete(dBs, s);
+  M4B_CUDA(cudaStreamSynchronize(s));
+  for (auto &e : ev) M4B_CUDA(cudaEventDestroy(e));
+  M4B_CUDA(cudaEventDestroy(e_slab));
+}
+
+static void run_on_workers(int used, const std::function<void(int)> &fn) {  // under g_workers_mu
+  for (int i = 0; i < used; i++) {
+    DeviceWorker *w = g_workers[i];
+    {
+      std::lock_guard<std::mutex> lk(w->mu);
+      w->job = [=] { fn(i); };
+      w->pending = true;
+    }
+    w->cv.notify_all();
+  }
+  for (int i = 0; i < used; i++) {
+    DeviceWorker *w = g_workers[i];
+    std::unique_lock<std::mutex> lk(w->mu);
+    w->cv.wait(lk, [&] { return !w->pending; });
+  }
+}
+
 static void multi_device_host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int clear, int form, int G) {
   std::lock_guard<std::mutex> g(g_workers_mu);
   while ((int)g_workers.size() < G) {  // workers live for the rest of the process
@@ -703,34 +896,39 @@ static void multi_device_host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, 
   }
   const rci_t m = A->nrows;
   const rci_t per = ((m + G - 1) / G + 255) / 256 * 256;
-  // shallow views of the callers' matrices: rows [r0, r1) through the same rows[] array
-  std::vector<mzd_t> Av(G), Cv(G);
-  int used = 0;
-  for (int i = 0; i < G; i++) {
+  const int used = (m + per - 1) / per;
+  if (used > 1 && peers_ready(used)) {
+    // B travels once: slab g of it over GPU g's link, then NVLink
+    MultiJob J;
+    J.G = J.used = used;
+    J.clear = clear;
+    J.form = form;
+    J.C = C;
+    J.A = A;
+    J.B = B;
+    J.per = per;
+    const rci_t rows_b = B->nrows;  // k (form 0) or n (form 1)
+    J.slab = ((rows_b + used - 1) / used + 1023) / 1024 * 1024;
+    J.bar.n = used;
+    run_on_workers(used, [&](int i) { multi_worker(&J, i); });
+    for (int i = 0; i < used; i++) {
+      M4B_CUDA(cudaEventDestroy(J.e_alloc[i]));
+      M4B_CUDA(cudaEventDestroy(J.e_xchg[i]));
+    }
+    return;
+  }
+  // no peer access between the GPUs: independent row-blocks, every GPU uploads all of B
+  std::vector<mzd_t> Av(used), Cv(used);
+  for (int i = 0; i < used; i++) {
     const rci_t r0 = (rci_t)i * per, r1 = r0 + per < m ? r0 + per : m;
-    if (r0 >= m) break;
     Av[i] = *A;
     Av[i].nrows = r1 - r0;
     Av[i].rows = A->rows + r0;
     Cv[i] = *C;
     Cv[i].nrows = r1 - r0;
     Cv[i].rows = C->rows + r0;
-    DeviceWorker *w = g_workers[i];
-    mzd_t *Ci = &Cv[i];
-    const mzd_t *Ai = &Av[i];
-    {
-      std::lock_guard<std::mutex> lk(w->mu);
-      w->job = [=] { pipelined_host_product(Ci, Ai, B, clear, form, current_stream()); };
-      w->pending = true;
-    }
-    w->cv.notify_all();
-    used++;
   }
-  for (int i = 0; i < used; i++) {
-    DeviceWorker *w = g_workers[i];
-    std::unique_lock<std::mutex> lk(w->mu);
-    w->cv.wait(lk, [&] { return !w->pending; });
-  }
+  run_on_workers(used, [&](int i) { pipelined_host_product(&Cv[i], &Av[i], B, clear, form, current_stream()); });
 }
 
 // y (^)= A*x for the shapes the reference's mat-vec calls have: BinMatrix::mul_slice passes x as an
@@ -808,11 +1006,9 @@ static mzd_t *host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int clear, 
       multi_device_host_product(C, A, B, clear, form, G);
       return C;
     }
-    if (strassen_levels(m, k, n, M4RI_B200_ALGO_MMA, cutoff) <= 1) {
-      // (deeper recursions only pay beyond n = 65536, where the 7/8 per level outweighs the copies)
-      pipelined_host_product(C, A, B, clear, form, s);
-      return C;
-    }
+    // (every block of the pipeline takes a Strassen level where its shape pays for one)
+    pipelined_host_product(C, A, B, clear, form, s);
+    return C;
   }
   DMat *dA = dmat_new(A->nrows, A->ncols, s), *dB = dmat_new(B->nrows, B->ncols, s),
        *dC = dmat_new(m, n, s);
@@ -1053,6 +1249,7 @@ void m4ri_b200_timing_reset(void) {
   for (auto &p : g_tev) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
   g_tev.clear();
   g_tops = 0;
+  g_timing_thread = std::this_thread::get_id();
   g_timing_on = true;
 }
 double m4ri_b200_timing_ms(void) {

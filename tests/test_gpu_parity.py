@@ -477,34 +477,72 @@ def test_fp4_accumulators_are_exact(gpu, m4, orc):
             L.mzd_free(b)
 
 
-def test_multi_device_host_products(gpu, m4, orc):
-    """m4ri_b200_set_devices(G): one host-ABI call spread over the GPUs of the process (row-blocks
-    of A and C on per-GPU worker threads). Needs two visible GPUs; the result must be the
-    single-GPU words, for the plain, accumulate and pre-transposed forms on a ragged shape."""
+@pytest.mark.parametrize("peer", [True, False])
+def test_multi_device_host_products(gpu, m4, orc, monkeypatch, peer):
+    """m4ri_b200_set_devices(G): ONE host-ABI call spread over the GPUs of the process, for every G
+    from 2 to the number of visible GPUs (skips with one). Default plan: GPU g uploads only its
+    k-slab of B, the slabs of Bt are exchanged with NVLink peer stores; peer=False forces the
+    independent plan (every GPU uploads all of B). The result must be the single-GPU words, for
+    the plain, accumulate and pre-transposed forms on ragged shapes."""
     L = m4.lib()
-    if L.m4ri_b200_device_count() < 2:
+    ndev = L.m4ri_b200_device_count()
+    if ndev < 2:
         pytest.skip("one GPU visible")
-    m, k, n = 5000, 20000, 9000
-    A, B, C0 = orc.random(m, k, 21), orc.random(k, n, 22), orc.random(m, n, 23)
-    want = orc.mul_m4rm(A, B, k, n, threads=0)[:, : orc.width(n)]
-    a, b = host(m4, A, k), host(m4, B, n)
+    if not peer:
+        import subprocess, sys
+        # the peer decision is cached per process: run the independent plan in a child
+        code = ("import os, sys; os.environ['M4RI_B200_NO_PEER'] = '1'; sys.path.insert(0, %r);"
+                "import numpy as np, m4ri_rust_b200 as m4, oracle as orc; L = m4.lib();"
+                "m, k, n = 3000, 20000, 9000; A, B = orc.random(m, k, 21), orc.random(k, n, 22);"
+                "want = orc.mul_m4rm(A, B, k, n, threads=0)[:, : orc.width(n)];"
+                "a, b = m4.mzd_from_words(A, k), m4.mzd_from_words(B, n); L.m4ri_b200_set_devices(2);"
+                "c = L.mzd_mul(None, a, b, 0); assert (m4.mzd_words(c)[:, : orc.width(n)] == want).all(); print('ok')"
+                ) % os.path.dirname(HERE)
+        r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0 and "ok" in r.stdout, r.stderr[-2000:]
+        return
     try:
-        L.m4ri_b200_set_devices(2)
-        assert L.m4ri_b200_get_devices() == 2
-        assert (result_words(m4, L.mzd_mul(None, a, b, 0)) == want).all()
-        c = host(m4, C0, n)
-        L.mzd_addmul(c, a, b, 0)
-        assert (result_words(m4, c) == (C0[:, : orc.width(n)] ^ want)).all()
-        bt = L.mzd_transpose(None, b)
-        L.m4ri_b200_set_algo(m4.ALGO_MMA)
-        got = result_words(m4, L._mzd_mul_naive(None, a, bt, 1))
-        assert (got == want).all()
-        L.mzd_free(bt)
+        for G in sorted(set([2, ndev])):
+            L.m4ri_b200_set_devices(G)
+            assert L.m4ri_b200_get_devices() == G
+            for (m, k, n) in [(5000, 20000, 9000), (2049, 30001, 4099), (600, 16384, 8192)]:
+                A, B, C0 = orc.random(m, k, 21), orc.random(k, n, 22), orc.random(m, n, 23)
+                want = orc.mul_m4rm(A, B, k, n, threads=0)[:, : orc.width(n)]
+                a, b = host(m4, A, k), host(m4, B, n)
+                assert (result_words(m4, L.mzd_mul(None, a, b, 0)) == want).all(), (G, m, k, n)
+                c = host(m4, C0, n)
+                L.mzd_addmul(c, a, b, 0)
+                assert (result_words(m4, c) == (C0[:, : orc.width(n)] ^ want)).all(), (G, m, k, n)
+                bt = L.mzd_transpose(None, b)
+                L.m4ri_b200_set_algo(m4.ALGO_MMA)
+                got = result_words(m4, L._mzd_mul_naive(None, a, bt, 1))
+                L.m4ri_b200_set_algo(m4.ALGO_AUTO)
+                assert (got == want).all(), (G, m, k, n)
+                for p in (a, b, bt):
+                    L.mzd_free(p)
+        # one big square product: every GPU's rows equal the single-GPU result
+        n = 16384
+        dA, dB = m4.DMat.init(n, n).fill_random(5), m4.DMat.init(n, n).fill_random(6)
+        a, b = dA.to_host(), dB.to_host()
+        L.m4ri_b200_set_devices(ndev)
+        cG = L.mzd_mul(None, a, b, 0)
+        L.m4ri_b200_set_devices(1)
+        c1 = L.mzd_mul(None, a, b, 0)
+        assert L.mzd_equal(cG, c1) == 1
+        for p in (a, b, cG, c1):
+            L.mzd_free(p)
     finally:
         L.m4ri_b200_set_algo(m4.ALGO_AUTO)
         L.m4ri_b200_set_devices(1)
-    for p in (a, b):
-        L.mzd_free(p)
+
+
+def test_set_devices_clamps_to_the_visible_gpus(gpu, m4):
+    L = m4.lib()
+    try:
+        L.m4ri_b200_set_devices(64)
+        assert L.m4ri_b200_get_devices() == L.m4ri_b200_device_count()
+    finally:
+        L.m4ri_b200_set_devices(1)
 
 
 def test_fp4_accumulators_exact_on_dense_operands(gpu, m4, orc):
