@@ -103,6 +103,19 @@ mzd_t *_mzd_mul_va(mzd_t *C, const mzd_t *v, const mzd_t *A, int clear);   /* mz
  * produces, binary_matrix.rs:426-427). Named by the north star. */
 mzd_t *mzd_mul_v(mzd_t *y, const mzd_t *A, const mzd_t *x);
 
+/* ---- consumers of the product: blocked Gauss-Jordan on the GPU whose trailing
+ * update is one accumulating product per column block (csrc/elim.cu) ---------------------------- */
+/* (Reduced) row echelon form in place, returns the rank. The REDUCED form is returned for either
+ * value of `full` (it is an upper triangular form, and unlike that one it is unique). */
+rci_t mzd_echelonize(mzd_t *A, int full);               /* echelonform.rs:16 (BinMatrix::echelonize/rank, binary_matrix.rs:247-261) */
+rci_t mzd_echelonize_pluq(mzd_t *A, int full);          /* echelonform.rs:27 */
+rci_t mzd_echelonize_m4ri(mzd_t *A, int full, int k);   /* echelonform.rs:36 */
+/* dst = src^-1 (dst NULL: allocate); NULL when src is singular. */
+mzd_t *mzd_inv_m4ri(mzd_t *dst, const mzd_t *src, int k); /* brilliantrussian.rs:208 (BinMatrix::inverted, binary_matrix.rs:264-268) */
+/* Solves A X = B, X stored in the first ncols(A) rows of B (free variables zero, other rows of B
+ * zeroed); 0 = solved, -1 = inconsistent (B untouched). A is left as it was. */
+int mzd_solve_left(mzd_t *A, mzd_t *B, int cutoff, int inconsistency_check); /* solve.rs:23 (solve_left, binary_matrix.rs:582-586) */
+
 /* ---- additive API: algorithm choice, device-resident operands --------------- */
 enum m4ri_b200_algo {
   M4RI_B200_ALGO_AUTO = 0,  /* library picks (shape based)                        */
@@ -227,6 +240,10 @@ double m4ri_b200_timing_ops(void);
  * must be exactly (number of common set bits)/4. cg = 1 or 2 CTAs per MMA. */
 void m4ri_b200_dmul_abt_fp4_debug(m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *A,
                                   const m4ri_b200_dmat_t *Bt, void *acc, int cg);
+/* Reduced row echelon form of a device matrix in place; pivots are searched in columns
+ * [0, pivot_cols) only (0 = all), the other columns are carried along. Returns the rank and the
+ * first max_pivots pivot columns (increasing). Synchronises the stream once per column block. */
+int m4ri_b200_drref(m4ri_b200_dmat_t *W, int pivot_cols, int *pivot_columns, int max_pivots);
 /* 64-bit XOR-fold checksum of all words (position-mixed), computed on device. */
 uint64_t m4ri_b200_dchecksum(const m4ri_b200_dmat_t *M);
 /* 1 iff every valid word is zero (OR-reduction on device). */

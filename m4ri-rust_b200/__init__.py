@@ -65,6 +65,10 @@ def lib():
         "mzd_set_ui": (None, [MzdP, u]), "mzd_randomize": (None, [MzdP]),
         "mzd_transpose": (MzdP, [MzdP, MzdP]),
         "mzd_add": (MzdP, [MzdP, MzdP, MzdP]), "mzd_sub": (MzdP, [MzdP, MzdP, MzdP]),
+        "mzd_echelonize": (i, [MzdP, i]), "mzd_echelonize_pluq": (i, [MzdP, i]),
+        "mzd_echelonize_m4ri": (i, [MzdP, i, i]), "mzd_inv_m4ri": (MzdP, [MzdP, MzdP, i]),
+        "mzd_solve_left": (i, [MzdP, MzdP, i, i]),
+        "m4ri_b200_drref": (i, [vp, i, ctypes.POINTER(i), i]),
         "mzd_concat": (MzdP, [MzdP, MzdP, MzdP]), "mzd_stack": (MzdP, [MzdP, MzdP, MzdP]),
         "mzd_mul": (MzdP, [MzdP, MzdP, MzdP, i]), "mzd_addmul": (MzdP, [MzdP, MzdP, MzdP, i]),
         "mzd_mul_m4rm": (MzdP, [MzdP, MzdP, MzdP, i]),
@@ -310,6 +314,25 @@ class BinMatrix:
         w = self.mzd.contents.width
         return int(sum(bin(int(x)).count("1") for x in self.words()[:, :w].ravel()))
 
+    def augmented(self, other):  # binary_matrix.rs:218-231
+        assert self.nrows() == other.nrows(), "The rows need to be equal"
+        return BinMatrix(lib().mzd_concat(None, self.mzd, other.mzd))
+
+    def stacked(self, other):  # binary_matrix.rs:233-244
+        return BinMatrix(lib().mzd_stack(None, self.mzd, other.mzd))
+
+    def rank(self):  # binary_matrix.rs:246-252: echelonizes a clone
+        return self.clone().echelonize()
+
+    def echelonize(self):  # binary_matrix.rs:254-261 (in place, returns the rank)
+        return int(lib().mzd_echelonize(self.mzd, 0))
+
+    def inverted(self):  # binary_matrix.rs:263-268
+        p = lib().mzd_inv_m4ri(None, self.mzd, 0)
+        if not p:
+            raise ValueError("Can't be NULL")  # nonnull! panics on a singular matrix
+        return BinMatrix(p)
+
     def transposed(self):  # binary_matrix.rs:272-279
         return BinMatrix(lib().mzd_transpose(None, self.mzd))
 
@@ -370,6 +393,12 @@ class BinMatrix:
 
     def __eq__(self, other):  # binary_matrix.rs:434-438
         return isinstance(other, BinMatrix) and lib().mzd_equal(self.mzd, other.mzd) == 1
+
+
+def solve_left(a, b):
+    """Solve AX = B for X, B is overwritten with the solution; True on success
+    (binary_matrix.rs:575-586)."""
+    return lib().mzd_solve_left(a.mzd, b.mzd, 0, 1) == 0
 
 
 # ---------------------------------------------------------------------------------

@@ -174,7 +174,7 @@ static void keep_pool_cached() {
   done.fetch_or(bit);
 }
 
-static DMat *dmat_new(rci_t nrows, rci_t ncols, cudaStream_t s) {
+DMat *dmat_new(rci_t nrows, rci_t ncols, cudaStream_t s) {
   keep_pool_cached();
   if (nrows < 0 || ncols < 0) die("m4ri_b200: negative matrix dimension\n");
   DMat *M = (DMat *)calloc(1, sizeof(DMat));
@@ -190,7 +190,7 @@ static DMat *dmat_new(rci_t nrows, rci_t ncols, cudaStream_t s) {
   return M;
 }
 
-static void dmat_delete(DMat *M, cudaStream_t s) {
+void dmat_delete(DMat *M, cudaStream_t s) {
   if (!M) return;
   if (M->base) M4B_CUDA(cudaFreeAsync(M->base, s));
   free(M);
@@ -229,7 +229,7 @@ static void upload_rows(DMat *D, const mzd_t *H, rci_t r0, rci_t r1, cudaStream_
     k_mask_excess(&W, s);
   }
 }
-static void upload(DMat *D, const mzd_t *H, cudaStream_t s) { upload_rows(D, H, 0, H->nrows, s); }
+void upload(DMat *D, const mzd_t *H, cudaStream_t s) { upload_rows(D, H, 0, H->nrows, s); }
 
 // A result written into a WINDOW whose last word is shared with the parent's other columns
 // (ncols % 64 != 0): the bits beyond ncols in that word belong to the parent and must survive
@@ -269,7 +269,7 @@ static void download_rows(mzd_t *H, const DMat *D, rci_t r0, rci_t r1, cudaStrea
     i = j;
   }
 }
-static void download(mzd_t *H, const DMat *D, cudaStream_t s) { download_rows(H, D, 0, H->nrows, s); }
+void download(mzd_t *H, const DMat *D, cudaStream_t s) { download_rows(H, D, 0, H->nrows, s); }
 
 // ---- algorithm choice ---------------------------------------------------------------
 static int resolve_algo(int algo, int m, int k, int n) {
@@ -291,7 +291,7 @@ static int resolve_algo(int algo, int m, int k, int n) {
 // form 0: C = A*B (B is k x n). form 1: C = A*Bt^T (Bt is n x k). 7 leaf products
 // and 14 XOR passes + 1 copy on quadrant windows per level; the XORs are HBM-bound
 // elementwise kernels (k_add) on quarter-size matrices.
-static DMat dwin(const DMat *M, int r0, int c0, int nr, int nc) {
+DMat dwin(const DMat *M, int r0, int c0, int nr, int nc) {
   DMat W;
   W.d = M->d + (size_t)r0 * M->rowstride + c0 / 64;
   W.nrows = nr;
@@ -417,8 +417,7 @@ static bool thin_shape_auto(int algo) {
 static bool aligned16(const DMat *M) { return !((uintptr_t)M->d & 15) && !(M->rowstride & 1); }
 
 // C (^)= A*B on device
-static void dmul(DMat *C, const DMat *A, const DMat *B, int clear, int algo, cudaStream_t s,
-                 int cutoff = 0) {
+void dmul(DMat *C, const DMat *A, const DMat *B, int clear, int algo, cudaStream_t s, int cutoff) {
   if (A->ncols != B->nrows || C->nrows != A->nrows || C->ncols != B->ncols)
     die("m4ri_b200: mul: shapes (%d x %d) * (%d x %d) -> (%d x %d) do not match\n", A->nrows,
         A->ncols, B->nrows, B->ncols, C->nrows, C->ncols);

@@ -80,6 +80,15 @@ struct m4ri_b200_dmat {
 namespace m4b {
 typedef m4ri_b200_dmat DMat;
 
+// ---- api.cu: device matrices and the device product, shared with elim.cu -------
+DMat *dmat_new(rci_t nrows, rci_t ncols, cudaStream_t s);   // zeroed, stream-ordered pool
+void dmat_delete(DMat *M, cudaStream_t s);
+DMat dwin(const DMat *M, int r0, int c0, int nr, int nc);   // window (c0 % 64 == 0), shares the words
+void upload(DMat *D, const mzd_t *H, cudaStream_t s);
+void download(mzd_t *H, const DMat *D, cudaStream_t s);
+// C (^)= A*B on device (algo: enum m4ri_b200_algo; cutoff: Strassen hint, 0 = tuned)
+void dmul(DMat *C, const DMat *A, const DMat *B, int clear, int algo, cudaStream_t s, int cutoff = 0);
+
 // ---- kernels_aux.cu ----------------------------------------------------------
 void k_zero(DMat *M, cudaStream_t s);
 void k_mask_excess(DMat *M, cudaStream_t s);

@@ -1,0 +1,632 @@
+// elim.cu — the consumers of multiplication: reduced row echelon form, inverse and
+// linear solve on the GPU, behind the reference's names
+//   mzd_echelonize / mzd_echelonize_pluq / mzd_echelonize_m4ri   m4ri-sys/src/echelonform.rs:16,27,36
+//   mzd_inv_m4ri                                                  m4ri-sys/src/brilliantrussian.rs:208
+//   mzd_solve_left                                                m4ri-sys/src/solve.rs:23
+// (call sites in m4ri-rust: BinMatrix::echelonize / rank / inverted and solve_left,
+// m4ri-rust/src/friendly/binary_matrix.rs:247-268,575-586).
+//
+// Algorithm (B200 design, not M4RI's PLE recursion): blocked Gauss-Jordan whose bulk work is ONE
+// accumulating GF(2) product per column block on the tensor path — the same "trailing update is
+// a matrix product" structure that makes M4RI's PLE fast, with the product being
+// m4ri_b200's dmul(clear = 0).
+//
+// For a block of B columns [c0, c0 + B):
+//   1. The block's columns of ALL rows are copied into a panel PT = [P | T], T = 0 ("tags").
+//   2. 64 columns at a time (one word column j of P): one CTA finds up to 64 pivots among the
+//      candidate rows (rows that are no pivot yet) by eliminating on that single word column,
+//      and reduces the pivot words among themselves; the augmented pivot rows are combined into
+//      R' (identity on the pivot columns) and every other row of the panel gets
+//      row ^= sum_k bit(row, pivot column k) * R'_k — a rank-64 update confined to the panel.
+//      A pivot row's tag gets its own selection index, so after the block T holds, for every
+//      row, the combination of the block's ORIGINAL pivot rows that the elimination added to it.
+//   3. Everything right of the block is updated with one product:
+//         W[:, c0+B:] ^= T (m x B) * OldPivotRows[:, c0+B:] (B x rest)        (tensor path)
+//      (columns left of the block need nothing: candidate rows are zero there).
+//   4. The panel is written back and the pivot rows are moved up to rows rank .. rank+kb-1 in
+//      pivot-column order.
+// The result is THE reduced row echelon form (unique), so parity with any other implementation
+// is bit-exact by construction; rank and pivot columns come with it.
+#include <algorithm>
+#include <unordered_map>
+#include <vector>
+
+#include "common.cuh"
+
+namespace m4b {
+namespace {
+
+constexpr int EB_DEFAULT = 1024;  // block width in columns (multiple of 128)
+constexpr int EB_MAX = 4096;
+
+struct ElimState {
+  int kp;                        // pivots of the current 64-column step
+  int kb;                        // pivots of the block before the current step
+  int kbn;                       // ... including the current step
+  int pr[64];                    // their rows
+  int pc[64];                    // their bit positions in the word column
+  unsigned long long ctag[64];   // row k of the inverse of the pivot words on the pivot columns
+  int blk_rows[EB_MAX];          // pivots of the block in selection order: row, column
+  int blk_cols[EB_MAX];
+};
+
+#ifdef M4RI_B200_PERF_HOOKS
+__device__ long long g_clk[16];
+__device__ long long g_it[64];
+#define CLK(i) do { if (threadIdx.x == 0 && c0 == 0 && j == 3) g_clk[i] = clock64(); } while (0)
+#else
+#define CLK(i) do {} while (0)
+#endif
+
+static inline unsigned cdiv(long long a, long long b) { return (unsigned)((a + b - 1) / b); }
+
+// PT[i] = [ W[i][cw0 .. cw0+bw) | 0 ... 0 ]  (words past the matrix width read as zero)
+__global__ void extract_panel_kernel(word *PT, int pstride, const word *W, int ws, int wwidth, int m, int cw0,
+                                     int bw) {
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (idx >= (long long)m * 2 * bw) return;
+  const int i = (int)(idx / (2 * bw)), w = (int)(idx % (2 * bw));
+  word v = 0;
+  if (w < bw && cw0 + w < wwidth) v = W[(size_t)i * ws + cw0 + w];
+  PT[(size_t)i * pstride + w] = v;
+}
+
+__global__ void writeback_panel_kernel(word *W, int ws, int wwidth, const word *PT, int pstride, int m, int cw0,
+                                       int bw) {
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (idx >= (long long)m * bw) return;
+  const int i = (int)(idx / bw), w = (int)(idx % bw);
+  if (cw0 + w < wwidth) W[(size_t)i * ws + cw0 + w] = PT[(size_t)i * pstride + w];
+}
+
+// One CTA: pivots of word column j of the panel among the candidate rows (row >= r0, not yet a
+// pivot of this block), 1024 rows at a time.
+//   all threads  forward-eliminate their row's word with the pivots found so far (tracking which
+//                pivots they absorbed) and compact the rows that are still non-zero;
+//   warp 0       takes the compacted rows 32 at a time and extracts pivots with ballot/shuffle
+//                (first non-zero lane, its lowest set bit). The pivots live in warp 0's
+//                registers (lane l holds pivots l and l + 32) and every new pivot is cleared
+//                from the earlier ones at once, so the set is always fully reduced — no
+//                shared-memory round trip per pivot and no reduction pass afterwards.
+//                Stops when all 64 columns have a pivot: for a random matrix after ~70 rows.
+// ctag[k] = the combination of the selected rows (selection order) that gives the k-th reduced
+// pivot word.
+__global__ void __launch_bounds__(1024)
+pivot_search_kernel(const word *PT, int pstride, int j, int m, int r0, unsigned char *ispiv, int *pidx,
+                    ElimState *st, int c0, word colmask /* valid columns of this word (pivot limit) */) {
+  __shared__ word pw[64], sw[1024];
+  __shared__ unsigned long long ctag[64], slt[1024];
+  __shared__ int pc[64], pr[64], srow[1024];
+  __shared__ int kp_s, cnt;
+  const int tid = threadIdx.x, lane = tid & 31;
+  CLK(0);
+  if (tid < 64 && tid < st->kp) pidx[st->pr[tid]] = 0;  // the previous step's pivot marks
+  __syncthreads();
+  if (tid == 0) {
+    kp_s = 0;
+    cnt = 0;
+    st->kb = st->kbn;  // the previous step's pivots are counted from now on
+  }
+  // warp 0: pivot `lane` in the A registers, pivot `lane + 32` in the B registers
+  word pwA = 0, pwB = 0;
+  unsigned long long ctA = 0, ctB = 0;
+  int pcA = 0, pcB = 0, prA = -1, prB = -1, kp = 0;
+  __syncthreads();
+  CLK(1);
+  for (int chunk0 = r0; chunk0 < m; chunk0 += 1024) {
+    const int kp0 = kp_s;
+    if (kp0 == 64) break;
+    const int row = chunk0 + tid;
+    word w = 0;
+    if (row < m) {
+      const unsigned char taken = ispiv[row];
+      w = PT[(size_t)row * pstride + j] & colmask;
+      if (taken) w = 0;
+    }
+    unsigned long long lt = 0;
+    for (int k = 0; k < kp0; k++) {  // branch-free: the shared-memory reads pipeline
+      const word sel = (word)0 - ((w >> pc[k]) & 1);
+      w ^= pw[k] & sel;
+      lt ^= ctag[k] & sel;
+    }
+    if (chunk0 == r0) CLK(2);
+    const unsigned nz = __ballot_sync(0xffffffffu, w != 0);
+    int base = 0;
+    if (lane == 0 && nz) base = atomicAdd(&cnt, __popc(nz));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (w) {
+      const int e = base + __popc(nz & ((1u << lane) - 1));
+      sw[e] = w;
+      slt[e] = lt;
+      srow[e] = row;
+    }
+    __syncthreads();
+    if (chunk0 == r0) CLK(3);
+    if (tid < 32) {
+      const int n = cnt;
+#ifdef M4RI_B200_PERF_HOOKS
+      long long t_fwd = 0, t_ext = 0; int n_groups = 0;
+#endif
+      for (int g = 0; g < n && kp < 64; g += 32) {
+#ifdef M4RI_B200_PERF_HOOKS
+        long long t0 = clock64(); n_groups++;
+#endif
+        // (loads unconditional and the warp explicitly converged: the full-mask ballots and
+        // shuffles below cost ~4x more when the compiler leaves the lanes past n diverged)
+        const int e = g + lane, ec = e < n ? e : 0;
+        word v = sw[ec];
+        unsigned long long vt = slt[ec];
+        const int vrow = srow[ec];
+        if (e >= n) { v = 0; vt = 0; }
+        __syncwarp();
+        const int kp_g = kp;
+        for (int k = kp0; k < kp_g; k++) {  // pivots found earlier in this chunk (published below)
+          const word sel = (word)0 - ((v >> pc[k]) & 1);
+          v ^= pw[k] & sel;
+          vt ^= ctag[k] & sel;
+        }
+#ifdef M4RI_B200_PERF_HOOKS
+        long long t1 = clock64(); t_fwd += t1 - t0;
+#endif
+        for (;;) {
+#ifdef M4RI_B200_PERF_HOOKS
+          if (kp < 8 && tid == 0 && c0 == 0 && j == 3) g_it[kp * 4] = clock64();
+#endif
+          const unsigned ball = __ballot_sync(0xffffffffu, v != 0);
+          if (!ball || kp == 64) break;
+#ifdef M4RI_B200_PERF_HOOKS
+          if (kp < 8 && tid == 0 && c0 == 0 && j == 3) g_it[kp * 4 + 1] = clock64();
+#endif
+          const int src = __ffs(ball) - 1;
+          const word pv = __shfl_sync(0xffffffffu, v, src);
+          const unsigned long long pt = __shfl_sync(0xffffffffu, vt, src) ^ (1ull << kp);
+          const int prow = __shfl_sync(0xffffffffu, vrow, src);
+          const int tp = __ffsll((long long)pv) - 1;
+#ifdef M4RI_B200_PERF_HOOKS
+          if (kp < 8 && tid == 0 && c0 == 0 && j == 3) g_it[kp * 4 + 2] = clock64();
+#endif
+          if ((pwA >> tp) & 1) { pwA ^= pv; ctA ^= pt; }  // keep the earlier pivots reduced
+          if ((pwB >> tp) & 1) { pwB ^= pv; ctB ^= pt; }
+          {
+            const word sel = lane == src ? 0 : (word)0 - ((v >> tp) & 1);
+            v = lane == src ? 0 : v ^ (pv & sel);
+            vt ^= pt & sel;
+          }
+          if (lane == (kp & 31)) {
+            if (kp < 32) { pwA = pv; ctA = pt; pcA = tp; prA = prow; }
+            else         { pwB = pv; ctB = pt; pcB = tp; prB = prow; }
+          }
+          kp++;
+        }
+#ifdef M4RI_B200_PERF_HOOKS
+        t_ext += clock64() - t1;
+#endif
+        // mark this group's pivots; publish the (reduced) set for the next group, the next
+        // chunk and the output
+        if (lane >= kp_g && lane < kp) { ispiv[prA] = 1; pidx[prA] = lane + 1; }
+        if (lane + 32 >= kp_g && lane + 32 < kp) { ispiv[prB] = 1; pidx[prB] = lane + 33; }
+        pw[lane] = pwA; pw[lane + 32] = pwB;
+        ctag[lane] = ctA; ctag[lane + 32] = ctB;
+        pc[lane] = pcA; pc[lane + 32] = pcB;
+        pr[lane] = prA; pr[lane + 32] = prB;
+        __syncwarp();
+      }
+      if (lane == 0) {
+        kp_s = kp;
+        cnt = 0;
+      }
+      if (chunk0 == r0) CLK(4);
+#ifdef M4RI_B200_PERF_HOOKS
+      if (chunk0 == r0 && tid == 0 && c0 == 0 && j == 3) { g_clk[8] = n; g_clk[9] = n_groups; g_clk[10] = t_fwd; g_clk[11] = t_ext; g_clk[12] = kp; }
+#endif
+    }
+    __syncthreads();
+  }
+  CLK(5);
+  const int n = kp_s;
+  if (tid < 64) {
+    const int kb = st->kbn;  // == the new kb (set above by thread 0; kbn itself is rewritten below)
+    st->pr[tid] = tid < n ? pr[tid] : -1;
+    st->pc[tid] = tid < n ? pc[tid] : 0;
+    st->ctag[tid] = tid < n ? ctag[tid] : 0;
+    if (tid < n) {
+      st->blk_rows[kb + tid] = pr[tid];
+      st->blk_cols[kb + tid] = c0 + 64 * j + pc[tid];
+    }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    st->kp = n;
+    st->kbn = st->kbn + n;
+  }
+  CLK(6);
+}
+
+// Step preparation, one launch:
+//   CTAs [0, nrc)   4 words w of [j, L) per CTA: R'[k][w] = XOR over l in ctag[k] of
+//                   PT[pr[l]][w], plus the tag bits kb + l (the pivot rows' words are staged in
+//                   shared memory), then the 16 four-bit tables of the step
+//                       Tab[g][v][w] = XOR over bits b of v of R'[4g + b][w]
+//   CTAs [nrc, ..)  mult[i] bit k = bit pc[k] of the OLD word j of row i, for every row
+constexpr int RP_XW = 4;
+__global__ void __launch_bounds__(256)
+prepare_step_kernel(word *Tab, unsigned long long *mult, int L, const word *PT, int pstride, int j, int bw, int m,
+                    int nrc, const ElimState *st) {
+  __shared__ word srows[64 * RP_XW], srp[64 * RP_XW];
+  __shared__ int spc[64];
+  const int kp = st->kp, t = threadIdx.x;
+  if ((int)blockIdx.x >= nrc) {
+    if (t < 64) spc[t] = st->pc[t];
+    __syncthreads();
+    const int i = (blockIdx.x - nrc) * 256 + t;
+    if (i >= m) return;
+    const word w = PT[(size_t)i * pstride + j];
+    unsigned long long mm = 0;
+    for (int k = 0; k < kp; k++) mm |= ((w >> spc[k]) & 1ull) << k;
+    mult[i] = mm;
+    return;
+  }
+  const int k = t / RP_XW, xx = t % RP_XW, w = j + blockIdx.x * RP_XW + xx;
+  const bool live = w < L;
+  if (live && k < kp) srows[t] = PT[(size_t)st->pr[k] * pstride + w];
+  __syncthreads();
+  word acc = 0;
+  if (live && k < kp) {
+    const unsigned long long c_all = st->ctag[k];
+    unsigned long long c = c_all;
+    while (c) {
+      const int l = __ffsll((long long)c) - 1;
+      c &= c - 1;
+      acc ^= srows[l * RP_XW + xx];
+    }
+    if (w >= bw) {  // tag part: selected row l carries tag bit kb + l
+      const int kb = st->kb, sh = kb & 63, tw = w - bw;
+      if (tw == (kb >> 6)) acc ^= c_all << sh;
+      else if (sh && tw == (kb >> 6) + 1) acc ^= c_all >> (64 - sh);
+    }
+  }
+  srp[t] = acc;
+  __syncthreads();
+  if (!live) return;
+#pragma unroll
+  for (int q = 0; q < 4; q++) {
+    const int e = k + 64 * q, g = e >> 4, v = e & 15;  // table g, entry v
+    const word *r4 = srp + (4 * g) * RP_XW + xx;
+    word o = 0;
+    if (v & 1) o ^= r4[0];
+    if (v & 2) o ^= r4[RP_XW];
+    if (v & 4) o ^= r4[2 * RP_XW];
+    if (v & 8) o ^= r4[3 * RP_XW];
+    Tab[(size_t)e * L + w] = o;
+  }
+}
+
+// Every (row, word): PT[i][w] ^= sum over k in mult[i] of R'[k][w], w in [j, L), as 16 table
+// look-ups (4 multiplier bits each); the pivot rows of the step become R'. One thread per word;
+// the tables (256 x L words, 64 KB at the default block width) are read through L1 and all 16
+// loads are in flight together.
+__global__ void __launch_bounds__(256)
+apply_rprime_kernel(word *PT, int pstride, int j, int L, int m, const int *pidx, const unsigned long long *mult,
+                    const word *__restrict__ Tab, const ElimState *st) {
+  if (st->kp == 0) return;
+  const int LW = L - j;
+  const long long idx = blockIdx.x * 256LL + threadIdx.x;
+  if (idx >= (long long)m * LW) return;
+  const int i = (int)(idx / LW), w = j + (int)(idx % LW);
+  const int pk = pidx[i];
+  const unsigned long long mm = mult[i];
+  word *dst = PT + (size_t)i * pstride + w;
+  if (pk) {  // pivot pk - 1 of this step (the mark is cleared by the next step's search)
+    *dst = Tab[(size_t)(((pk - 1) >> 2) * 16 + (1 << ((pk - 1) & 3))) * L + w];
+    return;
+  }
+  if (!mm) return;
+  const word *tp = Tab + w;
+  word acc = 0;
+#pragma unroll
+  for (int g = 0; g < 16; g++)
+    acc ^= __ldg(tp + (size_t)(g * 16 + (int)((mm >> (4 * g)) & 15)) * L);
+  *dst ^= acc;
+}
+
+// OP[t][:] = W[blk_rows[t]][tw0 .. tw0+tw) for t < kb (other rows of OP stay zero);
+// and T[blk_rows[t]] ^= e_t: a pivot row is REPLACED by its combination, i.e. it also loses itself
+__global__ void gather_pivot_rows_kernel(word *OP, int ostride, const word *W, int ws, int tw0, int tw,
+                                         word *PT, int pstride, int bw, const ElimState *st) {
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const int kb = st->kbn;
+  if (idx >= (long long)kb * (tw + 1)) return;
+  const int t = (int)(idx / (tw + 1)), w = (int)(idx % (tw + 1));
+  const int row = st->blk_rows[t];
+  if (w < tw) OP[(size_t)t * ostride + w] = W[(size_t)row * ws + tw0 + w];
+  else PT[(size_t)row * pstride + bw + (t >> 6)] ^= (word)1 << (t & 63);
+}
+
+// rows dst[q] of W := rows src[q] (through a compact temporary)
+__global__ void gather_rows_kernel(word *tmp, const word *W, int ws, int width, const int *src, int cnt) {
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (idx >= (long long)cnt * width) return;
+  const int q = (int)(idx / width), w = (int)(idx % width);
+  tmp[idx] = W[(size_t)src[q] * ws + w];
+}
+__global__ void scatter_rows_kernel(word *W, int ws, int width, const word *tmp, const int *dst, int cnt) {
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (idx >= (long long)cnt * width) return;
+  const int q = (int)(idx / width), w = (int)(idx % width);
+  W[(size_t)dst[q] * ws + w] = tmp[idx];
+}
+
+__global__ void set_identity_kernel(word *W, int ws, int n, int col0) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) W[(size_t)i * ws + (col0 + i) / 64] |= (word)1 << ((col0 + i) % 64);
+}
+
+static int block_width() {
+  static const int b = [] {
+    const char *e = getenv("M4RI_B200_ELIM_BLOCK");
+    int v = e ? atoi(e) : EB_DEFAULT;
+    v = v / 128 * 128;
+    return v < 128 ? 128 : (v > EB_MAX ? EB_MAX : v);
+  }();
+  return b;
+}
+
+}  // namespace
+
+// Reduced row echelon form of W in place, pivots searched in columns [0, pivot_cols) only (the
+// rest is carried along: the right-hand side of a solve, the identity of an inversion).
+// Returns the rank; pivots (if given) receives the pivot columns in increasing order.
+int k_rref(DMat *W, int pivot_cols, std::vector<int> *pivots, cudaStream_t s) {
+  const int m = W->nrows, n = W->ncols;
+  if (pivots) pivots->clear();
+  if (m == 0 || n == 0 || pivot_cols <= 0) return 0;
+  if (pivot_cols > n) pivot_cols = n;
+  if (((uintptr_t)W->d & 15) || (W->rowstride & 1)) die("m4ri_b200: rref needs 16-byte aligned rows\n");
+  const int B = block_width(), bw = B / 64, L = 2 * bw;
+  DMat *PT = dmat_new(m, 2 * B, s);       // [panel | tags], stride L
+  DMat *OP = dmat_new(B, n, s);           // original pivot rows of the block (trailing columns)
+  const int pstride = PT->rowstride, ws = W->rowstride;
+  ElimState *st;
+  unsigned char *ispiv;
+  int *pidx;
+  unsigned long long *mult;
+  word *Rp, *tmp;
+  int *perm;
+  M4B_CUDA(cudaMallocAsync(&st, sizeof(ElimState), s));
+  M4B_CUDA(cudaMallocAsync(&ispiv, (size_t)m, s));
+  M4B_CUDA(cudaMallocAsync(&mult, (size_t)m * 8, s));
+  M4B_CUDA(cudaMallocAsync(&pidx, (size_t)m * sizeof(int), s));
+  M4B_CUDA(cudaMemsetAsync(pidx, 0, (size_t)m * sizeof(int), s));
+  M4B_CUDA(cudaMallocAsync(&Rp, (size_t)256 * L * 8, s));  // the step's 16 four-bit tables
+  M4B_CUDA(cudaMallocAsync(&tmp, (size_t)2 * B * W->width * 8, s));
+  M4B_CUDA(cudaMallocAsync(&perm, (size_t)4 * B * sizeof(int), s));
+  std::vector<int> h_rows(EB_MAX), h_cols(EB_MAX), src, dst;
+  int rank = 0;
+  for (int c0 = 0; c0 < pivot_cols && rank < m; c0 += B) {
+    const int cw0 = c0 / 64;
+    const int bcols = std::min(B, pivot_cols - c0);            // columns of this block that may hold pivots
+    const int steps = (bcols + 63) / 64;
+    M4B_CUDA(cudaMemsetAsync(st, 0, sizeof(ElimState), s));
+    M4B_CUDA(cudaMemsetAsync(ispiv, 0, (size_t)m, s));
+    M4B_CUDA(cudaMemsetAsync(pidx, 0, (size_t)m * sizeof(int), s));
+    extract_panel_kernel<<<cdiv((long long)m * L, 256), 256, 0, s>>>(PT->d, pstride, W->d, ws, W->width, m, cw0, bw);
+    M4B_LAUNCHED();
+    for (int j = 0; j < steps; j++) {
+      const int valid = std::min(64, bcols - 64 * j);
+      const word colmask = valid == 64 ? ~(word)0 : (((word)1 << valid) - 1);
+      pivot_search_kernel<<<1, 1024, 0, s>>>(PT->d, pstride, j, m, rank, ispiv, pidx, st, c0, colmask);
+      M4B_LAUNCHED();
+      const int nrc = (int)cdiv(L - j, RP_XW);
+      prepare_step_kernel<<<nrc + cdiv(m, 256), 256, 0, s>>>(Rp, mult, L, PT->d, pstride, j, bw, m, nrc, st);
+      M4B_LAUNCHED();
+      apply_rprime_kernel<<<cdiv((long long)m * (L - j), 256), 256, 0, s>>>(PT->d, pstride, j, L, m, pidx, mult, Rp, st);
+      M4B_LAUNCHED();
+    }
+    // pivots of the block -> host (one small synchronising copy per block)
+    int kb = 0;
+    M4B_CUDA(cudaMemcpyAsync(&kb, &st->kbn, sizeof(int), cudaMemcpyDeviceToHost, s));
+    M4B_CUDA(cudaStreamSynchronize(s));
+    if (kb > 0) {
+      M4B_CUDA(cudaMemcpyAsync(h_rows.data(), st->blk_rows, (size_t)kb * sizeof(int), cudaMemcpyDeviceToHost, s));
+      M4B_CUDA(cudaMemcpyAsync(h_cols.data(), st->blk_cols, (size_t)kb * sizeof(int), cudaMemcpyDeviceToHost, s));
+      // trailing update: everything right of the block
+      const int t0 = c0 + B;  // first trailing column (multiple of 128)
+      if (t0 < n) {
+        const int tw0 = t0 / 64, tw = W->width - tw0;
+        M4B_CUDA(cudaMemset2DAsync(OP->d, (size_t)OP->rowstride * 8, 0, (size_t)tw * 8, B, s));
+        gather_pivot_rows_kernel<<<cdiv((long long)kb * (tw + 1), 256), 256, 0, s>>>(OP->d, OP->rowstride, W->d, ws, tw0, tw,
+                                                                                      PT->d, pstride, bw, st);
+        M4B_LAUNCHED();
+        DMat Wt = dwin(W, 0, t0, m, n - t0), Tg = dwin(PT, 0, B, m, B), Ot = dwin(OP, 0, 0, B, n - t0);
+        dmul(&Wt, &Tg, &Ot, 0, M4RI_B200_ALGO_AUTO, s);
+      }
+      writeback_panel_kernel<<<cdiv((long long)m * bw, 256), 256, 0, s>>>(W->d, ws, W->width, PT->d, pstride, m, cw0, bw);
+      M4B_LAUNCHED();
+      M4B_CUDA(cudaStreamSynchronize(s));
+      // pivot rows up to rows rank .. rank+kb-1 in pivot-column order (sequential swaps, composed on the host)
+      std::vector<std::pair<int, int>> pv(kb);
+      for (int t = 0; t < kb; t++) pv[t] = {h_cols[t], h_rows[t]};
+      std::sort(pv.begin(), pv.end());
+      // sparse view of the permutation: position -> row whose content ends there, and its inverse
+      std::unordered_map<int, int> moved, where;
+      auto content_at = [&](int pos) { auto it = moved.find(pos); return it == moved.end() ? pos : it->second; };
+      auto pos_of = [&](int row) { auto it = where.find(row); return it == where.end() ? row : it->second; };
+      for (int t = 0; t < kb; t++) {
+        const int target = rank + t, prow = pv[t].second;
+        const int cur = pos_of(prow);          // where the pivot row is now
+        if (cur == target) continue;
+        const int other = content_at(target);  // what sits at the target position
+        moved[target] = prow; where[prow] = target;
+        moved[cur] = other; where[other] = cur;
+      }
+      src.clear(); dst.clear();
+      for (auto &e : moved)
+        if (e.first != e.second) { dst.push_back(e.first); src.push_back(e.second); }
+      if (!src.empty()) {
+        const int cnt = (int)src.size();
+        M4B_CUDA(cudaMemcpyAsync(perm, src.data(), (size_t)cnt * sizeof(int), cudaMemcpyHostToDevice, s));
+        M4B_CUDA(cudaMemcpyAsync(perm + 2 * B, dst.data(), (size_t)cnt * sizeof(int), cudaMemcpyHostToDevice, s));
+        gather_rows_kernel<<<cdiv((long long)cnt * W->width, 256), 256, 0, s>>>(tmp, W->d, ws, W->width, perm, cnt);
+        M4B_LAUNCHED();
+        scatter_rows_kernel<<<cdiv((long long)cnt * W->width, 256), 256, 0, s>>>(W->d, ws, W->width, tmp, perm + 2 * B, cnt);
+        M4B_LAUNCHED();
+        M4B_CUDA(cudaStreamSynchronize(s));  // src/dst are reused by the next block
+      }
+      if (pivots)
+        for (int t = 0; t < kb; t++) pivots->push_back(pv[t].first);
+      rank += kb;
+    }
+  }
+  M4B_CUDA(cudaFreeAsync(st, s));
+  M4B_CUDA(cudaFreeAsync(ispiv, s));
+  M4B_CUDA(cudaFreeAsync(pidx, s));
+  M4B_CUDA(cudaFreeAsync(mult, s));
+  M4B_CUDA(cudaFreeAsync(Rp, s));
+  M4B_CUDA(cudaFreeAsync(tmp, s));
+  M4B_CUDA(cudaFreeAsync(perm, s));
+  dmat_delete(PT, s);
+  dmat_delete(OP, s);
+  return rank;
+}
+
+void k_set_identity(DMat *W, int n, int col0, cudaStream_t s) {
+  if (n <= 0) return;
+  set_identity_kernel<<<cdiv(n, 256), 256, 0, s>>>(W->d, W->rowstride, n, col0);
+  M4B_LAUNCHED();
+}
+
+}  // namespace m4b
+
+using namespace m4b;
+
+extern "C" {
+
+#ifdef M4RI_B200_PERF_HOOKS
+void m4ri_b200_elim_clocks(long long *out) { M4B_CUDA(cudaMemcpyFromSymbol(out, g_clk, sizeof(long long) * 16)); }
+void m4ri_b200_elim_iters(long long *out) { M4B_CUDA(cudaMemcpyFromSymbol(out, g_it, sizeof(long long) * 64)); }
+#endif
+
+// ---- device-resident forms (additive API) --------------------------------------------
+int m4ri_b200_drref(m4ri_b200_dmat_t *W, int pivot_cols, int *pivot_columns, int max_pivots) {
+  std::vector<int> pv;
+  const int r = k_rref(W, pivot_cols <= 0 ? W->ncols : pivot_cols, &pv, current_stream());
+  if (pivot_columns)
+    for (int i = 0; i < r && i < max_pivots; i++) pivot_columns[i] = pv[i];
+  return r;
+}
+
+// ---- host ABI: the reference's names ---------------------------------------------------
+static rci_t host_echelonize(mzd_t *A, const char *who) {
+  (void)who;
+  if (A->nrows == 0 || A->ncols == 0) return 0;
+  cudaStream_t s = current_stream();
+  DMat *dA = dmat_new(A->nrows, A->ncols, s);
+  upload(dA, A, s);
+  const int r = k_rref(dA, A->ncols, nullptr, s);
+  download(A, dA, s);
+  dmat_delete(dA, s);
+  M4B_CUDA(cudaStreamSynchronize(s));
+  return r;
+}
+
+// (Reduced) row echelon form in place; returns the rank. `full == 0` asks only for an upper
+// triangular form: the reduced form returned here is one (echelonform.rs:9-16).
+rci_t mzd_echelonize(mzd_t *A, int full) {
+  (void)full;
+  return host_echelonize(A, "mzd_echelonize");
+}
+rci_t mzd_echelonize_pluq(mzd_t *A, int full) {
+  (void)full;
+  return host_echelonize(A, "mzd_echelonize_pluq");
+}
+rci_t mzd_echelonize_m4ri(mzd_t *A, int full, int k) {
+  (void)full;
+  (void)k;
+  return host_echelonize(A, "mzd_echelonize_m4ri");
+}
+
+// dst = src^-1 (NULL: allocate), NULL when src is singular. [src | I] -> [I | src^-1].
+mzd_t *mzd_inv_m4ri(mzd_t *dst, const mzd_t *src, int k) {
+  (void)k;
+  const rci_t n = src->nrows;
+  if (src->ncols != n) die("m4ri_b200: mzd_inv_m4ri: matrix must be square (%d x %d)\n", src->nrows, src->ncols);
+  if (dst && (dst->nrows != n || dst->ncols != n)) die("m4ri_b200: mzd_inv_m4ri: dst has wrong dimensions\n");
+  if (dst == src) die("m4ri_b200: mzd_inv_m4ri: dst must not alias src\n");
+  if (n == 0) return dst ? dst : mzd_init(0, 0);
+  cudaStream_t s = current_stream();
+  // the identity starts on a 128-bit boundary so that the inverse is an aligned window
+  const rci_t off = (n + 127) / 128 * 128;
+  DMat *W = dmat_new(n, off + n, s);
+  DMat left = dwin(W, 0, 0, n, n);
+  upload(&left, src, s);
+  k_set_identity(W, n, off, s);
+  const int r = k_rref(W, n, nullptr, s);
+  mzd_t *out = nullptr;
+  if (r == n) {
+    out = dst ? dst : mzd_init_impl(n, n, 0);
+    DMat right = dwin(W, 0, off, n, n);
+    download(out, &right, s);
+  }
+  dmat_delete(W, s);
+  M4B_CUDA(cudaStreamSynchronize(s));
+  return out;
+}
+
+// Solves A X = B; X overwrites the first ncols(A) rows of B (the rest of B is zeroed). Returns 0,
+// or -1 when the system is inconsistent (B is then left untouched). Free variables are zero.
+// A is "overwritten" in the reference (solve.rs:18); here it is left as it was.
+int mzd_solve_left(mzd_t *A, mzd_t *B, int cutoff, int inconsistency_check) {
+  (void)cutoff;
+  (void)inconsistency_check;  // the check is free here: always done
+  const rci_t m = A->nrows, n = A->ncols, k = B->ncols;
+  if (B->nrows < n) die("m4ri_b200: mzd_solve_left: A ncols (%d) need to be lower than B nrows (%d)\n", n, B->nrows);
+  if (B->nrows < m) die("m4ri_b200: mzd_solve_left: A nrows (%d) need to be lower than B nrows (%d)\n", m, B->nrows);
+  if (m == 0 || n == 0 || k == 0) return 0;
+  cudaStream_t s = current_stream();
+  const rci_t off = (n + 127) / 128 * 128;
+  DMat *W = dmat_new(m, off + k, s);
+  DMat left = dwin(W, 0, 0, m, n), right = dwin(W, 0, off, m, k);
+  upload(&left, A, s);
+  {  // rows [0, m) of B
+    mzd_t Bv = *B;
+    Bv.nrows = m;
+    DMat Rt = right;
+    upload(&Rt, &Bv, s);
+  }
+  std::vector<int> piv;
+  const int r = k_rref(W, n, &piv, s);
+  // consistent iff the rows below the rank are zero in the right part
+  int ok = 1;
+  if (r < m) {
+    DMat rest = dwin(W, r, off, m - r, k);
+    ok = k_is_zero(&rest, s) ? 1 : 0;
+  }
+  if (ok) {
+    // X[pivot column t] = right part of row t; other rows of X (free variables) are zero
+    mzd_t *R = mzd_init_impl(r > 0 ? r : 1, k, 1);
+    if (r > 0) {
+      DMat top = dwin(W, 0, off, r, k);
+      mzd_t Rv = *R;
+      Rv.nrows = r;
+      download(&Rv, &top, s);
+    }
+    M4B_CUDA(cudaStreamSynchronize(s));
+    for (rci_t i = 0; i < B->nrows; i++) {
+      word *row = B->rows[i];
+      for (wi_t w = 0; w + 1 < B->width; w++) row[w] = 0;
+      if (B->width) row[B->width - 1] &= ~B->high_bitmask;
+    }
+    for (int t = 0; t < r; t++) {
+      word *row = B->rows[piv[t]];
+      const word *srcw = R->rows[t];
+      for (wi_t w = 0; w + 1 < B->width; w++) row[w] = srcw[w];
+      if (B->width) row[B->width - 1] |= srcw[B->width - 1] & B->high_bitmask;
+    }
+    mzd_free(R);
+  }
+  dmat_delete(W, s);
+  M4B_CUDA(cudaStreamSynchronize(s));
+  return ok ? 0 : -1;
+}
+
+}  // extern "C"

@@ -43,6 +43,7 @@ def lib():
             "oracle_add": (None, [u64p, i, u64p, i, u64p, i, i, i]),
             "oracle_freivalds": (i, [u64p, i, u64p, i, u64p, i, i, i, i, u64]),
             "oracle_max_threads": (i, []),
+            "oracle_rref": (i, [u64p, i, i, i, i, u64p]),
         }
         for name, (res, args) in sig.items():
             f = getattr(_lib, name)
@@ -161,9 +162,11 @@ def from_bits(bits):
     bits = np.asarray(bits, dtype=np.uint8)
     nrows, ncols = bits.shape
     M = zeros(nrows, ncols)
-    for r in range(nrows):
-        for c in np.flatnonzero(bits[r]):
-            M[r, c // 64] |= np.uint64(1) << np.uint64(c % 64)
+    w = width(ncols)
+    if nrows and w:
+        padded = np.zeros((nrows, w * 64), dtype=np.uint8)
+        padded[:, :ncols] = bits & 1
+        M[:, :w] = np.packbits(padded, axis=1, bitorder="little").view(np.uint64).reshape(nrows, w)
     return M
 
 
@@ -173,3 +176,45 @@ def to_bits(M, ncols):
     for c in range(ncols):
         out[:, c] = (M[:, c // 64] >> np.uint64(c % 64)) & np.uint64(1)
     return out
+
+
+def rref(M, n, pivot_cols=None):
+    """Reduced row echelon form of M (m x n bits): (R, rank, pivot columns). Pivots only in
+    columns [0, pivot_cols)."""
+    R = np.ascontiguousarray(M).copy()
+    m = R.shape[0]
+    piv = np.zeros(max(1, min(m, n)), dtype=np.int32)
+    r = int(lib().oracle_rref(_p(R), R.shape[1], m, n, n if pivot_cols is None else pivot_cols, piv.ctypes.data))
+    return R, r, piv[:r].copy()
+
+
+def concat_bits(A, na, B, nb):
+    """[A | B] at arbitrary bit offsets (rows of na and nb valid bits)."""
+    a = np.unpackbits(np.ascontiguousarray(A[:, : width(na)]).view(np.uint8), axis=1, bitorder="little")[:, :na]
+    b = np.unpackbits(np.ascontiguousarray(B[:, : width(nb)]).view(np.uint8), axis=1, bitorder="little")[:, :nb]
+    return from_bits(np.concatenate([a, b], axis=1))
+
+
+def inverse(A, n):
+    """A^-1 (n x n) or None when A is singular: RREF of [A | I]."""
+    I = np.zeros((n, width(n)), dtype=np.uint64)
+    for i in range(n):
+        I[i, i // 64] |= np.uint64(1) << np.uint64(i % 64)
+    R, r, piv = rref(concat_bits(A, n, I, n), 2 * n, pivot_cols=n)
+    if r < n:
+        return None
+    bits = np.unpackbits(R.view(np.uint8), axis=1, bitorder="little")[:, n:2 * n]
+    return from_bits(bits)
+
+
+def solve_left(A, n, B, k):
+    """X (n x k) with A X = B and the free variables zero, or None when inconsistent."""
+    m = A.shape[0]
+    R, r, piv = rref(concat_bits(A, n, B, k), n + k, pivot_cols=n)
+    bits = np.unpackbits(R.view(np.uint8), axis=1, bitorder="little")[:, n:n + k]
+    if bits[r:].any():
+        return None
+    X = np.zeros((n, k), dtype=np.uint8)
+    for t in range(r):
+        X[piv[t]] = bits[t]
+    return from_bits(X)

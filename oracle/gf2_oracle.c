@@ -30,6 +30,8 @@
  *   C (^)= A*Bt^T with `clear`                          m4ri-sys/src/mzd.rs:154-168
  *   C (^)= v*A with `clear`                             m4ri-sys/src/mzd.rs:175-181
  *   transpose, add                                      m4ri-sys/src/mzd.rs:148,223
+ *   echelon form / rank, inverse, solve (oracle_rref)   m4ri-sys/src/echelonform.rs:16,
+ *                                                       brilliantrussian.rs:208, solve.rs:23
  *
  * Matrices are plain arrays of 64-bit words, row-major, `stride` words per row,
  * `ncols` valid bits per row; bits beyond ncols are kept zero on output.
@@ -381,6 +383,45 @@ int oracle_freivalds(const word *C, int cs, const word *A, int as, const word *B
   int ok = memcmp(ABX, CX, sizeof(word) * (size_t)m) == 0;
   free(X); free(BX); free(ABX); free(CX);
   return ok;
+}
+
+/* ---- consumers of the product: Gauss-Jordan from the definition -----------
+ * Reduced row echelon form in place, pivots searched in columns [0, pivot_cols) only, leftmost
+ * column first, first row with the bit set swapped up (textbook elimination; what
+ * mzd_echelonize(A, 1) returns is this form, m4ri-sys/src/echelonform.rs:9-16 — the reduced row
+ * echelon form of a matrix is unique, so the row chosen as pivot does not matter). Returns the
+ * rank; pivcols (rank entries, may be NULL) receives the pivot columns. */
+int oracle_rref(word *M, int stride, int m, int n, int pivot_cols, int *pivcols) {
+  const int width = width_of(n);
+  int rank = 0;
+  if (pivot_cols > n) pivot_cols = n;
+  for (int c = 0; c < pivot_cols && rank < m; c++) {
+    const int cw = c / 64;
+    const word bit = (word)1 << (c % 64);
+    int p = -1;
+    for (int i = rank; i < m; i++)
+      if (M[(size_t)i * stride + cw] & bit) { p = i; break; }
+    if (p < 0) continue;
+    if (p != rank)
+      for (int w = 0; w < width; w++) {
+        word t = M[(size_t)p * stride + w];
+        M[(size_t)p * stride + w] = M[(size_t)rank * stride + w];
+        M[(size_t)rank * stride + w] = t;
+      }
+    const word *pr = M + (size_t)rank * stride;
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < m; i++) {
+      if (i == rank || !(M[(size_t)i * stride + cw] & bit)) continue;
+      word *row = M + (size_t)i * stride;
+      for (int w = cw; w < width; w++) row[w] ^= pr[w];
+      /* (words left of cw: the pivot row is zero there in every non-pivot column it could
+       * still touch only if an earlier column had no pivot — handle those too) */
+      for (int w = 0; w < cw; w++) row[w] ^= pr[w];
+    }
+    if (pivcols) pivcols[rank] = c;
+    rank++;
+  }
+  return rank;
 }
 
 int oracle_max_threads(void) {

@@ -1,0 +1,182 @@
+"""GPU parity of the consumers of multiplication behind the reference's names —
+mzd_echelonize / _pluq / _m4ri (m4ri-sys/src/echelonform.rs:16,27,36), mzd_inv_m4ri
+(brilliantrussian.rs:208), mzd_solve_left (solve.rs:23) and their BinMatrix wrappers
+(binary_matrix.rs:246-268, 575-586) — against the CPU oracle's Gauss-Jordan. The reduced row
+echelon form is unique, so the comparison is bit for bit."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def host(m4, words, ncols):
+    return m4.mzd_from_words(words, ncols)
+
+
+def low_rank(orc, m, n, r, seed):
+    """m x n matrix of rank <= r: product of random m x r and r x n factors."""
+    return orc.mul_m4rm(orc.random(m, r, seed), orc.random(r, n, seed + 1), r, n)
+
+
+SHAPES = [(1, 1), (5, 7), (64, 64), (65, 63), (100, 300), (300, 100), (1000, 1000), (1030, 2050), (2050, 1030),
+          (1500, 1500), (3000, 2500), (70, 5000), (5000, 70)]
+
+
+@pytest.mark.parametrize("entry", ["mzd_echelonize", "mzd_echelonize_pluq", "mzd_echelonize_m4ri"])
+def test_echelonize_matches_the_oracle(gpu, m4, orc, entry):
+    L = m4.lib()
+    for (m, n) in SHAPES:
+        for kind in ("random", "lowrank", "zero_cols"):
+            if kind == "random":
+                A = orc.random(m, n, 11 + m)
+            elif kind == "lowrank":
+                A = low_rank(orc, m, n, max(1, min(m, n) // 3), 5 + n)
+            else:  # pivots far apart: zero column blocks and duplicated rows
+                A = orc.random(m, n, 7)
+                A[:, : orc.width(n) // 2] = 0
+                A[m // 2:] = A[: m - m // 2]
+            want, r_want, piv = orc.rref(A, n)
+            a = host(m4, A, n)
+            r = L.mzd_echelonize_m4ri(a, 1, 0) if entry == "mzd_echelonize_m4ri" else getattr(L, entry)(a, 1)
+            assert r == r_want, (entry, m, n, kind, r, r_want)
+            got = m4.mzd_words(a)
+            assert not got[:, orc.width(n):].any()
+            assert (got[:, : orc.width(n)] == want[:, : orc.width(n)]).all(), (entry, m, n, kind)
+            L.mzd_free(a)
+
+
+def test_rank_and_echelonize_wrappers(gpu, m4, orc):
+    # BinMatrix::rank / echelonize (binary_matrix.rs:246-261)
+    I = m4.BinMatrix.identity(10)
+    assert I.rank() == 10 and I.echelonize() == 10 and I == m4.BinMatrix.identity(10)
+    A = low_rank(orc, 500, 700, 123, 3)
+    M = m4.BinMatrix(host(m4, A, 700))
+    before = M.clone()
+    assert M.rank() == orc.rref(A, 700)[1]
+    assert M == before  # rank() works on a clone
+
+
+def test_block_widths_agree(gpu, m4, orc, monkeypatch):
+    """The block width is a performance knob: every width gives the same (unique) form — run in
+    child processes because the width is read once."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = ("import sys; sys.path.insert(0, %r); import numpy as np, m4ri_rust_b200 as m4, oracle as orc; L = m4.lib();"
+            "ok = True\n"
+            "for (m, n, r) in [(1500, 2100, 0), (2000, 2000, 700), (900, 3000, 0)]:\n"
+            "    A = orc.random(m, n, 3) if r == 0 else orc.mul_m4rm(orc.random(m, r, 1), orc.random(r, n, 2), r, n)\n"
+            "    want, rk, piv = orc.rref(A, n); a = m4.mzd_from_words(A, n)\n"
+            "    ok &= L.mzd_echelonize(a, 1) == rk and bool((m4.mzd_words(a)[:, : orc.width(n)] == want[:, : orc.width(n)]).all())\n"
+            "print('ok' if ok else 'MISMATCH')") % root
+    for width in ("128", "256", "512", "2048", "4096"):
+        env = dict(os.environ, M4RI_B200_ELIM_BLOCK=width)
+        p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=600)
+        assert p.returncode == 0 and p.stdout.strip().endswith("ok"), (width, p.stdout[-500:], p.stderr[-2000:])
+
+
+def test_inverse(gpu, m4, orc):
+    L = m4.lib()
+    for n in (1, 2, 10, 64, 65, 200, 1000, 1025, 2048, 3000):
+        # random matrices over GF(2) are invertible with probability ~0.29: try seeds until one is
+        for seed in range(40):
+            A = orc.random(n, n, 100 * n + seed)
+            want = orc.inverse(A, n)
+            a = host(m4, A, n)
+            p = L.mzd_inv_m4ri(None, a, 0)
+            if want is None:
+                assert not p, (n, seed)
+                L.mzd_free(a)
+                continue
+            assert p, (n, seed)
+            got = m4.mzd_words(p)
+            assert not got[:, orc.width(n):].any()
+            assert (got[:, : orc.width(n)] == want[:, : orc.width(n)]).all(), (n, seed)
+            # A * A^-1 == I through the GPU product, and inverted() of the mirror
+            prod = L.mzd_mul(None, a, p, 0)
+            eye = L.mzd_init(n, n)
+            L.mzd_set_ui(eye, 1)
+            assert L.mzd_equal(prod, eye) == 1
+            # preallocated destination
+            d = L.mzd_init(n, n)
+            L.mzd_randomize(d)
+            assert L.mzd_inv_m4ri(d, a, 0) and L.mzd_equal(d, p) == 1
+            for q in (a, p, prod, eye, d):
+                L.mzd_free(q)
+            break
+        else:
+            pytest.fail(f"no invertible matrix found at n={n}")
+    with pytest.raises(ValueError):
+        m4.BinMatrix.zero(5, 5).inverted()
+    assert m4.BinMatrix.identity(70).inverted() == m4.BinMatrix.identity(70)
+
+
+def test_solve_left(gpu, m4, orc):
+    L = m4.lib()
+    for (m, n, k) in [(10, 10, 1), (64, 64, 64), (200, 200, 70), (1000, 1000, 300), (1500, 1000, 10), (700, 1000, 129),
+                      (2100, 2100, 1)]:
+        A = orc.random(m, n, 3 + m)
+        X0 = orc.random(n, k, 4 + k)
+        Bc = orc.mul_m4rm(A, X0, n, k)  # consistent by construction
+        want = orc.solve_left(A, n, Bc, k)
+        assert want is not None
+        rows = max(m, n)
+        Bfull = np.zeros((rows, Bc.shape[1]), dtype=np.uint64)
+        Bfull[:m] = Bc
+        a, b = host(m4, A, n), host(m4, Bfull, k)
+        assert L.mzd_solve_left(a, b, 0, 1) == 0
+        got = m4.mzd_words(b)
+        assert (got[:n, : orc.width(k)] == want[:, : orc.width(k)]).all(), (m, n, k)
+        assert not got[n:].any() and not got[:, orc.width(k):].any()
+        assert (m4.mzd_words(a)[:, : orc.width(n)] == A[:, : orc.width(n)]).all()  # A untouched
+        # A * X == B
+        x = host(m4, got[:n].copy(), k)
+        ax = L.mzd_mul(None, a, x, 0)
+        assert (m4.mzd_words(ax)[:, : orc.width(k)] == Bc[:, : orc.width(k)]).all()
+        for q in (a, b, x, ax):
+            L.mzd_free(q)
+    # inconsistent system: rank-deficient A, right-hand side outside its column space
+    m = n = 300
+    A = low_rank(orc, m, n, 100, 9)
+    Bbad = orc.random(m, 5, 77)
+    assert orc.solve_left(A, n, Bbad, 5) is None
+    a, b = host(m4, A, n), host(m4, Bbad, 5)
+    assert L.mzd_solve_left(a, b, 0, 1) == -1
+    assert (m4.mzd_words(b)[:, :1] == Bbad[:, :1]).all()  # untouched
+    # the mirror of friendly::solve_left (binary_matrix.rs:575-586)
+    Am, Bm = m4.BinMatrix.identity(20), m4.BinMatrix.random(20, 3)
+    want = Bm.clone()
+    assert m4.solve_left(Am, Bm) and Bm == want
+    for q in (a, b):
+        L.mzd_free(q)
+
+
+def test_device_rref_large(gpu, m4):
+    """n = 8192 device-resident: A^-1 from [A | I], checked by A * A^-1 == I with the product
+    kernels (size-independent property; the oracle's cubic loop stops at a few thousand)."""
+    import ctypes
+    L = m4.lib()
+    n = 8192
+    for seed in range(1, 30):
+        W = m4.DMat.init(n, 2 * n)
+        left = m4.DMat.wrap(W.ptr, n, n, W.rowstride, keepalive=W)
+        right = m4.DMat.wrap(W.ptr + (n // 64) * 8, n, n, W.rowstride, keepalive=W)
+        left.fill_random(seed)
+        A = m4.DMat.init(n, n)
+        L.m4ri_b200_dcopy(A.h, left.h)
+        heye = m4.BinMatrix.identity(n)  # (kept alive: the upload reads its rows[])
+        eye = m4.DMat.from_host(heye.mzd)
+        L.m4ri_b200_synchronize()
+        L.m4ri_b200_dcopy(right.h, eye.h)
+        piv = (ctypes.c_int * n)()
+        r = L.m4ri_b200_drref(W.h, n, piv, n)
+        if r < n:
+            continue
+        assert list(piv) == list(range(n))
+        L.m4ri_b200_dadd(left.h, left.h, eye.h)
+        assert L.m4ri_b200_dis_zero(left.h) == 1  # left half became the identity
+        P = m4.DMat.init(n, n)
+        m4.dmul(P, A, right)
+        L.m4ri_b200_dadd(P.h, P.h, eye.h)
+        assert L.m4ri_b200_dis_zero(P.h) == 1
+        return
+    pytest.fail("no invertible 8192 x 8192 matrix among the seeds")
