@@ -1,5 +1,6 @@
 // Builds (if needed) and links libm4ri_b200.so. Replaces the autoreconf/configure/make of the
-// vendored M4RI that m4ri-sys/build.rs:27-69 runs, for the multiplication path only.
+// vendored M4RI that m4ri-sys/build.rs:27-69 runs, for every symbol m4ri-rust references
+// (one allocator: never link a second libm4ri next to it).
 use std::{env, path::PathBuf, process::Command};
 
 fn main() {
@@ -18,9 +19,5 @@ fn main() {
     println!("cargo:rustc-link-search=native={}", lib.display());
     println!("cargo:rustc-link-lib=dylib=m4ri_b200");
     println!("cargo:rustc-link-arg=-Wl,-rpath,{}", lib.display());
-    if env::var("CARGO_FEATURE_FULL_M4RI").is_ok() {
-        // listed after m4ri_b200: the B200 definitions of the shared names win at link time
-        println!("cargo:rustc-link-lib=dylib=m4ri");
-    }
     println!("cargo:rerun-if-env-changed=M4RI_B200_DIR");
 }

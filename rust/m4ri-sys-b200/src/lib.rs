@@ -1,4 +1,8 @@
-//! `extern "C"` surface of `libm4ri_b200.so` for the multiplication path of m4ri-rust.
+//! `extern "C"` surface of `libm4ri_b200.so` for the multiplication path of m4ri-rust and its
+//! immediate consumers (concat/stack, echelon form, inverse, solve) — every `m4ri-sys` symbol
+//! that `m4ri-rust/src/friendly/*.rs` references is exported by the one library, so no second
+//! allocator is ever linked in (mixing this library with a system libm4ri is unsupported:
+//! `mzd_free` dies on a descriptor it did not allocate).
 //!
 //! The names, argument order and the 64-byte matrix descriptor are the ones `m4ri-sys`
 //! declares for the M4RI C library (`include/m4ri_b200.h` cites the `m4ri-sys` line next to
@@ -63,6 +67,9 @@ extern "C" {
     pub fn mzd_transpose(dst: *mut Mzd, a: *const Mzd) -> *mut Mzd;
     pub fn mzd_add(c: *mut Mzd, a: *const Mzd, b: *const Mzd) -> *mut Mzd;
     pub fn mzd_sub(c: *mut Mzd, a: *const Mzd, b: *const Mzd) -> *mut Mzd;
+    /// [A | B] (`BinMatrix::augmented`, binary_matrix.rs:271-276) and A over B (`stacked`, 279-283).
+    pub fn mzd_concat(c: *mut Mzd, a: *const Mzd, b: *const Mzd) -> *mut Mzd;
+    pub fn mzd_stack(c: *mut Mzd, a: *const Mzd, b: *const Mzd) -> *mut Mzd;
 
     // ---- products (C == NULL: the library allocates, the caller frees with mzd_free) ----
     pub fn mzd_mul(c: *mut Mzd, a: *const Mzd, b: *const Mzd, cutoff: c_int) -> *mut Mzd;
@@ -76,6 +83,17 @@ extern "C" {
     pub fn _mzd_mul_va(c: *mut Mzd, v: *const Mzd, a: *const Mzd, clear: c_int) -> *mut Mzd;
     /// y = A*x with x (ncols x 1) and y (nrows x 1): the shape `BinMatrix::mul_slice` builds.
     pub fn mzd_mul_v(y: *mut Mzd, a: *const Mzd, x: *const Mzd) -> *mut Mzd;
+
+    // ---- consumers of the product: reduced row echelon form on the GPU (csrc/elim.cu) ----
+    /// Reduced row echelon form in place; returns the rank (`full` is accepted and ignored:
+    /// the result is always the fully reduced form, which is also a valid echelon form).
+    pub fn mzd_echelonize(a: *mut Mzd, full: c_int) -> Rci;
+    pub fn mzd_echelonize_pluq(a: *mut Mzd, full: c_int) -> Rci;
+    pub fn mzd_echelonize_m4ri(a: *mut Mzd, full: c_int, k: c_int) -> Rci;
+    /// NULL when `src` is singular.
+    pub fn mzd_inv_m4ri(dst: *mut Mzd, src: *const Mzd, k: c_int) -> *mut Mzd;
+    /// Solves A X = B, X in the first ncols(A) rows of B; 0 on success, -1 when inconsistent.
+    pub fn mzd_solve_left(a: *mut Mzd, b: *mut Mzd, cutoff: c_int, inconsistency_check: c_int) -> c_int;
 
     // ---- engine control ----
     pub fn m4ri_b200_set_algo(algo: c_int);
@@ -108,6 +126,10 @@ extern "C" {
     pub fn m4ri_b200_dmul_abt(c: *mut DMat, a: *const DMat, bt: *const DMat, clear: c_int, algo: c_int);
     pub fn m4ri_b200_dmul_v(y: *mut DMat, a: *const DMat, x: *const DMat, clear: c_int);
     pub fn m4ri_b200_dmul_va(c: *mut DMat, v: *const DMat, a: *const DMat, clear: c_int);
+    /// Y (b x nrows(A)) = rows of X (b x ncols(A)) each multiplied by A: b mat-vecs per pass over A.
+    pub fn m4ri_b200_dmul_v_batched(y: *mut DMat, a: *const DMat, x: *const DMat, clear: c_int);
+    /// Reduced row echelon form of a device matrix in place; returns the rank.
+    pub fn m4ri_b200_drref(w: *mut DMat, pivot_cols: c_int, pivot_columns: *mut c_int, max_pivots: c_int) -> c_int;
     pub fn m4ri_b200_dtranspose(dst: *mut DMat, a: *const DMat);
     pub fn m4ri_b200_dadd(c: *mut DMat, a: *const DMat, b: *const DMat);
     pub fn m4ri_b200_dcopy(dst: *mut DMat, a: *const DMat);
@@ -123,6 +145,18 @@ extern "C" {
 pub unsafe fn mzd_read_bit(m: *const Mzd, row: Rci, col: Rci) -> c_int {
     let words = *(*m).rows.offset(row as isize);
     ((*words.offset((col / 64) as isize) >> (col % 64)) & 1) as c_int
+}
+
+/// Sets bit (row, col) of a host matrix to `value & 1` (m4ri-sys/src/mzd.rs `mzd_write_bit`).
+///
+/// # Safety
+/// `m` must come from this library and `row`/`col` must be in range.
+#[inline]
+pub unsafe fn mzd_write_bit(m: *mut Mzd, row: Rci, col: Rci, value: c_int) {
+    let words = *(*m).rows.offset(row as isize);
+    let w = words.offset((col / 64) as isize);
+    let bit = 1u64 << (col % 64);
+    *w = (*w & !bit) | (((value & 1) as u64) << (col % 64));
 }
 
 #[cfg(test)]

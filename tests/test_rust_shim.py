@@ -59,3 +59,29 @@ def test_struct_fields_follow_the_header_order():
     fields = re.findall(r"pub (\w+):", body)
     assert fields == ["nrows", "ncols", "width", "rowstride", "offset_vector", "row_offset", "flags",
                       "blockrows_log", "padding", "high_bitmask", "blocks", "rows"]
+
+
+# Every C symbol m4ri-rust's own sources call (grep of m4ri-rust/src for mzd_* on the reference
+# checkout: friendly/binary_matrix.rs and friendly/binary_vector.rs; mzd_read_bit/mzd_write_bit are
+# inline Rust in m4ri-sys, mirrored in lib.rs). A user switching crates must find all of them.
+M4RI_RUST_USES = ("mzd_init", "mzd_free", "mzd_add", "mzd_equal", "mzd_mul_naive", "mzd_transpose", "mzd_stack",
+                  "mzd_solve_left", "mzd_set_ui", "mzd_randomize", "mzd_mul_m4rm", "mzd_mul", "mzd_inv_m4ri",
+                  "mzd_echelonize", "mzd_copy", "mzd_concat")
+
+
+def test_every_symbol_m4ri_rust_calls_is_bound_and_exported(m4):
+    rust = rust_decls()
+    so = os.path.join(ROOT, "m4ri-rust_b200", "lib", "libm4ri_b200.so")
+    out = subprocess.run(["nm", "-D", "--defined-only", so], capture_output=True, text=True, check=True).stdout
+    exported = {line.split()[-1] for line in out.splitlines() if line.strip()}
+    for name in M4RI_RUST_USES:
+        assert name in rust, f"{name} missing from rust/m4ri-sys-b200/src/lib.rs"
+        assert name in exported, f"{name} not exported by libm4ri_b200.so"
+    src = open(LIB_RS).read()
+    assert "pub unsafe fn mzd_read_bit" in src and "pub unsafe fn mzd_write_bit" in src
+
+
+def test_no_second_allocator_is_linked():
+    for f in ("Cargo.toml", "build.rs"):
+        text = open(os.path.join(ROOT, "rust", "m4ri-sys-b200", f)).read()
+        assert "full-m4ri" not in text and "dylib=m4ri\"" not in text
