@@ -539,6 +539,18 @@ def main():
                 "frac_of_measured_scaled_bf16": achieved / meas if achieved else None,
                 "peak_measured_source": "%d x bf16_tflops (burst) of MEASURED_PEAKS.json (%s): the dense %s rate is %dx bf16" % (
                     4 if fp4 else 2, pk["src"], "fp4" if fp4 else "int8", 4 if fp4 else 2)}
+        if fp4:
+            # the kind::mxf4 pipe rate measured under this kernel's own issue pattern and clocks
+            # (tools/fp4_peak.py, perf-hook build: expansion, drain and epilogue waits disabled)
+            try:
+                pm = json.load(open(os.path.join(ROOT, "profiles", "peaks_measured.json")))
+                mp = pm["fp4_pipe_back_to_back_ops_per_s"] / 1e12
+                roof["peak_measured_fp4"] = mp
+                roof["frac_of_measured_fp4"] = achieved / mp if achieved else None
+                roof["peak_measured_fp4_source"] = "profiles/peaks_measured.json fp4_pipe_back_to_back_ops_per_s (%s, %s)" % (
+                    pm.get("fp4_peak_shape"), pm.get("fp4_peak_how"))
+            except (OSError, KeyError, ValueError):
+                pass
     else:
         # Four-Russians gather: bound by shared-memory load bandwidth, measured by
         # m4ri-rust_b200/lib/microbench (profiles/); expressed in the metric's unit
@@ -551,13 +563,19 @@ def main():
                 "peak_source": "measured shared-memory load bandwidth x 512 bit-ops per 32-bit table word (t=8)"}
     # DRAM traffic of one launch of that kernel at the leaf shape, from the committed ncu capture
     try:
-        leaf = round((kern_ops / kern_count / 2.0) ** (1.0 / 3.0))
+        per_launch = kern_ops / kern_count / 2.0  # m*k*n of one launch
+        shape = None
+        for lv in range(4):  # the rank's row-block (n/world x n x n) after lv Strassen levels
+            mm, kk = n // world >> lv, n >> lv
+            if abs(mm * kk * kk - per_launch) < 1e-6 * per_launch:
+                shape = (mm, kk, kk)
         tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        ent = tj.get(f"{kern_name}@{leaf}x{leaf}x{leaf}") if world == 1 else None
+        ent = tj.get("%s@%dx%dx%d" % ((kern_name,) + shape)) if shape else None
         if ent:
             roof["traffic"] = ent["bytes"]
             roof["traffic_source"] = ent["source"]
-            roof["algorithmic_bytes"] = 3 * leaf * leaf // 8
+            roof["traffic_launch_shape"] = "%dx%dx%d" % shape
+            roof["algorithmic_bytes"] = (shape[0] * shape[1] + shape[1] * shape[2] + shape[0] * shape[2]) // 8
     except Exception:
         pass
     roof["kernel"] = kern_name

@@ -38,7 +38,22 @@ if ("--time" in sys.argv or "--time-only" in sys.argv) and bad == 0:
     import ctypes
     L.m4ri_b200_set_strassen_levels(int(os.environ.get("LEVELS", "0")))  # time the kernel itself
     sizes = [int(x) for x in os.environ["SIZES"].split(",")] if os.environ.get("SIZES") else None
-    for n in (sizes or ((32768,) if '--time-only' in sys.argv else (4096, 8192, 16384, 32768))):
+    # SHAPES=m:k:n,... times C (m x n) = A (m x k) * Bt^T (Bt n x k) instead of cubes
+    shapes = [tuple(int(v) for v in x.split(":")) for x in os.environ["SHAPES"].split(",")] if os.environ.get("SHAPES") else None
+    for n in (shapes or sizes or ((32768,) if '--time-only' in sys.argv else (4096, 8192, 16384, 32768))):
+        if isinstance(n, tuple):
+            (m_, k_, n_) = n
+            dA, dBt, dC = m4.DMat.init(m_, k_), m4.DMat.init(n_, k_), m4.DMat.init(m_, n_)
+            dA.fill_random(1); dBt.fill_random(2)
+            for _ in range(2):
+                m4.dmul_abt(dC, dA, dBt, clear=True, algo=m4.ALGO_MMA)
+            L.m4ri_b200_synchronize()
+            L.m4ri_b200_timing_reset()
+            for _ in range(5):
+                m4.dmul_abt(dC, dA, dBt, clear=True, algo=m4.ALGO_MMA)
+            ms = L.m4ri_b200_timing_ms() / 5
+            print(f"{variant} {m_}x{k_}x{n_}: {ms:.3f} ms  {2.0 * m_ * k_ * n_ / ms / 1e9:.1f} Tbit-op/s", flush=True)
+            continue
         dA, dB, dBt, dC = (m4.DMat.init(n, n) for _ in range(4))
         dA.fill_random(1); dB.fill_random(2)
         L.m4ri_b200_dtranspose(dBt.h, dB.h)
