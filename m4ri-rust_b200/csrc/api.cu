@@ -746,9 +746,8 @@ static bool peers_ready(int G) {  // under g_workers_mu
 }
 // called by worker `dev` (its device current): peers may read/write this device's pool memory
 static void open_pool_to_peers(int dev, int G) {
-  static std::atomic<unsigned long long> done{0};
-  const unsigned long long bit = 1ull << dev;
-  if (done.load() & bit) return;
+  static std::atomic<int> opened[64];  // number of leading devices this one is already open to
+  if (dev >= 64 || opened[dev].load() >= G) return;  // (set_devices may grow G between calls)
   cudaMemPool_t pool;
   M4B_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
   for (int p = 0; p < G; p++) {
@@ -762,7 +761,7 @@ static void open_pool_to_peers(int dev, int G) {
     if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) M4B_CUDA(e);
     (void)cudaGetLastError();
   }
-  done.fetch_or(bit);
+  opened[dev].store(G);
 }
 
 static void multi_worker(MultiJob *J, int g) {
