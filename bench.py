@@ -274,7 +274,20 @@ def run_lpn(args):
     for _ in range(reps):
         col = M.mul_slice(xw)
     e2e_ms = (time.perf_counter() - t0) * 1e3 / reps
-    out["matvec_via_mul_slice"] = {"ms": e2e_ms, "kernel": L.m4ri_b200_timing_name().decode(),
+    # the C call inside it alone (what a Rust host pays; the rest is the Python mirror's packing of
+    # x into a k x 1 mzd_t and of the m one-bit rows of the result back into words)
+    xcol = L.mzd_init(k, 1)
+    for i in range(k):
+        m4.mzd_words(xcol)[i, 0] = (int(xw[i // 64]) >> (i % 64)) & 1
+    for _ in range(2):
+        L.mzd_free(L.mzd_mul_naive(None, hA, xcol))
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        L.mzd_free(L.mzd_mul_naive(None, hA, xcol))
+    c_ms = (time.perf_counter() - t0) * 1e3 / reps
+    L.mzd_free(xcol)
+    out["matvec_via_mul_slice"] = {"ms": e2e_ms, "c_call_ms": c_ms, "c_call_pcie_gbs": m * w * 8 / c_ms / 1e6,
+                                   "kernel": L.m4ri_b200_timing_name().decode(),
                                    "h2d_bytes_per_call": m * w * 8, "d2h_bytes_per_call": (m // 64) * 8,
                                    "api": "BinMatrix.mul_slice -> mzd_transpose + mzd_mul_naive(NULL, A, x) on host mzd_t (binary_matrix.rs:416-431)",
                                    "pcie_gbs": m * w * 8 / e2e_ms / 1e6}

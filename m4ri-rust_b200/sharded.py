@@ -156,8 +156,9 @@ class FusedBroadcastMul:
     two device-side barriers per step order the peer stores against the products.
     """
 
-    def __init__(self, m4, m, k, n, dist, src=0):
+    def __init__(self, m4, m, k, n, dist, src=0, root_serves=None, chunks=None):
         import ctypes
+        import os
         import torch.distributed._symmetric_memory as symm_mem
         self.m4, self.L, self.dist, self.src = m4, m4.lib(), dist, src
         self.m, self.k, self.n = m, k, n
@@ -167,7 +168,20 @@ class FusedBroadcastMul:
         if k % 128 or n % 128:
             raise ValueError("k and n must be multiples of 128 bits")
         self.r0, self.rows = row_block(m, self.world, self.rank)
-        self.s0, self.srows = exchange_slab(k, self.world, self.rank, src)  # this rank's k-slab of B
+        # Plan of the exchange (tools/gpu_exchange.sh; defaults measured at N = 4 and 8):
+        #   root_serves  the root only serves its B, the other ranks share the slabs: the root's
+        #                NVLink egress is the bottleneck otherwise (reads served + its own stores)
+        #   chunks       a non-root rank pulls its slab with the copy engine in `chunks` pieces
+        #                into a local staging buffer while the scatter kernel works on the previous
+        #                piece: remote reads (ingress) overlap the peer stores (egress) instead of
+        #                alternating inside one kernel
+        if root_serves is None:
+            root_serves = os.environ.get("M4RI_B200_XCHG_ROOT_SERVES", "auto")
+            root_serves = (self.world >= 6) if root_serves == "auto" else root_serves == "1"
+        if chunks is None:
+            chunks = int(os.environ.get("M4RI_B200_XCHG_CHUNKS", "4"))
+        self.root_serves, self.chunks = bool(root_serves), max(1, chunks)
+        self.s0, self.srows = exchange_slab(k, self.world, self.rank, src, root_serves=self.root_serves)
         ws, kws = n // 64, k // 64
         dev = torch.device("cuda", torch.cuda.current_device())
         self.tB = symm_mem.empty((k, ws), dtype=torch.int64, device=dev)    # valid on src only
@@ -181,21 +195,53 @@ class FusedBroadcastMul:
         self.dC = D.wrap(self.tC.data_ptr(), self.rows, n, ws, keepalive=self.tC)
         self.dB = D.wrap(self.tB.data_ptr(), k, n, ws, keepalive=self.tB)
         self.dBt = D.wrap(self.tBt.data_ptr(), n, k, kws, keepalive=self.tBt)
+        self.pieces = []  # (source matrix, destination array, staging copy or None)
         if self.srows > 0:
-            src_ptr = int(self.hB.buffer_ptrs[src]) + self.s0 * ws * 8
-            self.dSlab = D.wrap(src_ptr, self.srows, n, ws, keepalive=self.tB)
-            self.dDst = [D.wrap(int(p) + (self.s0 // 64) * 8, n, self.srows, kws, keepalive=self.tBt)
-                         for p in self.hBt.buffer_ptrs]
-            self.dst_arr = (ctypes.c_void_p * self.world)(*[d.h for d in self.dDst])
+            remote = self.rank != src and self.chunks > 1
+            tiles = self.srows // 1024 if self.srows % 1024 == 0 else 0
+            nch = min(self.chunks, tiles) if (remote and tiles) else 1
+            if nch > 1:
+                self.stage = torch.empty((self.srows, ws), dtype=torch.int64, device=dev)
+                self.rootB = self.hB.get_buffer(src, (k, ws), torch.int64)
+                self.copy_stream = torch.cuda.Stream(device=dev)
+                self.ev_go = torch.cuda.Event()
+            self.keep = []
+            for c in range(nch):
+                c0, c1 = (tiles * c // nch) * 1024 if nch > 1 else 0, (tiles * (c + 1) // nch) * 1024 if nch > 1 else self.srows
+                if nch > 1:
+                    dSrc = D.wrap(self.stage.data_ptr() + c0 * ws * 8, c1 - c0, n, ws, keepalive=self.stage)
+                    copy = (self.stage[c0:c1], self.rootB[self.s0 + c0: self.s0 + c1], torch.cuda.Event())
+                else:
+                    dSrc = D.wrap(int(self.hB.buffer_ptrs[src]) + self.s0 * ws * 8, self.srows, n, ws, keepalive=self.tB)
+                    copy = None
+                dDst = [D.wrap(int(p) + ((self.s0 + c0) // 64) * 8, n, c1 - c0, kws, keepalive=self.tBt)
+                        for p in self.hBt.buffer_ptrs]
+                self.keep.append(dDst)
+                self.pieces.append((dSrc, (ctypes.c_void_p * self.world)(*[d.h for d in dDst]), copy))
 
-    def step(self, algo=0):
+    def exchange(self):
+        """Distribute the root's B: afterwards every rank's Bt holds all of B transposed."""
         # the symmetric-memory barriers run on torch's current stream: the library must issue the
         # scatter and the product on that same stream or the barriers order nothing
         import ctypes
         self.L.m4ri_b200_set_stream(ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
         self.hBt.barrier(channel=0)  # every rank is done reading its Bt of the previous step
-        if self.srows > 0:
-            self.L.m4ri_b200_dtranspose_scatter(self.dst_arr, self.world, self.dSlab.h)
+        main = torch.cuda.current_stream()
+        if len(self.pieces) > 1:
+            # the staging buffer is free again: the previous step's scatters precede this point
+            self.ev_go.record(main)
+            with torch.cuda.stream(self.copy_stream):
+                self.copy_stream.wait_event(self.ev_go)
+                for (_, _, (dst, srcv, ev)) in self.pieces:
+                    dst.copy_(srcv, non_blocking=True)
+                    ev.record(self.copy_stream)
+        for (dSrc, dst_arr, copy) in self.pieces:
+            if copy is not None:
+                main.wait_event(copy[2])
+            self.L.m4ri_b200_dtranspose_scatter(dst_arr, self.world, dSrc.h)
         self.hBt.barrier(channel=1)  # every slab of Bt has landed everywhere
+
+    def step(self, algo=0):
+        self.exchange()
         if self.rows > 0:
             self.m4.dmul_abt(self.dC, self.dA, self.dBt, clear=True, algo=algo)
