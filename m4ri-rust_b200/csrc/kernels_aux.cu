@@ -288,9 +288,10 @@ void k_transpose_scatter(DMat *const *D, int ndst, const DMat *A, cudaStream_t s
     dsts.p[i] = (uint32_t *)D[i]->d;
   }
   const int sw32 = A->width * 2, dw32 = D[0]->width * 2;
-  // several destinations = peer stores over NVLink: the wide kernel unless told otherwise
+  // destinations of a scatter are peer or multicast mappings (stores over NVLink): the wide
+  // kernel (whole 128-byte rows per store burst) unless told otherwise
   const int var = transpose_variant();
-  if ((var == 2 || (var == 0 && ndst > 1)) && transpose_wide_ok(dsts.p, ndst, D[0]->rowstride * 2)) {
+  if (var != 1 && transpose_wide_ok(dsts.p, ndst, D[0]->rowstride * 2)) {
     launch_transpose_wide(dsts, A, D[0]->rowstride * 2, dw32, s);
     return;
   }

@@ -156,7 +156,7 @@ class FusedBroadcastMul:
     two device-side barriers per step order the peer stores against the products.
     """
 
-    def __init__(self, m4, m, k, n, dist, src=0, root_serves=None, chunks=None):
+    def __init__(self, m4, m, k, n, dist, src=0, root_serves=None, chunks=None, plan=None):
         import ctypes
         import os
         import torch.distributed._symmetric_memory as symm_mem
@@ -175,12 +175,24 @@ class FusedBroadcastMul:
         #                into a local staging buffer while the scatter kernel works on the previous
         #                piece: remote reads (ingress) overlap the peer stores (egress) instead of
         #                alternating inside one kernel
+        #   plan         "peer": G peer stores per output row (above). "mc_slabs": the same slabs, but
+        #                ONE store per row to the NVSwitch multicast address of the symmetric Bt
+        #                buffer — the switch replicates it into every GPU's copy (NVLS), so a
+        #                rank's egress is its slab, not (G-1) x its slab. "mc_root": the root alone
+        #                transposes all of its (local) B and multicasts Bt: no remote reads, root
+        #                egress |B| (the floor for a B that starts on one GPU). "auto": mc_root
+        #                when the handle has a multicast address, else peer.
+        #                (multimem.st and st.global compile to the same STG on sm_100a: a plain
+        #                store to the multicast mapping is the multicast store)
+        if plan is None:
+            plan = os.environ.get("M4RI_B200_XCHG_PLAN", "auto")
         if root_serves is None:
             root_serves = os.environ.get("M4RI_B200_XCHG_ROOT_SERVES", "auto")
             root_serves = (self.world >= 6) if root_serves == "auto" else root_serves == "1"
         if chunks is None:
             chunks = int(os.environ.get("M4RI_B200_XCHG_CHUNKS", "4"))
         self.root_serves, self.chunks = bool(root_serves), max(1, chunks)
+        self.plan = plan  # resolved below, once the buffers have a handle
         self.s0, self.srows = exchange_slab(k, self.world, self.rank, src, root_serves=self.root_serves)
         ws, kws = n // 64, k // 64
         dev = torch.device("cuda", torch.cuda.current_device())
@@ -195,6 +207,13 @@ class FusedBroadcastMul:
         self.dC = D.wrap(self.tC.data_ptr(), self.rows, n, ws, keepalive=self.tC)
         self.dB = D.wrap(self.tB.data_ptr(), k, n, ws, keepalive=self.tB)
         self.dBt = D.wrap(self.tBt.data_ptr(), n, k, kws, keepalive=self.tBt)
+        mc = int(getattr(self.hBt, "multicast_ptr", 0) or 0)
+        if self.plan == "auto":
+            self.plan = "mc_root" if mc else "peer"
+        if self.plan != "peer" and not mc:
+            raise RuntimeError("exchange plan %r needs a multicast mapping of the symmetric buffer" % self.plan)
+        if self.plan == "mc_root":  # one slab: everything, on the root
+            self.s0, self.srows = (0, k) if self.rank == src else (0, 0)
         self.pieces = []  # (source matrix, destination array, staging copy or None)
         if self.srows > 0:
             remote = self.rank != src and self.chunks > 1
@@ -214,10 +233,10 @@ class FusedBroadcastMul:
                 else:
                     dSrc = D.wrap(int(self.hB.buffer_ptrs[src]) + self.s0 * ws * 8, self.srows, n, ws, keepalive=self.tB)
                     copy = None
-                dDst = [D.wrap(int(p) + ((self.s0 + c0) // 64) * 8, n, c1 - c0, kws, keepalive=self.tBt)
-                        for p in self.hBt.buffer_ptrs]
+                ptrs = self.hBt.buffer_ptrs if self.plan == "peer" else [mc]
+                dDst = [D.wrap(int(p) + ((self.s0 + c0) // 64) * 8, n, c1 - c0, kws, keepalive=self.tBt) for p in ptrs]
                 self.keep.append(dDst)
-                self.pieces.append((dSrc, (ctypes.c_void_p * self.world)(*[d.h for d in dDst]), copy))
+                self.pieces.append((dSrc, (ctypes.c_void_p * len(dDst))(*[d.h for d in dDst]), len(dDst), copy))
 
     def exchange(self):
         """Distribute the root's B: afterwards every rank's Bt holds all of B transposed."""
@@ -232,13 +251,13 @@ class FusedBroadcastMul:
             self.ev_go.record(main)
             with torch.cuda.stream(self.copy_stream):
                 self.copy_stream.wait_event(self.ev_go)
-                for (_, _, (dst, srcv, ev)) in self.pieces:
+                for (_, _, _, (dst, srcv, ev)) in self.pieces:
                     dst.copy_(srcv, non_blocking=True)
                     ev.record(self.copy_stream)
-        for (dSrc, dst_arr, copy) in self.pieces:
+        for (dSrc, dst_arr, ndst, copy) in self.pieces:
             if copy is not None:
                 main.wait_event(copy[2])
-            self.L.m4ri_b200_dtranspose_scatter(dst_arr, self.world, dSrc.h)
+            self.L.m4ri_b200_dtranspose_scatter(dst_arr, ndst, dSrc.h)
         self.hBt.barrier(channel=1)  # every slab of Bt has landed everywhere
 
     def step(self, algo=0):

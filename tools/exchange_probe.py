@@ -35,10 +35,21 @@ def timed(fn, reps=5):
 
 
 out = {"n": n, "world": world, "plans": {}}
-plans = [(False, 1), (False, 4), (True, 1), (True, 4), (True, 8)] if world >= 3 else [(False, 1), (False, 2), (False, 4), (False, 8)]
+plans = [("peer", False, 1), ("peer", world >= 6, 4), ("mc_slabs", False, 1), ("mc_slabs", False, 4), ("mc_slabs", world >= 3, 4), ("mc_root", False, 1)]
 want = None
-for (serves, chunks) in plans:
-    fm = sharded.FusedBroadcastMul(m4, n, n, n, dist, src=0, root_serves=serves, chunks=chunks)
+def note(msg):
+    if os.environ.get("PROBE_VERBOSE"):
+        torch.cuda.synchronize()
+        print(f"[rank {rank}] {msg}", file=sys.stderr, flush=True)
+
+
+for (plan, serves, chunks) in plans:
+    note(f"plan {plan} {serves} {chunks}")
+    try:
+        fm = sharded.FusedBroadcastMul(m4, n, n, n, dist, src=0, root_serves=serves, chunks=chunks, plan=plan)
+    except RuntimeError as e:
+        out["plans"]["%s,root_serves=%d,chunks=%d" % (plan, serves, chunks)] = {"unavailable": str(e)}
+        continue
     L.m4ri_b200_dfill_random_at(fm.dA.h, 1, fm.r0 * (n // 64))
     if rank == 0:
         fm.dB.fill_random(2)
@@ -50,17 +61,22 @@ for (serves, chunks) in plans:
         tmp = fm.tB.clone()
         dist.broadcast(tmp, src=0)
         dT = m4.DMat.init(n, n)
-        L.m4ri_b200_dtranspose(dT.h, m4.DMat.wrap(tmp.data_ptr(), n, n, n // 64, keepalive=tmp).h)
+        dTmp = m4.DMat.wrap(tmp.data_ptr(), n, n, n // 64, keepalive=tmp)
+        L.m4ri_b200_dtranspose(dT.h, dTmp.h)
         want = dT.checksum()
-        del tmp, dT
+        del dTmp, tmp, dT
+    note("want ready")
+    fm.exchange()
+    note("first exchange done")
     rec = {"exchange_ms": timed(fm.exchange), "step_ms": timed(lambda: fm.step(0))}
+    note("timed")
     fm.tBt.zero_(); torch.cuda.synchronize(); dist.barrier()
     fm.exchange(); torch.cuda.synchronize(); dist.barrier()
     ok = torch.tensor([1 if fm.dBt.checksum() == want else 0], device="cuda")
     dist.all_reduce(ok, op=dist.ReduceOp.MIN)
     rec["bt_correct_on_every_rank"] = bool(int(ok))
     rec["pieces"] = len(fm.pieces)
-    out["plans"]["root_serves=%d,chunks=%d" % (serves, chunks)] = rec
+    out["plans"]["%s,root_serves=%d,chunks=%d" % (plan, serves, chunks)] = rec
     del fm
     torch.cuda.synchronize(); dist.barrier()
 if rank == 0:
