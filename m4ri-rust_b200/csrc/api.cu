@@ -130,7 +130,7 @@ cudaStream_t current_stream() {
 }
 
 // ---- path (b) variant ----
-void k_mul_abt_mma(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream_t s) {
+static int mma_variant() {
   int v = g_mma_variant.load();
   if (v == 0) {
     const char *e = getenv("M4RI_B200_MMA");
@@ -144,6 +144,10 @@ void k_mul_abt_mma(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream
         : !strcmp(e, "fp4s256cg1") ? M4RI_B200_MMA_FP4_S256_SINGLE
         : !strcmp(e, "fp4") ? M4RI_B200_MMA_FP4_PAIR : M4RI_B200_MMA_FP4_S256_PAIR;
   }
+  return v;
+}
+void k_mul_abt_mma(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream_t s) {
+  const int v = mma_variant();
   if (v == M4RI_B200_MMA_V1) k_mul_abt_mma1(C, A, Bt, clear, s);
   else if (v == M4RI_B200_MMA_FP4_S256_SINGLE || v == M4RI_B200_MMA_FP4_S256_PAIR)
     k_mul_abt_mma6(C, A, Bt, clear, v == M4RI_B200_MMA_FP4_S256_SINGLE ? 1 : 2, s);
@@ -309,6 +313,55 @@ static void leaf_mul(DMat *C, const DMat *A, const DMat *B, int clear, int algo,
   else k_mul_abt_simple(C, A, B, clear, s);
 }
 
+static DMat *dmat_new_overwritten(rci_t nrows, rci_t ncols, cudaStream_t s);
+// ---- the last Strassen level, fused (tensor path, default kernel) --------------------------
+// Classic Strassen over GF(2): every operand of the seven products is a quadrant or the sum of
+// two, and every product goes into one or two quadrants of C:
+//   M1 = (A11+A22)(B11+B22) -> C11, C22     M5 = (A11+A12) B22       -> C11, C12
+//   M2 = (A21+A22) B11      -> C21, C22     M6 = (A21+A11)(B11+B12)  -> C22
+//   M3 = A11 (B12+B22)      -> C12, C22     M7 = (A12+A22)(B21+B22)  -> C11
+//   M4 = A22 (B21+B11)      -> C11, C21
+// The ten operand sums are two launches (k_quad_sums: 4 quadrants read once, 5 sums written) and
+// the product kernel's epilogue writes or accumulates into both destinations itself, so the level
+// costs 2 add passes instead of the 15 of the Winograd schedule below (0.44 -> 0.15 ms at
+// n = 32768) and C (^)= needs no temporary. Bt is n x k: quadrant (i, j) of B is rows j, columns
+// i of Bt.
+static bool fused_level_ok(const DMat *C, const DMat *A, int algo, int form) {
+  const int v = mma_variant();
+  return algo == M4RI_B200_ALGO_MMA && form == 1 && !getenv("M4RI_B200_NO_FUSED_STRASSEN") &&
+         (v == M4RI_B200_MMA_FP4_S256_PAIR || v == M4RI_B200_MMA_FP4_S256_SINGLE) && C->nrows % 512 == 0 &&
+         C->ncols % 512 == 0 && A->ncols % 512 == 0 && !(C->rowstride & 1) && !((uintptr_t)C->d & 15);
+}
+static void strassen_fused_level(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream_t s) {
+  const int m2 = C->nrows / 2, n2 = C->ncols / 2, k2 = A->ncols / 2;
+  const int cg = mma_variant() == M4RI_B200_MMA_FP4_S256_SINGLE ? 1 : 2;
+  DMat Aq[4] = {dwin(A, 0, 0, m2, k2), dwin(A, 0, k2, m2, k2), dwin(A, m2, 0, m2, k2), dwin(A, m2, k2, m2, k2)};
+  // B11, B12, B21, B22 as windows of Bt
+  DMat Bq[4] = {dwin(Bt, 0, 0, n2, k2), dwin(Bt, n2, 0, n2, k2), dwin(Bt, 0, k2, n2, k2), dwin(Bt, n2, k2, n2, k2)};
+  DMat Cq[4] = {dwin(C, 0, 0, m2, n2), dwin(C, 0, n2, m2, n2), dwin(C, m2, 0, m2, n2), dwin(C, m2, n2, m2, n2)};
+  DMat *SA[5], *SB[5];
+  for (int i = 0; i < 5; i++) SA[i] = dmat_new_overwritten(m2, k2, s), SB[i] = dmat_new_overwritten(n2, k2, s);
+  // A11+A22, A21+A22, A11+A12, A21+A11, A12+A22 / B11+B22, B12+B22, B21+B11, B11+B12, B21+B22
+  static const int pa[5][2] = {{0, 3}, {2, 3}, {0, 1}, {2, 0}, {1, 3}};
+  static const int pb[5][2] = {{0, 3}, {1, 3}, {2, 0}, {0, 1}, {2, 3}};
+  k_quad_sums(SA, Aq, pa, s);
+  k_quad_sums(SB, Bq, pb, s);
+  bool fresh[4] = {clear != 0, clear != 0, clear != 0, clear != 0};  // the next write overwrites the quadrant
+  auto prod = [&](const DMat *X, const DMat *Y, int t1, int t2) {
+    k_mul_abt_mma6(&Cq[t1], X, Y, fresh[t1], cg, s, t2 >= 0 ? &Cq[t2] : nullptr, t2 >= 0 ? fresh[t2] : 0);
+    fresh[t1] = false;
+    if (t2 >= 0) fresh[t2] = false;
+  };
+  prod(SA[0], SB[0], 0, 3);   // M1
+  prod(SA[1], &Bq[0], 2, 3);  // M2
+  prod(&Aq[0], SB[1], 1, 3);  // M3
+  prod(&Aq[3], SB[2], 0, 2);  // M4
+  prod(SA[2], &Bq[3], 0, 1);  // M5
+  prod(SA[3], SB[3], 3, -1);  // M6
+  prod(SA[4], SB[4], 0, -1);  // M7
+  for (int i = 0; i < 5; i++) dmat_delete(SA[i], s), dmat_delete(SB[i], s);
+}
+
 // C = A (*) B, overwriting C. Quadrant (i,j) of the logical k x n matrix B.
 static DMat *dmat_new_overwritten(rci_t nrows, rci_t ncols, cudaStream_t s);
 static void strassen_mul(DMat *C, const DMat *A, const DMat *B, int algo, int form, int levels,
@@ -317,6 +370,10 @@ static void strassen_mul(DMat *C, const DMat *A, const DMat *B, int algo, int fo
   // halves must stay 128-bit aligned column windows and whole 256-row tiles
   if (levels <= 0 || (m % 512) || (n % 512) || (k % 512)) {
     leaf_mul(C, A, B, 1, algo, form, s);
+    return;
+  }
+  if (levels == 1 && fused_level_ok(C, A, algo, form)) {
+    strassen_fused_level(C, A, B, 1, s);
     return;
   }
   const int m2 = m / 2, n2 = n / 2, k2 = k / 2;
@@ -398,6 +455,8 @@ static void product_with_strassen(DMat *C, const DMat *A, const DMat *B, int cle
   const int L = strassen_levels(C->nrows, A->ncols, C->ncols, algo, cutoff);
   if (L <= 0 || (C->nrows % 512) || (C->ncols % 512) || (A->ncols % 512)) {
     leaf_mul(C, A, B, clear, algo, form, s);
+  } else if (L == 1 && fused_level_ok(C, A, algo, form)) {
+    strassen_fused_level(C, A, B, clear, s);  // accumulates in the epilogue: no temporary
   } else if (clear) {
     strassen_mul(C, A, B, algo, form, L, s);
   } else {

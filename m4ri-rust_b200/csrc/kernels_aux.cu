@@ -101,6 +101,57 @@ void k_add(DMat *C, const DMat *A, const DMat *B, cudaStream_t s) {
   M4B_LAUNCHED();
 }
 
+// The operand sums of one fused Strassen level (api.cu::strassen_fused_level): the four quadrants
+// are read once, five pairwise sums are written. 16-byte vectors; 9 instead of 15 transfers.
+struct QuadSums {
+  const ulonglong2 *q[4];
+  ulonglong2 *o[5];
+  int pa[5], pb[5];
+};
+__global__ void quad_sums_kernel(QuadSums a, int nrows, int wv, int qs, int os) {
+  const long long total = (long long)nrows * wv;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int r = (int)(i / wv), w = (int)(i % wv);
+    ulonglong2 v[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) v[j] = a.q[j][(size_t)r * qs + w];
+#pragma unroll
+    for (int j = 0; j < 5; j++) {
+      ulonglong2 x = v[0], y = v[0];
+#pragma unroll
+      for (int t = 1; t < 4; t++) {
+        if (a.pa[j] == t) x = v[t];
+        if (a.pb[j] == t) y = v[t];
+      }
+      a.o[j][(size_t)r * os + w] = make_ulonglong2(x.x ^ y.x, x.y ^ y.y);
+    }
+  }
+}
+void k_quad_sums(DMat *const out[5], const DMat q[4], const int pairs[5][2], cudaStream_t s) {
+  QuadSums a;
+  const int nrows = q[0].nrows, width = q[0].width;
+  if (nrows == 0 || width == 0) return;
+  for (int j = 0; j < 4; j++) {
+    if (q[j].nrows != nrows || q[j].width != width || q[j].rowstride != q[0].rowstride || (q[j].rowstride & 1) ||
+        ((uintptr_t)q[j].d & 15) || (width & 1))
+      die("m4ri_b200: quad_sums needs four equal, 16-byte aligned quadrants\n");
+    a.q[j] = (const ulonglong2 *)q[j].d;
+  }
+  for (int j = 0; j < 5; j++) {
+    if (out[j]->nrows != nrows || out[j]->width != width || out[j]->rowstride != out[0]->rowstride ||
+        (out[j]->rowstride & 1) || ((uintptr_t)out[j]->d & 15))
+      die("m4ri_b200: quad_sums: bad output\n");
+    a.o[j] = (ulonglong2 *)out[j]->d;
+    a.pa[j] = pairs[j][0];
+    a.pb[j] = pairs[j][1];
+  }
+  const long long total = (long long)nrows * (width / 2);
+  unsigned grid = (unsigned)min((long long)cdiv(total, 256), (long long)sm_count() * 16);
+  quad_sums_kernel<<<grid, 256, 0, s>>>(a, nrows, width / 2, q[0].rowstride / 2, out[0]->rowstride / 2);
+  M4B_LAUNCHED();
+}
+
 // ---------------------------------------------------------------------------
 // transpose: 256-row x 1024-bit input tiles. 32x32 bit blocks are turned in
 // registers (five masked shuffle exchanges), collected in shared memory and

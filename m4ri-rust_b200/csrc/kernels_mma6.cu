@@ -249,7 +249,7 @@ template <int CG, bool WIDE, bool FULL>
 __global__ void __launch_bounds__(NTHREADS, 1)
 mma6_kernel(uint32_t *__restrict__ C, const uint8_t *__restrict__ Ab, const uint8_t *__restrict__ Bb,
             int m, int n, int k, long long a_rsb, long long b_rsb, int cs32, int cw32, int tiles_m,
-            int tiles_n, int clear, int dbg) {
+            int tiles_n, int clear, int dbg, uint32_t *__restrict__ C2, int clear2) {
   constexpr int NCOL = 128 * CG;  // accumulator columns = tile columns
   extern __shared__ uint8_t smem_raw[];
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B: 1024-B alignment
@@ -527,15 +527,20 @@ mma6_kernel(uint32_t *__restrict__ C, const uint8_t *__restrict__ Ab, const uint
         if (lane == 0) mbar_arrive_cluster(dempty_leader);
       }
       const int cw0 = tn * (NCOL / 32) + part * (HCOL / 32);
-      if (row < m) {
-        uint32_t *dst = C + (size_t)row * cs32 + cw0;
+      // one or two destinations with the same shape and stride (the fused Strassen level sends a
+      // product into two quadrants of C), each overwritten or accumulated into
+      for (int tgt = 0; tgt < 2; tgt++) {
+        uint32_t *Ct = tgt ? C2 : C;
+        const int clr = tgt ? clear2 : clear;
+        if (Ct == nullptr || row >= m) continue;
+        uint32_t *dst = Ct + (size_t)row * cs32 + cw0;
         if constexpr (HCOL >= 128) {
 #pragma unroll
           for (int q4 = 0; q4 < HCOL / 128; q4++) {
             const int cw = cw0 + 4 * q4;
             if (cw + 4 <= cw32) {
               uint4 o = make_uint4(out[4 * q4], out[4 * q4 + 1], out[4 * q4 + 2], out[4 * q4 + 3]);
-              if (!clear) {
+              if (!clr) {
                 const uint4 old = *reinterpret_cast<const uint4 *>(dst + 4 * q4);
                 o.x ^= old.x; o.y ^= old.y; o.z ^= old.z; o.w ^= old.w;
               }
@@ -544,13 +549,13 @@ mma6_kernel(uint32_t *__restrict__ C, const uint8_t *__restrict__ Ab, const uint
 #pragma unroll
               for (int jj = 0; jj < 4; jj++)
                 if (cw + jj < cw32)
-                  dst[4 * q4 + jj] = clear ? out[4 * q4 + jj] : (dst[4 * q4 + jj] ^ out[4 * q4 + jj]);
+                  dst[4 * q4 + jj] = clr ? out[4 * q4 + jj] : (dst[4 * q4 + jj] ^ out[4 * q4 + jj]);
             }
           }
         } else {  // CG == 1 with eight epilogue warps: 64 columns = two words per warp
 #pragma unroll
           for (int jj = 0; jj < HCOL / 32; jj++)
-            if (cw0 + jj < cw32) dst[jj] = clear ? out[jj] : (dst[jj] ^ out[jj]);
+            if (cw0 + jj < cw32) dst[jj] = clr ? out[jj] : (dst[jj] ^ out[jj]);
         }
       }
     }
@@ -566,7 +571,7 @@ mma6_kernel(uint32_t *__restrict__ C, const uint8_t *__restrict__ Ab, const uint
 
 // ---- host side -------------------------------------------------------------------
 template <int CG, bool WIDE, bool FULL>
-static void launch_mma6(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream_t s) {
+static void launch_mma6(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream_t s, DMat *C2, int clear2) {
   static std::atomic<unsigned long long> attr_seen{0};
   if (first_use_on_this_device(attr_seen)) {
     M4B_CUDA(cudaFuncSetAttribute(mma6_kernel<CG, WIDE, FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_V6));
@@ -600,7 +605,8 @@ static void launch_mma6(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaS
                                 (const uint8_t *)(A->d + k0 / 64), (const uint8_t *)(Bt->d + k0 / 64),
                                 C->nrows, C->ncols, kc, (long long)A->rowstride * 8,
                                 (long long)Bt->rowstride * 8, C->rowstride * 2, C->width * 2, tiles_m,
-                                tiles_n, (clear && k0 == 0) ? 1 : 0, dbg));
+                                tiles_n, (clear && k0 == 0) ? 1 : 0, dbg, C2 ? (uint32_t *)C2->d : (uint32_t *)nullptr,
+                                (clear2 && k0 == 0) ? 1 : 0));
     M4B_LAUNCHED();
     timing_end(s);
   }
@@ -610,11 +616,15 @@ static bool my_tiles_ok(int m, int n, int k, int tile) {
   return m % tile == 0 && n % tile == 0 && k % KS_BITS == 0 && (k <= K_CHUNK_MAX || K_CHUNK_MAX % KS_BITS == 0);
 }
 
-// C (^)= A*Bt^T on the FP4 pipe; cg = CTAs per MMA
-void k_mul_abt_mma6(DMat *C, const DMat *A, const DMat *Bt, int clear, int cg, cudaStream_t s) {
+// C (^)= A*Bt^T on the FP4 pipe; cg = CTAs per MMA. With C2: the same product also goes to
+// (clear2) or into (!clear2) C2, a matrix of C's shape and row stride.
+void k_mul_abt_mma6(DMat *C, const DMat *A, const DMat *Bt, int clear, int cg, cudaStream_t s, DMat *C2, int clear2) {
   if (C->nrows == 0 || C->ncols == 0) return;
+  if (C2 && (C2->nrows != C->nrows || C2->ncols != C->ncols || C2->rowstride != C->rowstride || ((uintptr_t)C2->d & 15)))
+    die("m4ri_b200: the second destination of a product must have the first one's shape, stride and alignment\n");
   if (A->ncols == 0) {
     if (clear) k_zero(C, s);
+    if (C2 && clear2) k_zero(C2, s);
     return;
   }
   if (!has_tcgen05()) die("m4ri_b200: the tcgen05 MMA path needs an sm_100 device\n");
@@ -625,13 +635,13 @@ void k_mul_abt_mma6(DMat *C, const DMat *A, const DMat *Bt, int clear, int cg, c
   // whole tiles and whole stages in every k-chunk of the launch loop: the unconditional-load kernel
   const bool full = wide && my_tiles_ok(C->nrows, C->ncols, A->ncols, tile);
   if (cg == 2) {
-    if (full) launch_mma6<2, true, true>(C, A, Bt, clear, s);
-    else if (wide) launch_mma6<2, true, false>(C, A, Bt, clear, s);
-    else launch_mma6<2, false, false>(C, A, Bt, clear, s);
+    if (full) launch_mma6<2, true, true>(C, A, Bt, clear, s, C2, clear2);
+    else if (wide) launch_mma6<2, true, false>(C, A, Bt, clear, s, C2, clear2);
+    else launch_mma6<2, false, false>(C, A, Bt, clear, s, C2, clear2);
   } else {
-    if (full) launch_mma6<1, true, true>(C, A, Bt, clear, s);
-    else if (wide) launch_mma6<1, true, false>(C, A, Bt, clear, s);
-    else launch_mma6<1, false, false>(C, A, Bt, clear, s);
+    if (full) launch_mma6<1, true, true>(C, A, Bt, clear, s, C2, clear2);
+    else if (wide) launch_mma6<1, true, false>(C, A, Bt, clear, s, C2, clear2);
+    else launch_mma6<1, false, false>(C, A, Bt, clear, s, C2, clear2);
   }
 }
 

@@ -451,6 +451,49 @@ def test_every_tensor_kernel_variant(gpu, m4, orc, variant):
         L.m4ri_b200_set_mma_variant(0)
 
 
+@pytest.mark.parametrize("variant", ["fp4s256", "fp4s256cg1"])
+def test_fused_strassen_level(gpu, m4, orc, variant, monkeypatch):
+    """The last Strassen level of the default kernel is fused (classic Strassen: operand sums in
+    two launches, every product written or accumulated into one or two quadrants of C by the
+    kernel's epilogue): bit-exact against the oracle for C = and C ^=, on rectangular shapes, in
+    both operand forms, with two levels (Winograd outside, fused inside), and equal to the
+    unfused schedule."""
+    L = m4.lib()
+    L.m4ri_b200_set_mma_variant(m4.MMA_VARIANTS[variant])
+    try:
+        for levels, (m, k, n) in [(1, (1024, 1024, 1024)), (1, (512, 1536, 2048)), (1, (2048, 512, 1024)),
+                                  (2, (2048, 1024, 3072)), (1, (1024, 66560, 512))]:
+            L.m4ri_b200_set_strassen_levels(levels)
+            A, B, C0 = orc.random(m, k, 31 + m), orc.random(k, n, 32 + n), orc.random(m, n, 33)
+            want = orc.mul_m4rm(A, B, k, n, threads=0)[:, : orc.width(n)]
+            a, b = host(m4, A, k), host(m4, B, n)
+            dA, dB, dC = m4.DMat.from_host(a), m4.DMat.from_host(b), m4.DMat.init(m, n)
+            l0 = m4.launch_count()
+            m4.dmul(dC, dA, dB, clear=True, algo=m4.ALGO_MMA)
+            fused_launches = m4.launch_count() - l0
+            assert (dC.to_words()[:, : orc.width(n)] == want).all(), (variant, levels, m, k, n)
+            # accumulate form on the pre-transposed operand: C0 ^= A * Bt^T
+            dBt = m4.DMat.init(n, k)
+            L.m4ri_b200_dtranspose(dBt.h, dB.h)
+            c0 = host(m4, C0, n)
+            dC0 = m4.DMat.from_host(c0)
+            m4.dmul_abt(dC0, dA, dBt, clear=False, algo=m4.ALGO_MMA)
+            assert (dC0.to_words()[:, : orc.width(n)] == (C0[:, : orc.width(n)] ^ want)).all(), (variant, levels, m, k, n)
+            # the unfused (Winograd) schedule gives the same words with more launches
+            monkeypatch.setenv("M4RI_B200_NO_FUSED_STRASSEN", "1")
+            l0 = m4.launch_count()
+            m4.dmul(dC, dA, dB, clear=True, algo=m4.ALGO_MMA)
+            unfused_launches = m4.launch_count() - l0
+            monkeypatch.delenv("M4RI_B200_NO_FUSED_STRASSEN")
+            assert (dC.to_words()[:, : orc.width(n)] == want).all()
+            assert fused_launches < unfused_launches, (fused_launches, unfused_launches)
+            for p in (a, b, c0):
+                L.mzd_free(p)
+    finally:
+        L.m4ri_b200_set_strassen_levels(-1)
+        L.m4ri_b200_set_mma_variant(0)
+
+
 def test_fp4_accumulators_are_exact(gpu, m4, orc):
     """The FP4 path's fp32 accumulators equal popcount(A_i & Bt_j)/4 exactly, also in the worst
     case the wrapper allows (all ones, k = 65536): no rounding anywhere in the tensor core."""
