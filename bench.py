@@ -342,7 +342,7 @@ def main():
     n = args.n or (32768 if world == 1 else 65536)
     workload = f"square mzd_mul n={n} random" + (
         "" if world == 1 else f", C/A row-blocks sharded over {world} ranks, B of rank 0 distributed every step: "
-        + ("exchange fused into the transpose (each rank transposes one k-slab of the root's B, read over NVLink, and stores it into every rank's Bt with peer stores)"
+        + ("exchange fused into the transpose (plan in config.exchange_plan)"
            if args.exchange == "fused" else
            f"NCCL broadcast in k-chunks ({args.chunks}) overlapped with the product; the product leaves {args.reserve} SMs to NCCL while a chunk is in flight"))
     config = {"workload": workload, "m": n, "k": n, "n": n, "algo": args.algo,
@@ -396,6 +396,11 @@ def main():
         # NVLink and stores it into every rank's Bt (peer stores); one product launch per step
         fm = sharded.FusedBroadcastMul(m4, n, n, n, dist, src=0)
         tA, tB, tC, dA, dB, dC = fm.tA, fm.tB, fm.tC, fm.dA, fm.dB, fm.dC
+        config["exchange_plan"] = {
+            "mc_root": "mc_root: the root transposes its B in one kernel whose stores go to the NVSwitch multicast mapping of the symmetric Bt buffer: one store per 16 bytes reaches every GPU (root egress |B|, no remote reads)",
+            "mc_slabs": "mc_slabs: every rank transposes one k-slab of the root's B (read over NVLink) and stores it to the multicast mapping of Bt",
+            "peer": "peer: every rank transposes one k-slab of the root's B (read over NVLink; root_serves=%s, pulled in %d pieces by the copy engine) and stores it into every rank's Bt with peer stores" % (fm.root_serves, fm.chunks),
+        }[fm.plan]
     else:
         tA = torch.empty((rows, ws), dtype=torch.int64, device="cuda")
         tB = torch.empty((n, ws), dtype=torch.int64, device="cuda")
