@@ -581,19 +581,22 @@ def main():
                 "peak_source": "measured shared-memory load bandwidth x 512 bit-ops per 32-bit table word (t=8)"}
     # DRAM traffic of one launch of that kernel at the leaf shape, from the committed ncu capture
     try:
-        per_launch = kern_ops / kern_count / 2.0  # m*k*n of one launch
-        shape = None
+        per_launch = kern_ops / kern_count / 2.0  # sum of m*k*n over the products of one launch
+        shape, group = None, 1
         for lv in range(4):  # the rank's row-block (n/world x n x n) after lv Strassen levels
             mm, kk = n // world >> lv, n >> lv
-            if abs(mm * kk * kk - per_launch) < 1e-6 * per_launch:
-                shape = (mm, kk, kk)
+            for g in (1, 7):  # the fused last level runs its seven leaf products as one launch
+                if abs(g * mm * kk * kk - per_launch) < 1e-6 * per_launch:
+                    shape, group = (mm, kk, kk), g
         tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        ent = tj.get("%s@%dx%dx%d" % ((kern_name,) + shape)) if shape else None
+        key = "%s@%s%dx%dx%d" % ((kern_name, "7x" if group == 7 else "") + shape) if shape else None
+        ent = tj.get(key) if key else None
+        if shape:
+            roof["launch_shape"] = ("7 products of " if group == 7 else "") + "%dx%dx%d" % shape
+            roof["algorithmic_bytes"] = group * (shape[0] * shape[1] + shape[1] * shape[2] + shape[0] * shape[2]) // 8
         if ent:
             roof["traffic"] = ent["bytes"]
             roof["traffic_source"] = ent["source"]
-            roof["traffic_launch_shape"] = "%dx%dx%d" % shape
-            roof["algorithmic_bytes"] = (shape[0] * shape[1] + shape[1] * shape[2] + shape[0] * shape[2]) // 8
     except Exception:
         pass
     roof["kernel"] = kern_name

@@ -346,19 +346,31 @@ static void strassen_fused_level(DMat *C, const DMat *A, const DMat *Bt, int cle
   static const int pb[5][2] = {{0, 3}, {1, 3}, {2, 0}, {0, 1}, {2, 3}};
   k_quad_sums(SA, Aq, pa, s);
   k_quad_sums(SB, Bq, pb, s);
-  bool fresh[4] = {clear != 0, clear != 0, clear != 0, clear != 0};  // the next write overwrites the quadrant
-  auto prod = [&](const DMat *X, const DMat *Y, int t1, int t2) {
-    k_mul_abt_mma6(&Cq[t1], X, Y, fresh[t1], cg, s, t2 >= 0 ? &Cq[t2] : nullptr, t2 >= 0 ? fresh[t2] : 0);
-    fresh[t1] = false;
-    if (t2 >= 0) fresh[t2] = false;
-  };
-  prod(SA[0], SB[0], 0, 3);   // M1
-  prod(SA[1], &Bq[0], 2, 3);  // M2
-  prod(&Aq[0], SB[1], 1, 3);  // M3
-  prod(&Aq[3], SB[2], 0, 2);  // M4
-  prod(SA[2], &Bq[3], 0, 1);  // M5
-  prod(SA[3], SB[3], 3, -1);  // M6
-  prod(SA[4], SB[4], 0, -1);  // M7
+  if (!getenv("M4RI_B200_NO_GROUPED_STRASSEN")) {
+    // all seven products as ONE persistent launch (no launch gaps, one partial last wave instead of
+    // seven): destinations are shared between concurrent products, so C is zeroed first when it is
+    // to be overwritten and every product accumulates with atomic XORs
+    if (clear) k_zero(C, s);
+    DMat *C1[7] = {&Cq[0], &Cq[2], &Cq[1], &Cq[0], &Cq[0], &Cq[3], &Cq[0]};
+    DMat *C2[7] = {&Cq[3], &Cq[3], &Cq[3], &Cq[2], &Cq[1], nullptr, nullptr};
+    const DMat *X[7] = {SA[0], SA[1], &Aq[0], &Aq[3], SA[2], SA[3], SA[4]};
+    const DMat *Y[7] = {SB[0], &Bq[0], SB[1], SB[2], &Bq[3], SB[3], SB[4]};
+    k_mul_abt_mma6_group(7, C1, C2, X, Y, cg, s);
+  } else {
+    bool fresh[4] = {clear != 0, clear != 0, clear != 0, clear != 0};  // the next write overwrites the quadrant
+    auto prod = [&](const DMat *X, const DMat *Y, int t1, int t2) {
+      k_mul_abt_mma6(&Cq[t1], X, Y, fresh[t1], cg, s, t2 >= 0 ? &Cq[t2] : nullptr, t2 >= 0 ? fresh[t2] : 0);
+      fresh[t1] = false;
+      if (t2 >= 0) fresh[t2] = false;
+    };
+    prod(SA[0], SB[0], 0, 3);   // M1
+    prod(SA[1], &Bq[0], 2, 3);  // M2
+    prod(&Aq[0], SB[1], 1, 3);  // M3
+    prod(&Aq[3], SB[2], 0, 2);  // M4
+    prod(SA[2], &Bq[3], 0, 1);  // M5
+    prod(SA[3], SB[3], 3, -1);  // M6
+    prod(SA[4], SB[4], 0, -1);  // M7
+  }
   for (int i = 0; i < 5; i++) dmat_delete(SA[i], s), dmat_delete(SB[i], s);
 }
 

@@ -129,6 +129,8 @@ void k_mul_abt_mma4(DMat *C, const DMat *A, const DMat *Bt, int clear, int cg, f
 // ---- kernels_mma5.cu: the same contraction, packed bits by direct global loads
 void k_mul_abt_mma5(DMat *C, const DMat *A, const DMat *Bt, int clear, int cg, cudaStream_t s);
 // ---- kernels_mma6.cu: the same contraction, 256-bit stages x 6, 16 expander + 8 epilogue warps (default)
+void k_mul_abt_mma6_group(int count, DMat *const *C1, DMat *const *C2, const DMat *const *A, const DMat *const *Bt,
+                          int cg, cudaStream_t s);
 void k_quad_sums(DMat *const out[5], const DMat q[4], const int pairs[5][2], cudaStream_t s);
 void k_mul_abt_mma6(DMat *C, const DMat *A, const DMat *Bt, int clear, int cg, cudaStream_t s, DMat *C2 = nullptr,
                     int clear2 = 0);

@@ -245,11 +245,32 @@ __device__ __forceinline__ uint32_t pack_parity(const uint32_t (&v)[32]) {
 // counted scoreboard waits. (With conditional loads of unknown count the first use of a buffer
 // waited for ALL outstanding loads — the prefetch was lost and the expansion cost 0.32 ms
 // instead of 0.09 ms per 16384^3 leaf, profiles/r2c_mma6_explore*.log.)
+// One launch = `count` products of ONE shape (m x k) * (n x k)^T, tiles numbered product-major:
+// the seven products of a fused Strassen level run as one persistent grid (no launch gaps, one
+// partial last wave instead of seven). Each product has one or two destinations of the same shape
+// and stride, overwritten (clear) or accumulated into. Products of one launch may share
+// destinations: then `atomic` is set, every destination is pre-zeroed by the caller and all of
+// them accumulate with red.global.xor (XOR commutes: the result does not depend on the order).
+constexpr int GROUP_MAX = 7;
+struct Mma6Group {
+  int count, atomic;
+  const uint8_t *A[GROUP_MAX], *B[GROUP_MAX];
+  long long a_rsb[GROUP_MAX], b_rsb[GROUP_MAX];
+  uint32_t *C1[GROUP_MAX], *C2[GROUP_MAX];
+  int clear1[GROUP_MAX], clear2[GROUP_MAX];
+};
+__device__ __forceinline__ void red_xor64(uint32_t *p, uint32_t lo, uint32_t hi) {
+  asm volatile("red.global.xor.b64 [%0], %1;" ::"l"(p), "l"((unsigned long long)lo | ((unsigned long long)hi << 32))
+               : "memory");
+}
+__device__ __forceinline__ void red_xor32(uint32_t *p, uint32_t v) {
+  asm volatile("red.global.xor.b32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
 template <int CG, bool WIDE, bool FULL>
 __global__ void __launch_bounds__(NTHREADS, 1)
-mma6_kernel(uint32_t *__restrict__ C, const uint8_t *__restrict__ Ab, const uint8_t *__restrict__ Bb,
-            int m, int n, int k, long long a_rsb, long long b_rsb, int cs32, int cw32, int tiles_m,
-            int tiles_n, int clear, int dbg, uint32_t *__restrict__ C2, int clear2) {
+mma6_kernel(const __grid_constant__ Mma6Group grp, int m, int n, int k, int cs32, int cw32, int tiles_m,
+            int tiles_n, int dbg) {
   constexpr int NCOL = 128 * CG;  // accumulator columns = tile columns
   extern __shared__ uint8_t smem_raw[];
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B: 1024-B alignment
@@ -266,7 +287,7 @@ mma6_kernel(uint32_t *__restrict__ C, const uint8_t *__restrict__ Ab, const uint
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = CG == 1 ? 0u : cluster_ctarank();
   const int cluster_id = blockIdx.x / CG, nclusters = gridDim.x / CG;
-  const int ntiles = tiles_m * tiles_n;
+  const int tiles_per = tiles_m * tiles_n, ntiles = tiles_per * grp.count;
   const int nks = (k + KS_BITS - 1) / KS_BITS;  // stages per tile
   const int my_tiles = cluster_id < ntiles ? (ntiles - cluster_id + nclusters - 1) / nclusters : 0;
 
@@ -297,8 +318,6 @@ mma6_kernel(uint32_t *__restrict__ C, const uint8_t *__restrict__ Ab, const uint
     const uint32_t lane_base = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
     const uint32_t a_lane = lane_base + TMEM_A_COL;
     const uint32_t full_leader = map_to_rank(full_bar, 0);
-    const uint8_t *const base = isA ? Ab : Bb;
-    const long long rsb = isA ? a_rsb : b_rsb;
     const int nrows = isA ? m : n;
     const int wbytes = ((k + 63) >> 6) << 3;  // valid bytes of a row (whole words; excess bits are zero)
     if (isA && g == 0) {
@@ -320,7 +339,7 @@ mma6_kernel(uint32_t *__restrict__ C, const uint8_t *__restrict__ Ab, const uint
     const int own = total > first ? (total - first + STEP - 1) / STEP : 0;
     // ---- load cursor ----
     int l_ti = 0, l_ks = first, l_w = 0, l_cur_ti = -1;
-    const uint8_t *l_p = base;
+    const uint8_t *l_p = isA ? grp.A[0] : grp.B[0];
     auto load_next = [&](uint32_t (&x)[8 * UPT]) {
       while (l_ks >= nks) { l_ks -= nks; l_ti++; }
       if constexpr (FULL) {
@@ -328,8 +347,10 @@ mma6_kernel(uint32_t *__restrict__ C, const uint8_t *__restrict__ Ab, const uint
         const int ti = l_ti < my_tiles ? l_ti : my_tiles - 1;
         if (ti != l_cur_ti) {
           int tm, tn;
-          tile_coords(cluster_id + ti * nclusters, tiles_m, tiles_n, tm, tn);
-          l_p = base + (size_t)(((isA ? tm : tn) * CG + (int)rank) * 128 + r) * rsb;
+          const int t = cluster_id + ti * nclusters, pr = t / tiles_per;
+          tile_coords(t - pr * tiles_per, tiles_m, tiles_n, tm, tn);
+          l_p = (isA ? grp.A[pr] : grp.B[pr]) +
+                (size_t)(((isA ? tm : tn) * CG + (int)rank) * 128 + r) * (isA ? grp.a_rsb[pr] : grp.b_rsb[pr]);
           l_cur_ti = ti;
         }
         const uint8_t *p = l_p + (l_ti < my_tiles ? l_ks : 0) * KS_BYTES + u0 * 32;
@@ -339,10 +360,11 @@ mma6_kernel(uint32_t *__restrict__ C, const uint8_t *__restrict__ Ab, const uint
         if (l_ti >= my_tiles) return;  // past the end: the buffer is never expanded
         if (l_ti != l_cur_ti) {
           int tm, tn;
-          tile_coords(cluster_id + l_ti * nclusters, tiles_m, tiles_n, tm, tn);
+          const int t = cluster_id + l_ti * nclusters, pr = t / tiles_per;
+          tile_coords(t - pr * tiles_per, tiles_m, tiles_n, tm, tn);
           const int row = ((isA ? tm : tn) * CG + (int)rank) * 128 + r;
           const bool valid = row < nrows;
-          l_p = base + (size_t)(valid ? row : 0) * rsb;
+          l_p = (isA ? grp.A[pr] : grp.B[pr]) + (size_t)(valid ? row : 0) * (isA ? grp.a_rsb[pr] : grp.b_rsb[pr]);
           l_w = valid ? wbytes : 0;
           l_cur_ti = l_ti;
         }
@@ -469,7 +491,8 @@ mma6_kernel(uint32_t *__restrict__ C, const uint8_t *__restrict__ Ab, const uint
     const uint32_t dempty_leader = map_to_rank(dempty_bar, 0);
     for (int ti = 0; ti < my_tiles; ti++) {
       int tm, tn;
-      tile_coords(cluster_id + ti * nclusters, tiles_m, tiles_n, tm, tn);
+      const int t = cluster_id + ti * nclusters, pr = t / tiles_per;
+      tile_coords(t - pr * tiles_per, tiles_m, tiles_n, tm, tn);
       const int row = (tm * CG + (int)rank) * 128 + qd * 32 + lane;
 #if defined(MMA6_SPIN_ACCUM)
       mbar_wait(accum_bar, ti & 1);
@@ -530,10 +553,18 @@ mma6_kernel(uint32_t *__restrict__ C, const uint8_t *__restrict__ Ab, const uint
       // one or two destinations with the same shape and stride (the fused Strassen level sends a
       // product into two quadrants of C), each overwritten or accumulated into
       for (int tgt = 0; tgt < 2; tgt++) {
-        uint32_t *Ct = tgt ? C2 : C;
-        const int clr = tgt ? clear2 : clear;
+        uint32_t *Ct = tgt ? grp.C2[pr] : grp.C1[pr];
+        const int clr = tgt ? grp.clear2[pr] : grp.clear1[pr];
         if (Ct == nullptr || row >= m) continue;
         uint32_t *dst = Ct + (size_t)row * cs32 + cw0;
+        if (grp.atomic) {  // destinations shared with other products of this launch (pre-zeroed)
+#pragma unroll
+          for (int jj = 0; jj < HCOL / 32; jj += 2) {
+            if (cw0 + jj + 2 <= cw32) red_xor64(dst + jj, out[jj], out[jj + 1]);
+            else if (cw0 + jj < cw32) red_xor32(dst + jj, out[jj]);
+          }
+          continue;
+        }
         if constexpr (HCOL >= 128) {
 #pragma unroll
           for (int q4 = 0; q4 < HCOL / 128; q4++) {
@@ -570,15 +601,22 @@ mma6_kernel(uint32_t *__restrict__ C, const uint8_t *__restrict__ Ab, const uint
 }  // namespace
 
 // ---- host side -------------------------------------------------------------------
+// One product per entry of the arrays (count <= GROUP_MAX), all of one shape.
+struct Mma6Job {
+  DMat *C1, *C2;
+  const DMat *A, *Bt;
+  int clear1, clear2;
+};
 template <int CG, bool WIDE, bool FULL>
-static void launch_mma6(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaStream_t s, DMat *C2, int clear2) {
+static void launch_mma6(const Mma6Job *jobs, int count, int atomic, cudaStream_t s) {
   static std::atomic<unsigned long long> attr_seen{0};
   if (first_use_on_this_device(attr_seen)) {
     M4B_CUDA(cudaFuncSetAttribute(mma6_kernel<CG, WIDE, FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_V6));
   }
+  const DMat *C = jobs[0].C1, *A = jobs[0].A;
   const int tile = 128 * CG;
   const int tiles_m = (C->nrows + tile - 1) / tile, tiles_n = (C->ncols + tile - 1) / tile;
-  const int ntiles = tiles_m * tiles_n;
+  const int ntiles = tiles_m * tiles_n * count;
   int nclusters = sm_count() / CG;
   if (nclusters > ntiles) nclusters = ntiles;
 #ifdef M4RI_B200_PERF_HOOKS
@@ -588,6 +626,19 @@ static void launch_mma6(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaS
 #endif
   for (int k0 = 0; k0 < A->ncols; k0 += K_CHUNK_MAX) {
     const int kc = A->ncols - k0 < K_CHUNK_MAX ? A->ncols - k0 : K_CHUNK_MAX;
+    Mma6Group grp = {};
+    grp.count = count;
+    grp.atomic = atomic;
+    for (int i = 0; i < count; i++) {
+      grp.A[i] = (const uint8_t *)(jobs[i].A->d + k0 / 64);
+      grp.B[i] = (const uint8_t *)(jobs[i].Bt->d + k0 / 64);
+      grp.a_rsb[i] = (long long)jobs[i].A->rowstride * 8;
+      grp.b_rsb[i] = (long long)jobs[i].Bt->rowstride * 8;
+      grp.C1[i] = (uint32_t *)jobs[i].C1->d;
+      grp.C2[i] = jobs[i].C2 ? (uint32_t *)jobs[i].C2->d : nullptr;
+      grp.clear1[i] = (jobs[i].clear1 && k0 == 0) ? 1 : 0;
+      grp.clear2[i] = (jobs[i].clear2 && k0 == 0) ? 1 : 0;
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(nclusters * CG);
     cfg.blockDim = dim3(NTHREADS);
@@ -600,13 +651,9 @@ static void launch_mma6(DMat *C, const DMat *A, const DMat *Bt, int clear, cudaS
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    timing_begin(CG == 2 ? "mma6_kernel<2>" : "mma6_kernel<1>", s, 2.0 * C->nrows * C->ncols * kc);
-    M4B_CUDA(cudaLaunchKernelEx(&cfg, mma6_kernel<CG, WIDE, FULL>, (uint32_t *)C->d,
-                                (const uint8_t *)(A->d + k0 / 64), (const uint8_t *)(Bt->d + k0 / 64),
-                                C->nrows, C->ncols, kc, (long long)A->rowstride * 8,
-                                (long long)Bt->rowstride * 8, C->rowstride * 2, C->width * 2, tiles_m,
-                                tiles_n, (clear && k0 == 0) ? 1 : 0, dbg, C2 ? (uint32_t *)C2->d : (uint32_t *)nullptr,
-                                (clear2 && k0 == 0) ? 1 : 0));
+    timing_begin(CG == 2 ? "mma6_kernel<2>" : "mma6_kernel<1>", s, 2.0 * C->nrows * C->ncols * kc * count);
+    M4B_CUDA(cudaLaunchKernelEx(&cfg, mma6_kernel<CG, WIDE, FULL>, grp, C->nrows, C->ncols, kc, C->rowstride * 2,
+                                C->width * 2, tiles_m, tiles_n, dbg));
     M4B_LAUNCHED();
     timing_end(s);
   }
@@ -616,33 +663,59 @@ static bool my_tiles_ok(int m, int n, int k, int tile) {
   return m % tile == 0 && n % tile == 0 && k % KS_BITS == 0 && (k <= K_CHUNK_MAX || K_CHUNK_MAX % KS_BITS == 0);
 }
 
+static void dispatch_mma6(const Mma6Job *jobs, int count, int atomic, int cg, cudaStream_t s) {
+  const DMat *C = jobs[0].C1, *A = jobs[0].A;
+  bool wide = true;
+  for (int i = 0; i < count; i++) {
+    const Mma6Job &j = jobs[i];
+    if (!mma_shape_ok(j.C1, j.A, j.Bt)) die("m4ri_b200: mma kernel needs 16-byte aligned rows\n");
+    if (j.C1->nrows != C->nrows || j.C1->ncols != C->ncols || j.A->ncols != A->ncols || j.C1->rowstride != C->rowstride ||
+        ((uintptr_t)j.C1->d & 15) ||
+        (j.C2 && (j.C2->nrows != C->nrows || j.C2->ncols != C->ncols || j.C2->rowstride != C->rowstride ||
+                  ((uintptr_t)j.C2->d & 15))))
+      die("m4ri_b200: the destinations of one launch must share shape, stride and alignment\n");
+    // 256-bit loads need 32-byte aligned rows (true for every width that is a multiple of 256 bits)
+    wide = wide && !(((uintptr_t)j.A->d | (uintptr_t)j.Bt->d) & 31) && !(j.A->rowstride & 3) && !(j.Bt->rowstride & 3);
+  }
+  const int tile = 128 * cg;
+  // whole tiles and whole stages in every k-chunk of the launch loop: the unconditional-load kernel
+  const bool full = wide && my_tiles_ok(C->nrows, C->ncols, A->ncols, tile);
+  if (cg == 2) {
+    if (full) launch_mma6<2, true, true>(jobs, count, atomic, s);
+    else if (wide) launch_mma6<2, true, false>(jobs, count, atomic, s);
+    else launch_mma6<2, false, false>(jobs, count, atomic, s);
+  } else {
+    if (full) launch_mma6<1, true, true>(jobs, count, atomic, s);
+    else if (wide) launch_mma6<1, true, false>(jobs, count, atomic, s);
+    else launch_mma6<1, false, false>(jobs, count, atomic, s);
+  }
+}
+
 // C (^)= A*Bt^T on the FP4 pipe; cg = CTAs per MMA. With C2: the same product also goes to
 // (clear2) or into (!clear2) C2, a matrix of C's shape and row stride.
 void k_mul_abt_mma6(DMat *C, const DMat *A, const DMat *Bt, int clear, int cg, cudaStream_t s, DMat *C2, int clear2) {
   if (C->nrows == 0 || C->ncols == 0) return;
-  if (C2 && (C2->nrows != C->nrows || C2->ncols != C->ncols || C2->rowstride != C->rowstride || ((uintptr_t)C2->d & 15)))
-    die("m4ri_b200: the second destination of a product must have the first one's shape, stride and alignment\n");
   if (A->ncols == 0) {
     if (clear) k_zero(C, s);
     if (C2 && clear2) k_zero(C2, s);
     return;
   }
   if (!has_tcgen05()) die("m4ri_b200: the tcgen05 MMA path needs an sm_100 device\n");
-  if (!mma_shape_ok(C, A, Bt)) die("m4ri_b200: mma kernel needs 16-byte aligned rows\n");
-  // 256-bit loads need 32-byte aligned rows (true for every width that is a multiple of 256 bits)
-  const bool wide = !(((uintptr_t)A->d | (uintptr_t)Bt->d) & 31) && !(A->rowstride & 3) && !(Bt->rowstride & 3);
-  const int tile = 128 * cg;
-  // whole tiles and whole stages in every k-chunk of the launch loop: the unconditional-load kernel
-  const bool full = wide && my_tiles_ok(C->nrows, C->ncols, A->ncols, tile);
-  if (cg == 2) {
-    if (full) launch_mma6<2, true, true>(C, A, Bt, clear, s, C2, clear2);
-    else if (wide) launch_mma6<2, true, false>(C, A, Bt, clear, s, C2, clear2);
-    else launch_mma6<2, false, false>(C, A, Bt, clear, s, C2, clear2);
-  } else {
-    if (full) launch_mma6<1, true, true>(C, A, Bt, clear, s, C2, clear2);
-    else if (wide) launch_mma6<1, true, false>(C, A, Bt, clear, s, C2, clear2);
-    else launch_mma6<1, false, false>(C, A, Bt, clear, s, C2, clear2);
-  }
+  Mma6Job job = {C, C2, A, Bt, clear, clear2};
+  dispatch_mma6(&job, 1, 0, cg, s);
+}
+
+// `count` products of one shape in ONE launch; every C1[i]/C2[i] (C2[i] may be NULL) is
+// accumulated into with atomic XORs, so destinations may repeat across the products (the caller
+// zeroes them first when it wants C = instead of C ^=).
+void k_mul_abt_mma6_group(int count, DMat *const *C1, DMat *const *C2, const DMat *const *A, const DMat *const *Bt,
+                          int cg, cudaStream_t s) {
+  if (count < 1 || count > GROUP_MAX) die("m4ri_b200: a product group holds 1 to %d products\n", GROUP_MAX);
+  if (C1[0]->nrows == 0 || C1[0]->ncols == 0 || A[0]->ncols == 0) return;
+  if (!has_tcgen05()) die("m4ri_b200: the tcgen05 MMA path needs an sm_100 device\n");
+  Mma6Job jobs[GROUP_MAX];
+  for (int i = 0; i < count; i++) jobs[i] = {C1[i], C2[i], A[i], Bt[i], 0, 0};
+  dispatch_mma6(jobs, count, 1, cg, s);
 }
 
 }  // namespace m4b

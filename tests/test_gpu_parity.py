@@ -479,6 +479,11 @@ def test_fused_strassen_level(gpu, m4, orc, variant, monkeypatch):
             dC0 = m4.DMat.from_host(c0)
             m4.dmul_abt(dC0, dA, dBt, clear=False, algo=m4.ALGO_MMA)
             assert (dC0.to_words()[:, : orc.width(n)] == (C0[:, : orc.width(n)] ^ want)).all(), (variant, levels, m, k, n)
+            # seven separate launches with two-destination epilogues instead of the one grouped launch
+            monkeypatch.setenv("M4RI_B200_NO_GROUPED_STRASSEN", "1")
+            m4.dmul(dC, dA, dB, clear=True, algo=m4.ALGO_MMA)
+            monkeypatch.delenv("M4RI_B200_NO_GROUPED_STRASSEN")
+            assert (dC.to_words()[:, : orc.width(n)] == want).all(), (variant, levels, m, k, n)
             # the unfused (Winograd) schedule gives the same words with more launches
             monkeypatch.setenv("M4RI_B200_NO_FUSED_STRASSEN", "1")
             l0 = m4.launch_count()
@@ -653,7 +658,9 @@ def test_n65536_single_gpu(gpu, m4):
     L.m4ri_b200_timing_reset()
     m4.dmul(dC, dA, dB, algo=m4.ALGO_AUTO)
     L.m4ri_b200_synchronize()
-    assert L.m4ri_b200_timing_count() == 49, "AUTO at n = 65536 runs 7^2 leaf products (two levels)"
+    # two levels: 7 sub-products (Winograd outside), each ONE grouped launch of its 7 leaf products
+    assert L.m4ri_b200_timing_count() == 7, "AUTO at n = 65536 runs 7 grouped launches of 7 leaves (two levels)"
+    assert abs(L.m4ri_b200_timing_ops() - 49 * 2.0 * 16384 ** 3) < 1e6
     assert L.m4ri_b200_dfreivalds(dC.h, dA.h, dB.h, 0xF5E1) == 1
     chk = dC.checksum()
     # row-block of the sharded job: rows [16384, 24576)
