@@ -28,7 +28,6 @@
 // The result is THE reduced row echelon form (unique), so parity with any other implementation
 // is bit-exact by construction; rank and pivot columns come with it.
 #include <algorithm>
-#include <unordered_map>
 #include <vector>
 
 #include "common.cuh"
@@ -57,6 +56,14 @@ __device__ long long g_it[64];
 #else
 #define CLK(i) do {} while (0)
 #endif
+
+// State that lives across the blocks of one elimination (the per-block ElimState is cleared at
+// every block): nothing of it is needed on the host before the very end, so the whole
+// elimination is enqueued without a host round trip.
+struct ElimGlobal {
+  int rank;   // pivots found in the blocks done so far = first candidate row of the next block
+  int moves;  // rows the current block's permutation moves
+};
 
 static inline unsigned cdiv(long long a, long long b) { return (unsigned)((a + b - 1) / b); }
 
@@ -92,8 +99,9 @@ __global__ void writeback_panel_kernel(word *W, int ws, int wwidth, const word *
 // ctag[k] = the combination of the selected rows (selection order) that gives the k-th reduced
 // pivot word.
 __global__ void __launch_bounds__(1024)
-pivot_search_kernel(const word *PT, int pstride, int j, int m, int r0, unsigned char *ispiv, int *pidx,
+pivot_search_kernel(const word *PT, int pstride, int j, int m, const ElimGlobal *gl, unsigned char *ispiv, int *pidx,
                     ElimState *st, int c0, word colmask /* valid columns of this word (pivot limit) */) {
+  const int r0 = gl->rank;
   __shared__ word pw[64], sw[1024];
   __shared__ unsigned long long ctag[64], slt[1024];
   __shared__ int pc[64], pr[64], srow[1024];
@@ -334,7 +342,7 @@ apply_rprime_kernel(word *PT, int pstride, int j, int L, int m, const int *pidx,
 __global__ void gather_pivot_rows_kernel(word *OP, int ostride, const word *W, int ws, int tw0, int tw,
                                          word *PT, int pstride, int bw, const ElimState *st) {
   const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  const int kb = st->kbn;
+  const int kb = st->kbn;  // (the grid is sized for a full block of pivots)
   if (idx >= (long long)kb * (tw + 1)) return;
   const int t = (int)(idx / (tw + 1)), w = (int)(idx % (tw + 1));
   const int row = st->blk_rows[t];
@@ -342,14 +350,89 @@ __global__ void gather_pivot_rows_kernel(word *OP, int ostride, const word *W, i
   else PT[(size_t)row * pstride + bw + (t >> 6)] ^= (word)1 << (t & 63);
 }
 
+// End of a block, one CTA: where every row goes. The block's pivot rows move up to positions
+// rank .. rank+kb-1 in pivot-column order; the rows they displace there (which are no pivots of
+// this block) take the positions the pivot rows vacate outside that range — which displaced row
+// goes to which free position does not matter (non-pivot rows are only candidates of later
+// blocks or end up zero). Writes the move list (src -> dst, through a temporary), the pivot
+// columns in order, and advances rank.
+__global__ void __launch_bounds__(1024)
+plan_permutation_kernel(const ElimState *st, ElimGlobal *gl, int *src, int *dst, int *piv_all) {
+  __shared__ int s_cols[EB_MAX];
+  __shared__ unsigned char s_flag[EB_MAX];
+  __shared__ int s_warp[32], s_total;
+  const int kb = st->kbn, rank = gl->rank, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int t = tid; t < kb; t += 1024) {
+    s_cols[t] = st->blk_cols[t];
+    s_flag[t] = 0;
+  }
+  __syncthreads();
+  for (int t = tid; t < kb; t += 1024) {
+    const int c = s_cols[t], r = st->blk_rows[t];
+    int pos = 0;
+    for (int u = 0; u < kb; u++) pos += s_cols[u] < c;  // pivot columns are distinct
+    src[t] = r;
+    dst[t] = rank + pos;
+    piv_all[rank + pos] = c;
+    if (r >= rank && r < rank + kb) s_flag[r - rank] = 1;  // this target position holds a pivot row
+  }
+  __syncthreads();
+  // two compactions over [0, kb) with one block-wide exclusive scan each: pass 0 lists the
+  // displaced rows (positions of the target range without a pivot row), pass 1 the vacated
+  // positions (pivot rows outside the target range)
+  const int per = (kb + 1023) / 1024, i0 = tid * per, i1 = min(kb, i0 + per);
+  for (int pass = 0; pass < 2; pass++) {
+    int mine = 0;
+    for (int i = i0; i < i1; i++) {
+      const int r = pass ? st->blk_rows[i] : 0;
+      mine += pass ? !(r >= rank && r < rank + kb) : !s_flag[i];
+    }
+    int incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      int w = s_warp[lane], wi = w;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, wi, o);
+        if (lane >= o) wi += v;
+      }
+      s_warp[lane] = wi - w;
+      if (lane == 31) s_total = wi;
+    }
+    __syncthreads();
+    int at = kb + s_warp[warp] + incl - mine;
+    for (int i = i0; i < i1; i++) {
+      if (pass == 0) {
+        if (!s_flag[i]) src[at++] = rank + i;
+      } else {
+        const int r = st->blk_rows[i];
+        if (!(r >= rank && r < rank + kb)) dst[at++] = r;
+      }
+    }
+    __syncthreads();
+  }
+  if (tid == 0) {
+    gl->moves = kb + s_total;  // (both passes count the same number of rows)
+    gl->rank = rank + kb;
+  }
+}
+
 // rows dst[q] of W := rows src[q] (through a compact temporary)
-__global__ void gather_rows_kernel(word *tmp, const word *W, int ws, int width, const int *src, int cnt) {
+__global__ void gather_rows_kernel(word *tmp, const word *W, int ws, int width, const int *src, const ElimGlobal *gl) {
+  const int cnt = gl->moves;
   const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (idx >= (long long)cnt * width) return;
   const int q = (int)(idx / width), w = (int)(idx % width);
   tmp[idx] = W[(size_t)src[q] * ws + w];
 }
-__global__ void scatter_rows_kernel(word *W, int ws, int width, const word *tmp, const int *dst, int cnt) {
+__global__ void scatter_rows_kernel(word *W, int ws, int width, const word *tmp, const int *dst, const ElimGlobal *gl) {
+  const int cnt = gl->moves;
   const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (idx >= (long long)cnt * width) return;
   const int q = (int)(idx / width), w = (int)(idx % width);
@@ -386,23 +469,37 @@ int k_rref(DMat *W, int pivot_cols, std::vector<int> *pivots, cudaStream_t s) {
   DMat *PT = dmat_new(m, 2 * B, s);       // [panel | tags], stride L
   DMat *OP = dmat_new(B, n, s);           // original pivot rows of the block (trailing columns)
   const int pstride = PT->rowstride, ws = W->rowstride;
+  const int nblocks = (pivot_cols + B - 1) / B, maxrank = std::min(m, pivot_cols);
   ElimState *st;
+  ElimGlobal *gl;
   unsigned char *ispiv;
-  int *pidx;
+  int *pidx, *perm, *piv_all;
   unsigned long long *mult;
   word *Rp, *tmp;
-  int *perm;
   M4B_CUDA(cudaMallocAsync(&st, sizeof(ElimState), s));
+  M4B_CUDA(cudaMallocAsync(&gl, sizeof(ElimGlobal), s));
+  M4B_CUDA(cudaMemsetAsync(gl, 0, sizeof(ElimGlobal), s));
   M4B_CUDA(cudaMallocAsync(&ispiv, (size_t)m, s));
   M4B_CUDA(cudaMallocAsync(&mult, (size_t)m * 8, s));
   M4B_CUDA(cudaMallocAsync(&pidx, (size_t)m * sizeof(int), s));
-  M4B_CUDA(cudaMemsetAsync(pidx, 0, (size_t)m * sizeof(int), s));
   M4B_CUDA(cudaMallocAsync(&Rp, (size_t)256 * L * 8, s));  // the step's 16 four-bit tables
   M4B_CUDA(cudaMallocAsync(&tmp, (size_t)2 * B * W->width * 8, s));
   M4B_CUDA(cudaMallocAsync(&perm, (size_t)4 * B * sizeof(int), s));
-  std::vector<int> h_rows(EB_MAX), h_cols(EB_MAX), src, dst;
-  int rank = 0;
-  for (int c0 = 0; c0 < pivot_cols && rank < m; c0 += B) {
+  M4B_CUDA(cudaMallocAsync(&piv_all, (size_t)(maxrank + B) * sizeof(int), s));
+  // rank after every block, copied home asynchronously: the host never waits for it, it only
+  // looks (two blocks late) whether the rank has reached the row count and stops enqueueing
+  static thread_local int *h_rank = nullptr;  // pinned, kept for the thread's lifetime
+  static thread_local int h_rank_cap = 0;
+  if (h_rank_cap < nblocks + 1) {
+    if (h_rank) M4B_CUDA(cudaFreeHost(h_rank));
+    h_rank_cap = std::max(nblocks + 1, 1024);
+    M4B_CUDA(cudaMallocHost(&h_rank, (size_t)h_rank_cap * sizeof(int)));
+  }
+  std::vector<cudaEvent_t> ev(nblocks);
+  for (auto &e : ev) M4B_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  int blocks_done = 0;
+  for (int b = 0, c0 = 0; c0 < pivot_cols; b++, c0 += B) {
+    if (b >= 2 && cudaEventQuery(ev[b - 2]) == cudaSuccess && h_rank[b - 2] >= m) break;  // every row is a pivot row
     const int cw0 = c0 / 64;
     const int bcols = std::min(B, pivot_cols - c0);            // columns of this block that may hold pivots
     const int steps = (bcols + 63) / 64;
@@ -414,7 +511,7 @@ int k_rref(DMat *W, int pivot_cols, std::vector<int> *pivots, cudaStream_t s) {
     for (int j = 0; j < steps; j++) {
       const int valid = std::min(64, bcols - 64 * j);
       const word colmask = valid == 64 ? ~(word)0 : (((word)1 << valid) - 1);
-      pivot_search_kernel<<<1, 1024, 0, s>>>(PT->d, pstride, j, m, rank, ispiv, pidx, st, c0, colmask);
+      pivot_search_kernel<<<1, 1024, 0, s>>>(PT->d, pstride, j, m, gl, ispiv, pidx, st, c0, colmask);
       M4B_LAUNCHED();
       const int nrc = (int)cdiv(L - j, RP_XW);
       prepare_step_kernel<<<nrc + cdiv(m, 256), 256, 0, s>>>(Rp, mult, L, PT->d, pstride, j, bw, m, nrc, st);
@@ -422,68 +519,48 @@ int k_rref(DMat *W, int pivot_cols, std::vector<int> *pivots, cudaStream_t s) {
       apply_rprime_kernel<<<cdiv((long long)m * (L - j), 256), 256, 0, s>>>(PT->d, pstride, j, L, m, pidx, mult, Rp, st);
       M4B_LAUNCHED();
     }
-    // pivots of the block -> host (one small synchronising copy per block)
-    int kb = 0;
-    M4B_CUDA(cudaMemcpyAsync(&kb, &st->kbn, sizeof(int), cudaMemcpyDeviceToHost, s));
-    M4B_CUDA(cudaStreamSynchronize(s));
-    if (kb > 0) {
-      M4B_CUDA(cudaMemcpyAsync(h_rows.data(), st->blk_rows, (size_t)kb * sizeof(int), cudaMemcpyDeviceToHost, s));
-      M4B_CUDA(cudaMemcpyAsync(h_cols.data(), st->blk_cols, (size_t)kb * sizeof(int), cudaMemcpyDeviceToHost, s));
-      // trailing update: everything right of the block
-      const int t0 = c0 + B;  // first trailing column (multiple of 128)
-      if (t0 < n) {
-        const int tw0 = t0 / 64, tw = W->width - tw0;
-        M4B_CUDA(cudaMemset2DAsync(OP->d, (size_t)OP->rowstride * 8, 0, (size_t)tw * 8, B, s));
-        gather_pivot_rows_kernel<<<cdiv((long long)kb * (tw + 1), 256), 256, 0, s>>>(OP->d, OP->rowstride, W->d, ws, tw0, tw,
-                                                                                      PT->d, pstride, bw, st);
-        M4B_LAUNCHED();
-        DMat Wt = dwin(W, 0, t0, m, n - t0), Tg = dwin(PT, 0, B, m, B), Ot = dwin(OP, 0, 0, B, n - t0);
-        dmul(&Wt, &Tg, &Ot, 0, M4RI_B200_ALGO_AUTO, s);
-      }
-      writeback_panel_kernel<<<cdiv((long long)m * bw, 256), 256, 0, s>>>(W->d, ws, W->width, PT->d, pstride, m, cw0, bw);
+    // trailing update: everything right of the block, as ONE product of fixed shape (the pivot
+    // count stays on the device: rows of OP and columns of T beyond it are zero)
+    const int t0 = c0 + B;  // first trailing column (multiple of 128)
+    if (t0 < n) {
+      const int tw0 = t0 / 64, tw = W->width - tw0;
+      M4B_CUDA(cudaMemset2DAsync(OP->d, (size_t)OP->rowstride * 8, 0, (size_t)tw * 8, B, s));
+      gather_pivot_rows_kernel<<<cdiv((long long)B * (tw + 1), 256), 256, 0, s>>>(OP->d, OP->rowstride, W->d, ws, tw0, tw,
+                                                                                 PT->d, pstride, bw, st);
       M4B_LAUNCHED();
-      M4B_CUDA(cudaStreamSynchronize(s));
-      // pivot rows up to rows rank .. rank+kb-1 in pivot-column order (sequential swaps, composed on the host)
-      std::vector<std::pair<int, int>> pv(kb);
-      for (int t = 0; t < kb; t++) pv[t] = {h_cols[t], h_rows[t]};
-      std::sort(pv.begin(), pv.end());
-      // sparse view of the permutation: position -> row whose content ends there, and its inverse
-      std::unordered_map<int, int> moved, where;
-      auto content_at = [&](int pos) { auto it = moved.find(pos); return it == moved.end() ? pos : it->second; };
-      auto pos_of = [&](int row) { auto it = where.find(row); return it == where.end() ? row : it->second; };
-      for (int t = 0; t < kb; t++) {
-        const int target = rank + t, prow = pv[t].second;
-        const int cur = pos_of(prow);          // where the pivot row is now
-        if (cur == target) continue;
-        const int other = content_at(target);  // what sits at the target position
-        moved[target] = prow; where[prow] = target;
-        moved[cur] = other; where[other] = cur;
-      }
-      src.clear(); dst.clear();
-      for (auto &e : moved)
-        if (e.first != e.second) { dst.push_back(e.first); src.push_back(e.second); }
-      if (!src.empty()) {
-        const int cnt = (int)src.size();
-        M4B_CUDA(cudaMemcpyAsync(perm, src.data(), (size_t)cnt * sizeof(int), cudaMemcpyHostToDevice, s));
-        M4B_CUDA(cudaMemcpyAsync(perm + 2 * B, dst.data(), (size_t)cnt * sizeof(int), cudaMemcpyHostToDevice, s));
-        gather_rows_kernel<<<cdiv((long long)cnt * W->width, 256), 256, 0, s>>>(tmp, W->d, ws, W->width, perm, cnt);
-        M4B_LAUNCHED();
-        scatter_rows_kernel<<<cdiv((long long)cnt * W->width, 256), 256, 0, s>>>(W->d, ws, W->width, tmp, perm + 2 * B, cnt);
-        M4B_LAUNCHED();
-        M4B_CUDA(cudaStreamSynchronize(s));  // src/dst are reused by the next block
-      }
-      if (pivots)
-        for (int t = 0; t < kb; t++) pivots->push_back(pv[t].first);
-      rank += kb;
+      DMat Wt = dwin(W, 0, t0, m, n - t0), Tg = dwin(PT, 0, B, m, B), Ot = dwin(OP, 0, 0, B, n - t0);
+      dmul(&Wt, &Tg, &Ot, 0, M4RI_B200_ALGO_AUTO, s);
     }
+    writeback_panel_kernel<<<cdiv((long long)m * bw, 256), 256, 0, s>>>(W->d, ws, W->width, PT->d, pstride, m, cw0, bw);
+    M4B_LAUNCHED();
+    // pivot rows up to rows rank .. rank+kb-1 in pivot-column order, planned and done on the device
+    plan_permutation_kernel<<<1, 1024, 0, s>>>(st, gl, perm, perm + 2 * B, piv_all);
+    M4B_LAUNCHED();
+    gather_rows_kernel<<<cdiv((long long)2 * B * W->width, 256), 256, 0, s>>>(tmp, W->d, ws, W->width, perm, gl);
+    M4B_LAUNCHED();
+    scatter_rows_kernel<<<cdiv((long long)2 * B * W->width, 256), 256, 0, s>>>(W->d, ws, W->width, tmp, perm + 2 * B, gl);
+    M4B_LAUNCHED();
+    M4B_CUDA(cudaMemcpyAsync(&h_rank[b], &gl->rank, sizeof(int), cudaMemcpyDeviceToHost, s));
+    M4B_CUDA(cudaEventRecord(ev[b], s));
+    blocks_done = b + 1;
   }
+  M4B_CUDA(cudaStreamSynchronize(s));
+  const int rank = blocks_done ? h_rank[blocks_done - 1] : 0;
+  if (pivots && rank > 0) {
+    pivots->resize(rank);
+    M4B_CUDA(cudaMemcpyAsync(pivots->data(), piv_all, (size_t)rank * sizeof(int), cudaMemcpyDeviceToHost, s));
+    M4B_CUDA(cudaStreamSynchronize(s));
+  }
+  for (auto &e : ev) M4B_CUDA(cudaEventDestroy(e));
   M4B_CUDA(cudaFreeAsync(st, s));
+  M4B_CUDA(cudaFreeAsync(gl, s));
   M4B_CUDA(cudaFreeAsync(ispiv, s));
   M4B_CUDA(cudaFreeAsync(pidx, s));
   M4B_CUDA(cudaFreeAsync(mult, s));
   M4B_CUDA(cudaFreeAsync(Rp, s));
   M4B_CUDA(cudaFreeAsync(tmp, s));
   M4B_CUDA(cudaFreeAsync(perm, s));
+  M4B_CUDA(cudaFreeAsync(piv_all, s));
   dmat_delete(PT, s);
   dmat_delete(OP, s);
   return rank;

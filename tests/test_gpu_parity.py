@@ -494,6 +494,24 @@ def test_fused_strassen_level(gpu, m4, orc, variant, monkeypatch):
             assert fused_launches < unfused_launches, (fused_launches, unfused_launches)
             for p in (a, b, c0):
                 L.mzd_free(p)
+        # operands and result as (pointer, stride) windows of larger parents: rows continue past
+        # the window on both sides, the destination is zeroed and accumulated into in place
+        L.m4ri_b200_set_strassen_levels(1)
+        m, k, n = 1024, 1536, 512
+        PA, PB, PC = m4.DMat.init(m + 7, k + 640).fill_random(41), m4.DMat.init(n + 5, k + 384).fill_random(42), \
+            m4.DMat.init(m + 3, n + 1152).fill_random(43)
+        wA = m4.DMat.wrap(PA.ptr + 3 * PA.rowstride * 8 + 2 * 16, m, k, PA.rowstride, keepalive=PA)
+        wBt = m4.DMat.wrap(PB.ptr + 2 * PB.rowstride * 8 + 4 * 16, n, k, PB.rowstride, keepalive=PB)
+        wC = m4.DMat.wrap(PC.ptr + 1 * PC.rowstride * 8 + 6 * 16, m, n, PC.rowstride, keepalive=PC)
+        before = PC.to_words()
+        A = PA.to_words()[3: 3 + m, 4: 4 + k // 64].copy()
+        Bt = PB.to_words()[2: 2 + n, 8: 8 + k // 64].copy()
+        want = orc.mul_m4rm(A, orc.transpose(Bt, k), k, n, threads=0)[:, : n // 64]
+        m4.dmul_abt(wC, wA, wBt, clear=True, algo=m4.ALGO_MMA)
+        after = PC.to_words()
+        assert (after[1: 1 + m, 12: 12 + n // 64] == want).all()
+        after[1: 1 + m, 12: 12 + n // 64] = before[1: 1 + m, 12: 12 + n // 64]
+        assert (after == before).all(), "the product wrote outside its window"
     finally:
         L.m4ri_b200_set_strassen_levels(-1)
         L.m4ri_b200_set_mma_variant(0)
