@@ -498,7 +498,7 @@ def test_fused_strassen_level(gpu, m4, orc, variant, monkeypatch):
         # the window on both sides, the destination is zeroed and accumulated into in place
         L.m4ri_b200_set_strassen_levels(1)
         m, k, n = 1024, 1536, 512
-        PA, PB, PC = m4.DMat.init(m + 7, k + 640).fill_random(41), m4.DMat.init(n + 5, k + 384).fill_random(42), \
+        PA, PB, PC = m4.DMat.init(m + 7, k + 640).fill_random(41), m4.DMat.init(n + 5, k + 896).fill_random(42), \
             m4.DMat.init(m + 3, n + 1152).fill_random(43)
         wA = m4.DMat.wrap(PA.ptr + 3 * PA.rowstride * 8 + 2 * 16, m, k, PA.rowstride, keepalive=PA)
         wBt = m4.DMat.wrap(PB.ptr + 2 * PB.rowstride * 8 + 4 * 16, n, k, PB.rowstride, keepalive=PB)
