@@ -232,6 +232,17 @@ class BinMatrix {
     return c;
   }
   BinMatrix transposed() const { return BinMatrix(nonnull(mzd_transpose(nullptr, mzd_))); }  // :272-279
+  // [A] [B] => [A B] (:219-232) and A over B (:234-245)
+  BinMatrix augmented(const BinMatrix &o) const {
+    if (nrows() != o.nrows()) throw std::logic_error("The rows need to be equal");
+    return BinMatrix(nonnull(mzd_concat(nullptr, mzd_, o.mzd_)));
+  }
+  BinMatrix stacked(const BinMatrix &o) const { return BinMatrix(nonnull(mzd_stack(nullptr, mzd_, o.mzd_))); }
+  // echelonize in place, return the rank (:255-261); rank() does it on a clone (:247-253)
+  size_t echelonize() { return (size_t)mzd_echelonize(mzd_, 0); }
+  size_t rank() const { return clone().echelonize(); }
+  // the inverse as a new matrix (:263-268); "null mzd_t" when the matrix is singular, as nonnull! panics
+  BinMatrix inverted() const { return BinMatrix(nonnull(mzd_inv_m4ri(nullptr, mzd_, 0))); }
   BinMatrix clone() const { return BinMatrix(*this); }
 
   // 1 x n or n x 1 matrix -> vector; the column case transposes first (:332-361)
@@ -304,6 +315,9 @@ class BinMatrix {
 
 inline BinMatrix BinVector::as_matrix() const { return BinMatrix::from_rows({*this}); }
 inline BinMatrix BinVector::as_column_matrix() const { return as_matrix().transposed(); }
+
+// Solve AX = B for X; B holds the solution afterwards; true on success (binary_matrix.rs:575-586)
+inline bool solve_left(BinMatrix a, BinMatrix &b) { return mzd_solve_left(a.mzd(), b.mzd(), 0, 1) == 0; }
 
 // &v * &A: a 1 x n matrix through mul_impl! (binary_matrix.rs:552-573)
 inline BinVector operator*(const BinVector &v, const BinMatrix &m) {

@@ -170,6 +170,39 @@ TEST(ops_bench_shapes) {
   CHECK(r.as_vector() == (m * v128));
 }
 
+// ---- the consumers of the product (binary_matrix.rs:219-268, 575-586): the reference holds no
+// unit test for them, so they are checked with identities that need no second implementation ----
+TEST(consumers_of_the_product) {
+  BinMatrix a = BinMatrix::random(40, 70), b = BinMatrix::random(40, 9), c = BinMatrix::random(13, 70);
+  BinMatrix ab = a.augmented(b), ac = a.stacked(c);
+  CHECK(ab.nrows() == 40 && ab.ncols() == 79 && ac.nrows() == 53 && ac.ncols() == 70);
+  for (size_t i = 0; i < 40; i++) {
+    for (size_t j = 0; j < 70; j++) CHECK(ab.bit(i, j) == a.bit(i, j) && ac.bit(i, j) == a.bit(i, j));
+    for (size_t j = 0; j < 9; j++) CHECK(ab.bit(i, 70 + j) == b.bit(i, j));
+  }
+  for (size_t i = 0; i < 13; i++)
+    for (size_t j = 0; j < 70; j++) CHECK(ac.bit(40 + i, j) == c.bit(i, j));
+  CHECK(BinMatrix::identity(77).rank() == 77);
+  CHECK(BinMatrix::zero(5, 300).rank() == 0);
+  CHECK(a.stacked(a).rank() == a.rank());                       // repeated rows add nothing
+  CHECK((a.transposed() * a).rank() <= a.rank());
+  // a random square matrix is invertible with probability ~0.29: try until one is
+  for (int tries = 0; tries < 200; tries++) {
+    BinMatrix m = BinMatrix::random(96, 96);
+    if (m.rank() < 96) continue;
+    BinMatrix inv = m.inverted();
+    CHECK((m * inv) == BinMatrix::identity(96));
+    CHECK((inv * m) == BinMatrix::identity(96));
+    BinMatrix rhs = BinMatrix::random(96, 17), x = rhs.clone();
+    CHECK(solve_left(m.clone(), x));
+    CHECK((m * x) == rhs);                                      // AX = B
+    BinMatrix e = m.clone();
+    CHECK(e.echelonize() == 96 && e == BinMatrix::identity(96)); // full rank: the reduced form is I
+    return;
+  }
+  CHECK(false && "no invertible 96 x 96 matrix in 200 tries");
+}
+
 int main() {
   if (m4ri_b200_device_count() <= 0) {
     std::fprintf(stderr, "test_friendly: no CUDA device (libm4ri_b200 has no CPU fallback)\n");
