@@ -116,6 +116,38 @@ mzd_t *mzd_inv_m4ri(mzd_t *dst, const mzd_t *src, int k); /* brilliantrussian.rs
  * zeroed); 0 = solved, -1 = inconsistent (B untouched). A is left as it was. */
 int mzd_solve_left(mzd_t *A, mzd_t *B, int cutoff, int inconsistency_check); /* solve.rs:23 (solve_left, binary_matrix.rs:582-586) */
 
+/* ---- PLE / PLUQ decomposition and permutations (m4ri-sys/src/ple.rs, mzp.rs) ----
+ * mzp.rs:9-12 keeps Mzp opaque; the layout is M4RI's published mzp_t. P->values[i] = j means
+ * "swap i and j", applied for i = 0, 1, ... in turn (LAPACK style), values[i] >= i. */
+typedef struct mzp_t {
+  rci_t *values;
+  rci_t length;
+} mzp_t;
+mzp_t *mzp_init(rci_t length);                             /* mzp.rs:18  identity permutation */
+void mzp_free(mzp_t *P);                                   /* mzp.rs:21 */
+mzp_t *mzp_init_window(mzp_t *P, rci_t begin, rci_t end);  /* mzp.rs:26  shares P's values */
+void mzp_free_window(mzp_t *condemned);                    /* mzp.rs:29 (declared there as `Mzp_free_window`, exported too) */
+void Mzp_free_window(mzp_t *condemned);
+mzp_t *mzp_copy(mzp_t *P, const mzp_t *Q);                 /* mzp.rs:33  P NULL: allocate */
+void mzp_set_ui(mzp_t *P, unsigned int value);             /* mzp.rs:36  identity (value is ignored, as in M4RI) */
+void mzp_print(const mzp_t *P);                            /* mzp.rs:51 */
+/* Row / column permutations of a host matrix, done on the GPU (one gather pass):
+ * left: rows i <-> P[i] for i = 0 .. len-1 in turn; left_trans: the same swaps in reverse order;
+ * right_trans: columns i <-> P[i] for i = 0 .. len-1 in turn; right: in reverse order. */
+void mzd_apply_p_left(mzd_t *A, const mzp_t *P);           /* mzp.rs:39 */
+void mzd_apply_p_left_trans(mzd_t *A, const mzp_t *P);     /* mzp.rs:42 */
+void mzd_apply_p_right(mzd_t *A, const mzp_t *P);          /* mzp.rs:45 */
+void mzd_apply_p_right_trans(mzd_t *A, const mzp_t *P);    /* mzp.rs:48 */
+/* A = P L E in place, returns the rank r (ple.rs:65). P (length nrows) and Q (length ncols) are
+ * overwritten. Afterwards row i < r holds L[i][0..i) in columns [0, i) and row i of the echelon
+ * form E from its pivot column Q[i] on (E[i][Q[i]] = 1); rows i >= r hold L[i][0..r) in columns
+ * [0, r). L has a unit diagonal (not stored). Q[0] < Q[1] < ... < Q[r-1] is the column rank
+ * profile, Q[i] = i beyond. mzd_apply_p_left(A_input, P) == L * E. cutoff is accepted and ignored. */
+rci_t mzd_ple(mzd_t *A, mzp_t *P, mzp_t *Q, int cutoff);
+/* A = P L U Q in place, returns the rank (ple.rs:35): as mzd_ple, with U = E after the column
+ * swaps i <-> Q[i], i = 0 .. r-1 in turn (mzd_apply_p_right_trans), upper triangular r x ncols. */
+rci_t mzd_pluq(mzd_t *A, mzp_t *P, mzp_t *Q, int cutoff);
+
 /* ---- additive API: algorithm choice, device-resident operands --------------- */
 enum m4ri_b200_algo {
   M4RI_B200_ALGO_AUTO = 0,  /* library picks (shape based)                        */
@@ -244,6 +276,9 @@ void m4ri_b200_dmul_abt_fp4_debug(m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *A
  * [0, pivot_cols) only (0 = all), the other columns are carried along. Returns the rank and the
  * first max_pivots pivot columns (increasing). Synchronises the stream once per column block. */
 int m4ri_b200_drref(m4ri_b200_dmat_t *W, int pivot_cols, int *pivot_columns, int max_pivots);
+/* PLE (pluq = 0) or PLUQ (pluq != 0) decomposition of a device matrix in place, storage as
+ * mzd_ple / mzd_pluq; P (nrows entries) and Q (ncols entries) are HOST arrays. Returns the rank. */
+int m4ri_b200_dple(m4ri_b200_dmat_t *W, rci_t *P, rci_t *Q, int pluq);
 /* 64-bit XOR-fold checksum of all words (position-mixed), computed on device. */
 uint64_t m4ri_b200_dchecksum(const m4ri_b200_dmat_t *M);
 /* 1 iff every valid word is zero (OR-reduction on device). */

@@ -44,6 +44,14 @@ class Mzd(ctypes.Structure):
 
 
 MzdP = ctypes.POINTER(Mzd)
+
+
+class Mzp(ctypes.Structure):
+    """M4RI's mzp_t (opaque in m4ri-sys/src/mzp.rs:9-12): LAPACK-style transposition list."""
+    _fields_ = [("values", ctypes.POINTER(ctypes.c_int)), ("length", ctypes.c_int)]
+
+
+MzpP = ctypes.POINTER(Mzp)
 _lib = None
 
 
@@ -69,6 +77,13 @@ def lib():
         "mzd_echelonize_m4ri": (i, [MzdP, i, i]), "mzd_inv_m4ri": (MzdP, [MzdP, MzdP, i]),
         "mzd_solve_left": (i, [MzdP, MzdP, i, i]),
         "m4ri_b200_drref": (i, [vp, i, ctypes.POINTER(i), i]),
+        "mzp_init": (MzpP, [i]), "mzp_free": (None, [MzpP]), "mzp_init_window": (MzpP, [MzpP, i, i]),
+        "mzp_free_window": (None, [MzpP]), "Mzp_free_window": (None, [MzpP]), "mzp_copy": (MzpP, [MzpP, MzpP]),
+        "mzp_set_ui": (None, [MzpP, u]), "mzp_print": (None, [MzpP]),
+        "mzd_apply_p_left": (None, [MzdP, MzpP]), "mzd_apply_p_left_trans": (None, [MzdP, MzpP]),
+        "mzd_apply_p_right": (None, [MzdP, MzpP]), "mzd_apply_p_right_trans": (None, [MzdP, MzpP]),
+        "mzd_ple": (i, [MzdP, MzpP, MzpP, i]), "mzd_pluq": (i, [MzdP, MzpP, MzpP, i]),
+        "m4ri_b200_dple": (i, [vp, ctypes.POINTER(i), ctypes.POINTER(i), i]),
         "mzd_concat": (MzdP, [MzdP, MzdP, MzdP]), "mzd_stack": (MzdP, [MzdP, MzdP, MzdP]),
         "mzd_mul": (MzdP, [MzdP, MzdP, MzdP, i]), "mzd_addmul": (MzdP, [MzdP, MzdP, MzdP, i]),
         "mzd_mul_m4rm": (MzdP, [MzdP, MzdP, MzdP, i]),

@@ -47,6 +47,11 @@ struct ElimState {
   unsigned long long ctag[64];   // row k of the inverse of the pivot words on the pivot columns
   int blk_rows[EB_MAX];          // pivots of the block in selection order: row, column
   int blk_cols[EB_MAX];
+  // PLE only (lu_pivot_search_kernel): the step's pivots by COLUMN of the word
+  unsigned long long pivmask;    // columns that hold a pivot
+  word pwk[64];                  // pivot k's word j as the pivot row keeps it: [L | 1 | E]
+  word pwcol[64];                // the same words by pivot column
+  int kcol[64];                  // selection index by pivot column
 };
 
 #ifdef M4RI_B200_PERF_HOOKS
@@ -424,19 +429,282 @@ plan_permutation_kernel(const ElimState *st, ElimGlobal *gl, int *src, int *dst,
 }
 
 // rows dst[q] of W := rows src[q] (through a compact temporary)
-__global__ void gather_rows_kernel(word *tmp, const word *W, int ws, int width, const int *src, const ElimGlobal *gl) {
+// (rowid, PLE only: which original row sits at every position — moved with the rows)
+__global__ void gather_rows_kernel(word *tmp, const word *W, int ws, int width, const int *src, const ElimGlobal *gl,
+                                   int *tmpid, const int *rowid) {
   const int cnt = gl->moves;
   const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (idx >= (long long)cnt * width) return;
   const int q = (int)(idx / width), w = (int)(idx % width);
   tmp[idx] = W[(size_t)src[q] * ws + w];
+  if (rowid && w == 0) tmpid[q] = rowid[src[q]];
 }
-__global__ void scatter_rows_kernel(word *W, int ws, int width, const word *tmp, const int *dst, const ElimGlobal *gl) {
+__global__ void scatter_rows_kernel(word *W, int ws, int width, const word *tmp, const int *dst, const ElimGlobal *gl,
+                                    const int *tmpid, int *rowid) {
   const int cnt = gl->moves;
   const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (idx >= (long long)cnt * width) return;
   const int q = (int)(idx / width), w = (int)(idx % width);
   W[(size_t)dst[q] * ws + w] = tmp[idx];
+  if (rowid && w == 0) rowid[dst[q]] = tmpid[q];
+}
+
+// ---- PLE (mzd_ple / mzd_pluq, m4ri-sys/src/ple.rs:35,65): the LU flavour of a 64-column step ----
+// Columns are taken in increasing order; a row is eliminated only on the bits ABOVE a pivot
+// column and keeps the bit at the pivot column itself: that bit is its multiplier (the entry of
+// L). A row "stops" at the first non-pivot column where it still has a bit — there it can become
+// the pivot of that column.
+__device__ __forceinline__ word bits_above(int b) { return b >= 63 ? (word)0 : ~(word)0 << (b + 1); }
+
+// Continue the column scan of one row's word from bit `from` against the pivots published in
+// shared memory: returns the stop column (64: the row depends on the pivots).
+__device__ __forceinline__ int lu_scan(word &w, unsigned long long &lt, int from, word pivmask, word colmask,
+                                       const word *pwcol, const unsigned long long *ctcol) {
+  word consider = from >= 64 ? (word)0 : ~(word)0 << from;
+  for (;;) {
+    const word t = w & consider & colmask;
+    if (!t) return 64;
+    const int b = __ffsll((long long)t) - 1;
+    if (!((pivmask >> b) & 1)) return b;
+    w ^= pwcol[b] & bits_above(b);
+    lt ^= ctcol[b];
+    consider = bits_above(b);
+  }
+}
+
+// One CTA: the pivots of word column j for the PLE. 1024 candidate rows at a time are scanned
+// against the pivots found so far and the rows that stop somewhere are compacted; warp 0 takes
+// them 32 at a time: the smallest stop column of the group gets its pivot (first lane that stops
+// there), the other lanes stopping there absorb it and scan on. A pivot found later at a smaller
+// column never touches the earlier pivots: every row scanned before had a zero there.
+// ctag[k] = the combination of the ORIGINAL selected rows that makes pivot row k (row k of the
+// inverse of the step's unit lower triangular L, in selection indices).
+__global__ void __launch_bounds__(1024)
+lu_pivot_search_kernel(const word *PT, int pstride, int j, int m, const ElimGlobal *gl, unsigned char *ispiv, int *pidx,
+                       ElimState *st, int c0, word colmask) {
+  const int r0 = gl->rank;
+  __shared__ word pwcol[64], pwk[64], sw[1024];
+  __shared__ unsigned long long ctcol[64], ctk[64], slt[1024];
+  __shared__ int pc[64], pr[64], kcol[64], srow[1024], sstop[1024];
+  __shared__ word pmask_s;
+  __shared__ int kp_s, cnt, wcnt[32];
+  const int tid = threadIdx.x, lane = tid & 31;
+  if (tid < 64 && tid < st->kp) pidx[st->pr[tid]] = 0;  // the previous step's pivot marks
+  __syncthreads();
+  if (tid == 0) {
+    kp_s = 0;
+    cnt = 0;
+    pmask_s = 0;
+    st->kb = st->kbn;
+  }
+  if (tid < 64) {
+    pwcol[tid] = 0;
+    ctcol[tid] = 0;
+    kcol[tid] = 0;
+  }
+  int kp = 0;  // warp 0's count
+  __syncthreads();
+  for (int chunk0 = r0; chunk0 < m; chunk0 += 1024) {
+    const word pm = pmask_s;
+    if ((pm & colmask) == colmask) break;  // every column of the word has its pivot
+    const int row = chunk0 + tid;
+    word w = 0;
+    if (row < m && !ispiv[row]) w = PT[(size_t)row * pstride + j];
+    unsigned long long lt = 0;
+    const int stop = lu_scan(w, lt, 0, pm, colmask, pwcol, ctcol);
+    // compaction in row order (deterministic pivots): per-warp counts, then a prefix over them
+    const unsigned nz = __ballot_sync(0xffffffffu, stop < 64);
+    if (lane == 0) wcnt[tid >> 5] = __popc(nz);
+    __syncthreads();
+    const int wc = wcnt[lane];
+    const int base = __reduce_add_sync(0xffffffffu, lane < (tid >> 5) ? wc : 0);
+    if (tid < 32) {
+      const int total = __reduce_add_sync(0xffffffffu, wc);
+      if (lane == 0) cnt = total;
+    }
+    if (stop < 64) {
+      const int e = base + __popc(nz & ((1u << lane) - 1));
+      sw[e] = w;
+      slt[e] = lt;
+      srow[e] = row;
+      sstop[e] = stop;
+    }
+    __syncthreads();
+    if (tid < 32) {
+      const int n = cnt;
+      word pmask = pm;
+      for (int g = 0; g < n; g += 32) {
+        if ((pmask & colmask) == colmask) break;
+        const int e = g + lane, ec = e < n ? e : 0;
+        word v = sw[ec];
+        unsigned long long vt = slt[ec];
+        const int vrow = srow[ec];
+        int vstop = sstop[ec], mine = -1;
+        if (e >= n) { v = 0; vt = 0; vstop = 64; }
+        __syncwarp();
+        if (vstop < 64) vstop = lu_scan(v, vt, vstop, pmask, colmask, pwcol, ctcol);  // pivots of earlier groups
+        __syncwarp();
+        for (;;) {
+          const int cmin = __reduce_min_sync(0xffffffffu, vstop);
+          if (cmin >= 64) break;
+          const int src = __ffs(__ballot_sync(0xffffffffu, vstop == cmin)) - 1;
+          const word pv = __shfl_sync(0xffffffffu, v, src);
+          const unsigned long long pt = __shfl_sync(0xffffffffu, vt, src) ^ (1ull << kp);
+          const int prow = __shfl_sync(0xffffffffu, vrow, src);
+          if (lane == 0) {
+            pwcol[cmin] = pv; ctcol[cmin] = pt; kcol[cmin] = kp;
+            pwk[kp] = pv; ctk[kp] = pt; pr[kp] = prow; pc[kp] = cmin;
+          }
+          pmask |= (word)1 << cmin;
+          __syncwarp();
+          if (lane == src) {
+            mine = kp;
+            vstop = 64;
+          } else if (vstop == cmin) {
+            v ^= pv & bits_above(cmin);
+            vt ^= pt;
+            vstop = lu_scan(v, vt, cmin + 1, pmask, colmask, pwcol, ctcol);
+          }
+          __syncwarp();
+          kp++;
+        }
+        if (mine >= 0) { ispiv[vrow] = 1; pidx[vrow] = mine + 1; }
+      }
+      if (lane == 0) {
+        pmask_s = pmask;
+        kp_s = kp;
+        cnt = 0;
+      }
+    }
+    __syncthreads();
+  }
+  const int n = kp_s;
+  if (tid < 64) {
+    const int kb = st->kbn;
+    st->pr[tid] = tid < n ? pr[tid] : -1;
+    st->pc[tid] = tid < n ? pc[tid] : 0;
+    st->ctag[tid] = tid < n ? ctk[tid] : 0;
+    st->pwk[tid] = tid < n ? pwk[tid] : 0;
+    st->pwcol[tid] = pwcol[tid];
+    st->kcol[tid] = kcol[tid];
+    if (tid < n) {
+      st->blk_rows[kb + tid] = pr[tid];
+      st->blk_cols[kb + tid] = c0 + 64 * j + pc[tid];
+    }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    st->pivmask = pmask_s;
+    st->kp = n;
+    st->kbn = st->kbn + n;
+  }
+}
+
+// Word j of every row after the step, and the multipliers of the rank-64 update of the words
+// right of it: candidate rows are scanned against the complete pivot set (the bits left at the
+// pivot columns are the entries of L, mult = the same bits in selection indices), the step's
+// pivot rows get their [L | 1 | E] word, rows above the block's first candidate and the pivots of
+// earlier steps are left alone (mult = 0).
+__global__ void __launch_bounds__(256)
+lu_rows_kernel(word *PT, int pstride, int j, int m, const ElimGlobal *gl, const unsigned char *ispiv, const int *pidx,
+               unsigned long long *mult, const ElimState *st) {
+  __shared__ word pwcol[64];
+  __shared__ int kcol[64];
+  const int t = threadIdx.x;
+  if (t < 64) {
+    pwcol[t] = st->pwcol[t];
+    kcol[t] = st->kcol[t];
+  }
+  __syncthreads();
+  const int i = blockIdx.x * 256 + t;
+  if (i >= m) return;
+  const int pk = pidx[i];
+  if (pk) {
+    PT[(size_t)i * pstride + j] = st->pwk[pk - 1];
+    mult[i] = 0;
+    return;
+  }
+  if (i < gl->rank || ispiv[i] || st->kp == 0) {
+    mult[i] = 0;
+    return;
+  }
+  const word pivmask = st->pivmask;
+  word w = PT[(size_t)i * pstride + j], consider = ~(word)0;
+  unsigned long long mm = 0;
+  for (;;) {
+    const word tt = w & consider & pivmask;
+    if (!tt) break;
+    const int b = __ffsll((long long)tt) - 1;
+    w ^= pwcol[b] & bits_above(b);
+    mm |= 1ull << kcol[b];
+    consider = bits_above(b);
+  }
+  PT[(size_t)i * pstride + j] = w;
+  mult[i] = mm;
+}
+
+// ---- PLE, the end: L compressed into the first `rank` columns ---------------------------------
+// Lc[i] bit k = W[i][Q[k]] for k < min(i, rank): row i's multiplier for pivot k sits at pivot
+// column Q[k] during the elimination; the documented storage (ple.rs:44-51, "L and S stored in
+// place over A") has column k of L in column k.
+__global__ void gather_l_kernel(word *Lc, int lcs, int lcw, const word *W, int ws, int m, int rank, const int *Q) {
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (idx >= (long long)m * lcw) return;
+  const int i = (int)(idx / lcw), dw = (int)(idx % lcw);
+  const int kmax = min(i, rank);
+  const word *row = W + (size_t)i * ws;
+  word o = 0;
+  for (int b = 0; b < 64; b++) {
+    const int k = 64 * dw + b;
+    if (k >= kmax) break;
+    const int c = Q[k];
+    o |= ((row[c >> 6] >> (c & 63)) & 1) << b;
+  }
+  Lc[(size_t)i * lcs + dw] = o;
+}
+// Rows below the rank hold nothing but multipliers; a pivot row keeps its columns from Q[i] on.
+__global__ void strip_l_kernel(word *W, int ws, int width, int m, int rank, const int *Q) {
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (idx >= (long long)m * width) return;
+  const int i = (int)(idx / width), w = (int)(idx % width);
+  word *p = W + (size_t)i * ws + w;
+  if (i >= rank) { *p = 0; return; }
+  const int c = Q[i];
+  if (w < (c >> 6)) *p = 0;
+  else if (w == (c >> 6)) *p &= ~(word)0 << (c & 63);
+}
+// out[i][c] = in[i][colsrc[c]] for the first `rows` rows (PLUQ: U = E with its columns permuted)
+__global__ void permute_cols_kernel(word *out, int os, const word *in, int is, int rows, int width, int ncols,
+                                    const int *colsrc) {
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (idx >= (long long)rows * width) return;
+  const int i = (int)(idx / width), w = (int)(idx % width);
+  const word *row = in + (size_t)i * is;
+  word o = 0;
+  for (int b = 0; b < 64; b++) {
+    const int c = 64 * w + b;
+    if (c >= ncols) break;
+    const int sc = colsrc[c];
+    o |= ((row[sc >> 6] >> (sc & 63)) & 1) << b;
+  }
+  out[(size_t)i * os + w] = o;
+}
+__global__ void merge_l_kernel(word *W, int ws, const word *Lc, int lcs, int lcw, int m) {
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (idx >= (long long)m * lcw) return;
+  const int i = (int)(idx / lcw), w = (int)(idx % lcw);
+  W[(size_t)i * ws + w] |= Lc[(size_t)i * lcs + w];
+}
+// out[i] = in[src[i]] (mzd_apply_p_left*: the composed row permutation in one pass)
+__global__ void permute_rows_kernel(word *out, int os, const word *in, int is, int rows, int width, const int *src) {
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (idx >= (long long)rows * width) return;
+  const int i = (int)(idx / width), w = (int)(idx % width);
+  out[(size_t)i * os + w] = in[(size_t)src[i] * is + w];
+}
+__global__ void iota_kernel(int *a, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) a[i] = i;
 }
 
 __global__ void set_identity_kernel(word *W, int ws, int n, int col0) {
@@ -459,7 +727,13 @@ static int block_width() {
 // Reduced row echelon form of W in place, pivots searched in columns [0, pivot_cols) only (the
 // rest is carried along: the right-hand side of a solve, the identity of an inversion).
 // Returns the rank; pivots (if given) receives the pivot columns in increasing order.
-int k_rref(DMat *W, int pivot_cols, std::vector<int> *pivots, cudaStream_t s) {
+//
+// lu = true is the PLE flavour of the same blocked schedule (k_ple below): pivots column by
+// column, rows eliminated only below and right of a pivot, multipliers left at the pivot columns;
+// d_rowid (m ints on the device, identity on entry) follows the rows through the permutations
+// and d_pivots_out (may be NULL, >= min(m, pivot_cols) + block ints) receives the pivot columns.
+static int eliminate(DMat *W, int pivot_cols, bool lu, std::vector<int> *pivots, int *d_rowid, int *d_pivots_out,
+                     cudaStream_t s) {
   const int m = W->nrows, n = W->ncols;
   if (pivots) pivots->clear();
   if (m == 0 || n == 0 || pivot_cols <= 0) return 0;
@@ -473,7 +747,7 @@ int k_rref(DMat *W, int pivot_cols, std::vector<int> *pivots, cudaStream_t s) {
   ElimState *st;
   ElimGlobal *gl;
   unsigned char *ispiv;
-  int *pidx, *perm, *piv_all;
+  int *pidx, *perm, *piv_all, *tmpid = nullptr;
   unsigned long long *mult;
   word *Rp, *tmp;
   M4B_CUDA(cudaMallocAsync(&st, sizeof(ElimState), s));
@@ -485,7 +759,9 @@ int k_rref(DMat *W, int pivot_cols, std::vector<int> *pivots, cudaStream_t s) {
   M4B_CUDA(cudaMallocAsync(&Rp, (size_t)256 * L * 8, s));  // the step's 16 four-bit tables
   M4B_CUDA(cudaMallocAsync(&tmp, (size_t)2 * B * W->width * 8, s));
   M4B_CUDA(cudaMallocAsync(&perm, (size_t)4 * B * sizeof(int), s));
-  M4B_CUDA(cudaMallocAsync(&piv_all, (size_t)(maxrank + B) * sizeof(int), s));
+  if (d_pivots_out) piv_all = d_pivots_out;
+  else M4B_CUDA(cudaMallocAsync(&piv_all, (size_t)(maxrank + B) * sizeof(int), s));
+  if (d_rowid) M4B_CUDA(cudaMallocAsync(&tmpid, (size_t)2 * B * sizeof(int), s));
   // rank after every block, copied home asynchronously: the host never waits for it, it only
   // looks (two blocks late) whether the rank has reached the row count and stops enqueueing
   static thread_local int *h_rank = nullptr;  // pinned, kept for the thread's lifetime
@@ -511,6 +787,20 @@ int k_rref(DMat *W, int pivot_cols, std::vector<int> *pivots, cudaStream_t s) {
     for (int j = 0; j < steps; j++) {
       const int valid = std::min(64, bcols - 64 * j);
       const word colmask = valid == 64 ? ~(word)0 : (((word)1 << valid) - 1);
+      if (lu) {
+        // the word column itself is finished by lu_rows_kernel; the rank-64 update starts right of it
+        lu_pivot_search_kernel<<<1, 1024, 0, s>>>(PT->d, pstride, j, m, gl, ispiv, pidx, st, c0, colmask);
+        M4B_LAUNCHED();
+        const int nrc = (int)cdiv(L - j - 1, RP_XW);
+        prepare_step_kernel<<<nrc, 256, 0, s>>>(Rp, mult, L, PT->d, pstride, j + 1, bw, m, nrc, st);
+        M4B_LAUNCHED();
+        lu_rows_kernel<<<cdiv(m, 256), 256, 0, s>>>(PT->d, pstride, j, m, gl, ispiv, pidx, mult, st);
+        M4B_LAUNCHED();
+        apply_rprime_kernel<<<cdiv((long long)m * (L - j - 1), 256), 256, 0, s>>>(PT->d, pstride, j + 1, L, m, pidx,
+                                                                                 mult, Rp, st);
+        M4B_LAUNCHED();
+        continue;
+      }
       pivot_search_kernel<<<1, 1024, 0, s>>>(PT->d, pstride, j, m, gl, ispiv, pidx, st, c0, colmask);
       M4B_LAUNCHED();
       const int nrc = (int)cdiv(L - j, RP_XW);
@@ -536,9 +826,11 @@ int k_rref(DMat *W, int pivot_cols, std::vector<int> *pivots, cudaStream_t s) {
     // pivot rows up to rows rank .. rank+kb-1 in pivot-column order, planned and done on the device
     plan_permutation_kernel<<<1, 1024, 0, s>>>(st, gl, perm, perm + 2 * B, piv_all);
     M4B_LAUNCHED();
-    gather_rows_kernel<<<cdiv((long long)2 * B * W->width, 256), 256, 0, s>>>(tmp, W->d, ws, W->width, perm, gl);
+    gather_rows_kernel<<<cdiv((long long)2 * B * W->width, 256), 256, 0, s>>>(tmp, W->d, ws, W->width, perm, gl,
+                                                                                 tmpid, d_rowid);
     M4B_LAUNCHED();
-    scatter_rows_kernel<<<cdiv((long long)2 * B * W->width, 256), 256, 0, s>>>(W->d, ws, W->width, tmp, perm + 2 * B, gl);
+    scatter_rows_kernel<<<cdiv((long long)2 * B * W->width, 256), 256, 0, s>>>(W->d, ws, W->width, tmp, perm + 2 * B,
+                                                                                  gl, tmpid, d_rowid);
     M4B_LAUNCHED();
     M4B_CUDA(cudaMemcpyAsync(&h_rank[b], &gl->rank, sizeof(int), cudaMemcpyDeviceToHost, s));
     M4B_CUDA(cudaEventRecord(ev[b], s));
@@ -560,10 +852,97 @@ int k_rref(DMat *W, int pivot_cols, std::vector<int> *pivots, cudaStream_t s) {
   M4B_CUDA(cudaFreeAsync(Rp, s));
   M4B_CUDA(cudaFreeAsync(tmp, s));
   M4B_CUDA(cudaFreeAsync(perm, s));
-  M4B_CUDA(cudaFreeAsync(piv_all, s));
+  if (!d_pivots_out) M4B_CUDA(cudaFreeAsync(piv_all, s));
+  if (tmpid) M4B_CUDA(cudaFreeAsync(tmpid, s));
   dmat_delete(PT, s);
   dmat_delete(OP, s);
   return rank;
+}
+
+int k_rref(DMat *W, int pivot_cols, std::vector<int> *pivots, cudaStream_t s) {
+  return eliminate(W, pivot_cols, false, pivots, nullptr, nullptr, s);
+}
+
+// PLE / PLUQ decomposition of W in place (m4ri-sys/src/ple.rs:35,65). On return, with r the rank:
+//   rows 0 .. r-1    row i holds L[i][0 .. i) in columns [0, i) and, from column Q[i] on, row i of
+//                    the echelon form E (E[i][Q[i]] = 1, zero left of it) — for pluq, from column
+//                    i on, row i of U = E with columns i and Q[i] swapped for i = 0 .. r-1 in turn
+//   rows r .. m-1    L[i][0 .. r) in columns [0, r), zero elsewhere
+//   P (m entries)    row transpositions: swapping rows i and P[i] of the INPUT for i = 0 .. m-1 in
+//                    turn gives L * E (so A = P L E with P the product of the swaps; P[i] >= i)
+//   Q (n entries)    Q[i] = pivot column of row i for i < r (the column rank profile, increasing),
+//                    Q[i] = i beyond
+// Pivot rows are chosen deterministically (lowest row index among the candidates that stop at
+// the column, in chunks of 1024 rows); M4RI's choice differs in general — the decomposition is
+// not unique, its defining identity is what the tests check.
+int k_ple(DMat *W, int *P, int *Q, bool pluq, cudaStream_t s) {
+  const int m = W->nrows, n = W->ncols;
+  for (int i = 0; i < m; i++) P[i] = i;
+  for (int c = 0; c < n; c++) Q[c] = c;
+  if (m == 0 || n == 0) return 0;
+  const int B = block_width();
+  int *rowid, *dq;
+  M4B_CUDA(cudaMallocAsync(&rowid, (size_t)m * sizeof(int), s));
+  M4B_CUDA(cudaMallocAsync(&dq, (size_t)(std::min(m, n) + B) * sizeof(int), s));
+  iota_kernel<<<cdiv(m, 256), 256, 0, s>>>(rowid, m);
+  M4B_LAUNCHED();
+  std::vector<int> piv;
+  const int r = eliminate(W, n, true, &piv, rowid, dq, s);
+  std::vector<int> ids(m);
+  M4B_CUDA(cudaMemcpyAsync(ids.data(), rowid, (size_t)m * sizeof(int), cudaMemcpyDeviceToHost, s));
+  const int ws = W->rowstride, width = W->width;
+  if (r > 0) {
+    const int lcw = width_of(r);
+    DMat *Lc = dmat_new(m, r, s);
+    gather_l_kernel<<<cdiv((long long)m * lcw, 256), 256, 0, s>>>(Lc->d, Lc->rowstride, lcw, W->d, ws, m, r, dq);
+    M4B_LAUNCHED();
+    strip_l_kernel<<<cdiv((long long)m * width, 256), 256, 0, s>>>(W->d, ws, width, m, r, dq);
+    M4B_LAUNCHED();
+    if (pluq) {
+      // columns: swap i <-> Q[i] for i = 0 .. r-1 in turn; colsrc[c] = the column of E that lands at c
+      std::vector<int> colsrc(n);
+      for (int c = 0; c < n; c++) colsrc[c] = c;
+      bool moved = false;
+      for (int i = 0; i < r; i++)
+        if (piv[i] != i) { std::swap(colsrc[i], colsrc[piv[i]]); moved = true; }
+      if (moved) {
+        int *dsrc;
+        M4B_CUDA(cudaMallocAsync(&dsrc, (size_t)n * sizeof(int), s));
+        M4B_CUDA(cudaMemcpyAsync(dsrc, colsrc.data(), (size_t)n * sizeof(int), cudaMemcpyHostToDevice, s));
+        DMat *U = dmat_new(r, n, s);
+        permute_cols_kernel<<<cdiv((long long)r * width, 256), 256, 0, s>>>(U->d, U->rowstride, W->d, ws, r, width, n,
+                                                                           dsrc);
+        M4B_LAUNCHED();
+        DMat top = dwin(W, 0, 0, r, n);
+        k_copy(&top, U, s);
+        M4B_CUDA(cudaStreamSynchronize(s));  // colsrc is read by the copy above
+        dmat_delete(U, s);
+        M4B_CUDA(cudaFreeAsync(dsrc, s));
+      }
+    }
+    merge_l_kernel<<<cdiv((long long)m * lcw, 256), 256, 0, s>>>(W->d, ws, Lc->d, Lc->rowstride, lcw, m);
+    M4B_LAUNCHED();
+    dmat_delete(Lc, s);
+  } else {
+    k_zero(W, s);
+  }
+  M4B_CUDA(cudaStreamSynchronize(s));
+  M4B_CUDA(cudaFreeAsync(rowid, s));
+  M4B_CUDA(cudaFreeAsync(dq, s));
+  for (int i = 0; i < r; i++) Q[i] = piv[i];
+  // the final arrangement (position p holds input row ids[p]) as transpositions P[i] >= i
+  std::vector<int> cur(m), pos(m);
+  for (int i = 0; i < m; i++) cur[i] = pos[i] = i;
+  for (int i = 0; i < m; i++) {
+    const int want = ids[i], at = pos[want];
+    P[i] = at;
+    const int other = cur[i];
+    cur[at] = other;
+    pos[other] = at;
+    cur[i] = want;
+    pos[want] = i;
+  }
+  return r;
 }
 
 void k_set_identity(DMat *W, int n, int col0, cudaStream_t s) {
@@ -592,7 +971,85 @@ int m4ri_b200_drref(m4ri_b200_dmat_t *W, int pivot_cols, int *pivot_columns, int
   return r;
 }
 
+int m4ri_b200_dple(m4ri_b200_dmat_t *W, rci_t *P, rci_t *Q, int pluq) {
+  return k_ple(W, P, Q, pluq != 0, current_stream());
+}
+
 // ---- host ABI: the reference's names ---------------------------------------------------
+static rci_t host_ple(mzd_t *A, mzp_t *P, mzp_t *Q, bool pluq, const char *who) {
+  if (P->length != A->nrows || Q->length != A->ncols)
+    die("m4ri_b200: %s: Permutation P length (%d) must match A nrows (%d) and Q length (%d) A ncols (%d)\n", who,
+        P->length, A->nrows, Q->length, A->ncols);
+  if (A->nrows == 0 || A->ncols == 0) {
+    for (rci_t i = 0; i < P->length; i++) P->values[i] = i;
+    for (rci_t i = 0; i < Q->length; i++) Q->values[i] = i;
+    return 0;
+  }
+  cudaStream_t s = current_stream();
+  DMat *dA = dmat_new(A->nrows, A->ncols, s);
+  upload(dA, A, s);
+  const int r = k_ple(dA, P->values, Q->values, pluq, s);
+  download(A, dA, s);
+  dmat_delete(dA, s);
+  M4B_CUDA(cudaStreamSynchronize(s));
+  return r;
+}
+rci_t mzd_ple(mzd_t *A, mzp_t *P, mzp_t *Q, int cutoff) {
+  (void)cutoff;
+  return host_ple(A, P, Q, false, "mzd_ple");
+}
+rci_t mzd_pluq(mzd_t *A, mzp_t *P, mzp_t *Q, int cutoff) {
+  (void)cutoff;
+  return host_ple(A, P, Q, true, "mzd_pluq");
+}
+
+// The swaps i <-> P[i] (i ascending, or descending for `reverse`) composed into one gather list:
+// position p of the result holds element src[p] of the input.
+static std::vector<int> compose_swaps(const mzp_t *P, int n, bool reverse) {
+  std::vector<int> src(n);
+  for (int i = 0; i < n; i++) src[i] = i;
+  const int len = std::min((int)P->length, n);
+  for (int t = 0; t < len; t++) {
+    const int i = reverse ? len - 1 - t : t, j = P->values[i];
+    if (j < 0 || j >= n) die("m4ri_b200: permutation entry %d out of range at %d\n", j, i);
+    std::swap(src[i], src[j]);
+  }
+  return src;
+}
+static void host_apply_p(mzd_t *A, const mzp_t *P, bool columns, bool reverse) {
+  if (A->nrows == 0 || A->ncols == 0) return;
+  const int n = columns ? A->ncols : A->nrows;
+  const std::vector<int> src = compose_swaps(P, n, reverse);
+  bool moved = false;
+  for (int i = 0; i < n && !moved; i++) moved = src[i] != i;
+  if (!moved) return;
+  cudaStream_t s = current_stream();
+  DMat *dA = dmat_new(A->nrows, A->ncols, s), *dO = dmat_new(A->nrows, A->ncols, s);
+  upload(dA, A, s);
+  int *dsrc;
+  M4B_CUDA(cudaMallocAsync(&dsrc, (size_t)n * sizeof(int), s));
+  M4B_CUDA(cudaMemcpyAsync(dsrc, src.data(), (size_t)n * sizeof(int), cudaMemcpyHostToDevice, s));
+  const long long work = (long long)A->nrows * dA->width;
+  if (columns)
+    permute_cols_kernel<<<cdiv(work, 256), 256, 0, s>>>(dO->d, dO->rowstride, dA->d, dA->rowstride, A->nrows, dA->width,
+                                                       A->ncols, dsrc);
+  else
+    permute_rows_kernel<<<cdiv(work, 256), 256, 0, s>>>(dO->d, dO->rowstride, dA->d, dA->rowstride, A->nrows, dA->width,
+                                                       dsrc);
+  M4B_LAUNCHED();
+  download(A, dO, s);
+  M4B_CUDA(cudaStreamSynchronize(s));
+  M4B_CUDA(cudaFreeAsync(dsrc, s));
+  dmat_delete(dA, s);
+  dmat_delete(dO, s);
+}
+// rows i <-> P[i], i = 0 .. len-1 in turn (mzp.rs:39); _trans: the same swaps in reverse order
+void mzd_apply_p_left(mzd_t *A, const mzp_t *P) { host_apply_p(A, P, false, false); }
+void mzd_apply_p_left_trans(mzd_t *A, const mzp_t *P) { host_apply_p(A, P, false, true); }
+// columns i <-> P[i]: _trans in turn (mzp.rs:48), plain in reverse order (mzp.rs:45)
+void mzd_apply_p_right_trans(mzd_t *A, const mzp_t *P) { host_apply_p(A, P, true, false); }
+void mzd_apply_p_right(mzd_t *A, const mzp_t *P) { host_apply_p(A, P, true, true); }
+
 static rci_t host_echelonize(mzd_t *A, const char *who) {
   (void)who;
   if (A->nrows == 0 || A->ncols == 0) return 0;

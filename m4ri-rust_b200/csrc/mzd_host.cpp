@@ -336,4 +336,48 @@ void mzd_randomize(mzd_t *A) {
   }
 }
 
+// ---- permutations (m4ri-sys/src/mzp.rs:14-51): M4RI's published mzp_t, host bookkeeping ----------
+// A window is its own small descriptor sharing the parent's values: it is released with
+// mzp_free_window, never mzp_free.
+mzp_t *mzp_init(rci_t length) {
+  if (length < 0) die("m4ri_b200: mzp_init: negative length\n");
+  mzp_t *P = (mzp_t *)malloc(sizeof(mzp_t));
+  if (!P) die("m4ri_b200: mzp_init: out of memory\n");
+  P->values = (rci_t *)malloc(sizeof(rci_t) * (size_t)(length > 0 ? length : 1));
+  if (!P->values) die("m4ri_b200: mzp_init: out of memory\n");
+  P->length = length;
+  for (rci_t i = 0; i < length; i++) P->values[i] = i;
+  return P;
+}
+void mzp_free(mzp_t *P) {
+  if (!P) return;
+  free(P->values);
+  free(P);
+}
+mzp_t *mzp_init_window(mzp_t *P, rci_t begin, rci_t end) {
+  if (begin < 0 || end < begin || end > P->length) die("m4ri_b200: mzp_init_window: bad range\n");
+  mzp_t *W = (mzp_t *)malloc(sizeof(mzp_t));
+  if (!W) die("m4ri_b200: mzp_init_window: out of memory\n");
+  W->values = P->values + begin;
+  W->length = end - begin;
+  return W;
+}
+void mzp_free_window(mzp_t *condemned) { free(condemned); }
+void Mzp_free_window(mzp_t *condemned) { free(condemned); }  // the spelling mzp.rs:29 declares
+mzp_t *mzp_copy(mzp_t *P, const mzp_t *Q) {
+  if (!P) P = mzp_init(Q->length);
+  else if (P->length < Q->length) die("m4ri_b200: mzp_copy: target is too short\n");
+  for (rci_t i = 0; i < Q->length; i++) P->values[i] = Q->values[i];
+  return P;
+}
+void mzp_set_ui(mzp_t *P, unsigned int value) {
+  (void)value;
+  for (rci_t i = 0; i < P->length; i++) P->values[i] = i;
+}
+void mzp_print(const mzp_t *P) {
+  printf("[ ");
+  for (rci_t i = 0; i < P->length; i++) printf("%d ", (int)P->values[i]);
+  printf("]");
+}
+
 }  // extern "C"

@@ -44,6 +44,7 @@ def lib():
             "oracle_freivalds": (i, [u64p, i, u64p, i, u64p, i, i, i, i, u64]),
             "oracle_max_threads": (i, []),
             "oracle_rref": (i, [u64p, i, i, i, i, u64p]),
+            "oracle_ple": (i, [u64p, i, i, i, u64p, u64p, i]),
         }
         for name, (res, args) in sig.items():
             f = getattr(_lib, name)
@@ -218,3 +219,55 @@ def solve_left(A, n, B, k):
     for t in range(r):
         X[piv[t]] = bits[t]
     return from_bits(X)
+
+
+def ple(M, n, pluq=False):
+    """PLE (or PLUQ) decomposition from the definition (m4ri-sys/src/ple.rs:35,65):
+    (packed [L \\ E], rank, P, Q) with P, Q LAPACK-style transposition lists."""
+    R = np.ascontiguousarray(M).copy()
+    m = R.shape[0]
+    P = np.zeros(max(1, m), dtype=np.int32)
+    Q = np.zeros(max(1, n), dtype=np.int32)
+    r = int(lib().oracle_ple(_p(R), R.shape[1], m, n, P.ctypes.data, Q.ctypes.data, int(pluq)))
+    return R, r, P[:m].copy(), Q[:n].copy()
+
+
+def ple_reconstruct(packed, n, r, P, Q, pluq=False):
+    """The matrix a packed PLE / PLUQ result stands for: unpack L (m x r, unit diagonal) and E
+    (r x n; for pluq U with the column swaps undone), check their shape constraints, and return
+    P * L * E as packed words. Raises AssertionError when the storage contract is violated."""
+    m = packed.shape[0]
+    bits = to_bits(packed, n).astype(np.uint8)
+    Q = [int(q) for q in Q]
+    P = [int(p) for p in P]
+    assert all(Q[i] < Q[i + 1] for i in range(r - 1)), "pivot columns must increase"
+    assert all(Q[i] >= i for i in range(r)) and all(Q[i] == i for i in range(r, n)), "Q beyond the rank is the identity"
+    assert all(P[i] >= i for i in range(m)), "transpositions point forward"
+    L = np.zeros((m, max(r, 1)), dtype=np.uint8)
+    E = np.zeros((max(r, 1), n), dtype=np.uint8)
+    for i in range(m):
+        k = min(i, r)
+        L[i, :k] = bits[i, :k]
+        if i < r:
+            L[i, i] = 1
+            start = i if pluq else Q[i]
+            E[i, start:] = bits[i, start:]
+            assert not bits[i, k:start].any(), f"row {i}: bits between L and the pivot column"
+        else:
+            assert not bits[i, k:].any(), f"row {i} (below the rank) holds more than multipliers"
+    if pluq:
+        for i in range(r):
+            assert E[i, i] == 1, f"U[{i}][{i}] must be 1"
+        for i in reversed(range(r)):  # undo the column swaps
+            if Q[i] != i:
+                E[:, [i, Q[i]]] = E[:, [Q[i], i]]
+    for i in range(r):
+        assert E[i, Q[i]] == 1 and not E[i, : Q[i]].any(), f"E row {i} must start at its pivot column"
+    if r == 0:
+        prod = np.zeros((m, n), dtype=np.uint8)
+    else:
+        prod = to_bits(mul_m4rm(from_bits(L[:, :r]), from_bits(E[:r]), r, n), n)
+    for i in reversed(range(m)):  # A = P (L E): undo the row swaps
+        if P[i] != i:
+            prod[[i, P[i]]] = prod[[P[i], i]]
+    return from_bits(prod)

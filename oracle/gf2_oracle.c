@@ -30,6 +30,7 @@
  *   C (^)= A*Bt^T with `clear`                          m4ri-sys/src/mzd.rs:154-168
  *   C (^)= v*A with `clear`                             m4ri-sys/src/mzd.rs:175-181
  *   transpose, add                                      m4ri-sys/src/mzd.rs:148,223
+ *   PLE / PLUQ decomposition (oracle_ple)               m4ri-sys/src/ple.rs:35,65
  *   echelon form / rank, inverse, solve (oracle_rref)   m4ri-sys/src/echelonform.rs:16,
  *                                                       brilliantrussian.rs:208, solve.rs:23
  *
@@ -421,6 +422,76 @@ int oracle_rref(word *M, int stride, int m, int n, int pivot_cols, int *pivcols)
     if (pivcols) pivcols[rank] = c;
     rank++;
   }
+  return rank;
+}
+
+/* ---- PLE / PLUQ decomposition from the definition (m4ri-sys/src/ple.rs:35-65) --------------
+ * Textbook elimination, column by column: the first row (at or below the current rank) with the
+ * bit set is swapped up (P[rank] = that row, LAPACK-style transposition), Q[rank] = the column;
+ * every lower row with the bit set gets the pivot row added on the columns RIGHT of the pivot
+ * column and keeps the bit itself — its multiplier, the entry of L. Afterwards L is compressed:
+ * column k of L moves from column Q[k] to column k (ple.rs:44-51: "L and S are stored in place
+ * over A"). Storage on return (r = rank): row i < r = [L[i][0..i) | zeros | E[i][Q[i]..n)], row
+ * i >= r = [L[i][0..r) | zeros]; P[i] = i and Q[i] = i beyond the rank. pluq != 0 additionally
+ * swaps columns i and Q[i] of the echelon rows for i = 0..r-1 in turn (on rows 0..i: the rows
+ * below hold L there), which makes the upper part U upper triangular (ple.rs:10-33). */
+static int row_bit(const word *row, int c) { return (int)((row[c / 64] >> (c % 64)) & 1); }
+static void row_put(word *row, int c, int v) {
+  row[c / 64] = (row[c / 64] & ~((word)1 << (c % 64))) | ((word)(v & 1) << (c % 64));
+}
+int oracle_ple(word *M, int stride, int m, int n, int *P, int *Q, int pluq) {
+  const int width = width_of(n);
+  int rank = 0;
+  for (int i = 0; i < m; i++) P[i] = i;
+  for (int c = 0; c < n; c++) Q[c] = c;
+  for (int c = 0; c < n && rank < m; c++) {
+    const int cw = c / 64, cb = c % 64;
+    const word bit = (word)1 << cb;
+    int p = -1;
+    for (int i = rank; i < m; i++)
+      if (M[(size_t)i * stride + cw] & bit) { p = i; break; }
+    if (p < 0) continue;
+    if (p != rank)
+      for (int w = 0; w < width; w++) {
+        word t = M[(size_t)p * stride + w];
+        M[(size_t)p * stride + w] = M[(size_t)rank * stride + w];
+        M[(size_t)rank * stride + w] = t;
+      }
+    P[rank] = p;
+    Q[rank] = c;
+    const word *pr = M + (size_t)rank * stride;
+    const word above = cb == 63 ? 0 : ~(word)0 << (cb + 1);
+#pragma omp parallel for schedule(static)
+    for (int i = rank + 1; i < m; i++) {
+      word *row = M + (size_t)i * stride;
+      if (!(row[cw] & bit)) continue;
+      row[cw] ^= pr[cw] & above;
+      for (int w = cw + 1; w < width; w++) row[w] ^= pr[w];
+    }
+    rank++;
+  }
+  /* compress L: ascending k never overwrites a multiplier that is still to be moved
+   * (destinations so far are < k <= Q[k]) */
+  for (int i = 0; i < m; i++) {
+    word *row = M + (size_t)i * stride;
+    const int kmax = i < rank ? i : rank;
+    for (int k = 0; k < kmax; k++) {
+      if (Q[k] == k) continue;
+      const int v = row_bit(row, Q[k]);
+      row_put(row, Q[k], 0);
+      row_put(row, k, v);
+    }
+  }
+  if (pluq)
+    for (int i = 0; i < rank; i++) {
+      if (Q[i] == i) continue;
+      for (int r = 0; r <= i; r++) {
+        word *row = M + (size_t)r * stride;
+        const int a = row_bit(row, i), b = row_bit(row, Q[i]);
+        row_put(row, i, b);
+        row_put(row, Q[i], a);
+      }
+    }
   return rank;
 }
 

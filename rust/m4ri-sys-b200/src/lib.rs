@@ -44,6 +44,14 @@ pub struct Mzd {
     pub rows: *mut *mut Word,
 }
 
+/// Permutation as a list of transpositions (`values[i] = j`: swap i and j, for i = 0, 1, ... in
+/// turn). `m4ri-sys/src/mzp.rs:9-12` keeps it opaque; this is M4RI's published two-field layout.
+#[repr(C)]
+pub struct Mzp {
+    pub values: *mut Rci,
+    pub length: Rci,
+}
+
 /// Opaque device-resident matrix (same packing, even row stride, lives in HBM).
 #[repr(C)]
 pub struct DMat {
@@ -95,6 +103,26 @@ extern "C" {
     /// Solves A X = B, X in the first ncols(A) rows of B; 0 on success, -1 when inconsistent.
     pub fn mzd_solve_left(a: *mut Mzd, b: *mut Mzd, cutoff: c_int, inconsistency_check: c_int) -> c_int;
 
+    // ---- PLE / PLUQ decomposition and permutations (m4ri-sys ple.rs, mzp.rs; csrc/elim.cu) ----
+    /// A = P L E in place, returns the rank; P has length nrows, Q length ncols (`ple.rs:65`).
+    pub fn mzd_ple(a: *mut Mzd, p: *mut Mzp, q: *mut Mzp, cutoff: c_int) -> Rci;
+    /// A = P L U Q in place, returns the rank (`ple.rs:35`).
+    pub fn mzd_pluq(a: *mut Mzd, p: *mut Mzp, q: *mut Mzp, cutoff: c_int) -> Rci;
+    pub fn mzp_init(length: Rci) -> *mut Mzp;
+    pub fn mzp_free(p: *mut Mzp);
+    /// (`mzp.rs:26` declares no return value; the window is the returned pointer, as in M4RI.)
+    pub fn mzp_init_window(p: *mut Mzp, begin: Rci, end: Rci) -> *mut Mzp;
+    pub fn mzp_free_window(condemned: *mut Mzp);
+    /// The spelling `mzp.rs:29` declares; same function.
+    pub fn Mzp_free_window(condemned: *mut Mzp);
+    pub fn mzp_copy(p: *mut Mzp, q: *const Mzp) -> *mut Mzp;
+    pub fn mzp_set_ui(p: *mut Mzp, value: c_uint);
+    pub fn mzd_apply_p_left(a: *mut Mzd, p: *const Mzp);
+    pub fn mzd_apply_p_left_trans(a: *mut Mzd, p: *const Mzp);
+    pub fn mzd_apply_p_right(a: *mut Mzd, p: *const Mzp);
+    pub fn mzd_apply_p_right_trans(a: *mut Mzd, p: *const Mzp);
+    pub fn mzp_print(p: *const Mzp);
+
     // ---- engine control ----
     pub fn m4ri_b200_set_algo(algo: c_int);
     pub fn m4ri_b200_get_algo() -> c_int;
@@ -130,6 +158,8 @@ extern "C" {
     pub fn m4ri_b200_dmul_v_batched(y: *mut DMat, a: *const DMat, x: *const DMat, clear: c_int);
     /// Reduced row echelon form of a device matrix in place; returns the rank.
     pub fn m4ri_b200_drref(w: *mut DMat, pivot_cols: c_int, pivot_columns: *mut c_int, max_pivots: c_int) -> c_int;
+    /// PLE (`pluq == 0`) or PLUQ of a device matrix in place; `p` (nrows) and `q` (ncols) are host arrays.
+    pub fn m4ri_b200_dple(w: *mut DMat, p: *mut Rci, q: *mut Rci, pluq: c_int) -> c_int;
     pub fn m4ri_b200_dtranspose(dst: *mut DMat, a: *const DMat);
     pub fn m4ri_b200_dadd(c: *mut DMat, a: *const DMat, b: *const DMat);
     pub fn m4ri_b200_dcopy(dst: *mut DMat, a: *const DMat);

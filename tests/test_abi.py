@@ -16,7 +16,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def declared_symbols():
     src = open(os.path.join(ROOT, "include", "m4ri_b200.h")).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    names = re.findall(r"\b(_?mzd_[a-z0-9_]+|m4ri_b200_[a-z0-9_]+)\s*\(", src)
+    names = re.findall(r"\b(_?mzd_[a-z0-9_]+|[mM]zp_[a-z0-9_]+|m4ri_b200_[a-z0-9_]+)\s*\(", src)
     return sorted(set(n for n in names if n not in ("m4ri_b200_dmat",)))
 
 
@@ -27,7 +27,8 @@ def test_every_declared_symbol_is_exported(m4):
     for must in ["mzd_mul", "mzd_addmul", "mzd_mul_m4rm", "mzd_addmul_m4rm", "_mzd_mul_m4rm",
                  "mzd_mul_naive", "mzd_addmul_naive", "_mzd_mul_naive", "_mzd_mul_va", "mzd_mul_v",
                  "mzd_init", "mzd_free", "mzd_transpose", "mzd_copy", "mzd_equal", "mzd_add",
-                 "mzd_randomize", "mzd_set_ui"]:
+                 "mzd_randomize", "mzd_set_ui", "mzd_ple", "mzd_pluq", "mzp_init", "mzp_free",
+                 "mzd_apply_p_left", "mzd_apply_p_right_trans", "Mzp_free_window"]:
         assert must in names
     for n in names:
         assert hasattr(L, n), f"{n} declared in include/m4ri_b200.h but not exported"

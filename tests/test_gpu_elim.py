@@ -180,3 +180,121 @@ def test_device_rref_large(gpu, m4):
         assert L.m4ri_b200_dis_zero(P.h) == 1
         return
     pytest.fail("no invertible 8192 x 8192 matrix among the seeds")
+
+
+# ---- PLE / PLUQ (m4ri-sys/src/ple.rs:35,65) and the permutation calls (mzp.rs) -----------------
+def _perm_values(P):
+    return [int(P.contents.values[i]) for i in range(P.contents.length)]
+
+
+def _ple_cases(orc):
+    for (m, n) in SHAPES + [(4100, 700), (700, 4100), (2500, 2500)]:
+        for kind in ("random", "lowrank", "zero_cols"):
+            if kind == "random":
+                A = orc.random(m, n, 21 + m)
+            elif kind == "lowrank":
+                A = low_rank(orc, m, n, max(1, min(m, n) // 3), 9 + n)
+            else:
+                A = orc.random(m, n, 13)
+                A[:, : orc.width(n) // 2] = 0
+                A[m // 2:] = A[: m - m // 2]
+            yield m, n, kind, A
+
+
+@pytest.mark.parametrize("entry", ["mzd_ple", "mzd_pluq"])
+def test_ple_pluq_defining_identity(gpu, m4, orc, entry):
+    """The decomposition is not unique (the pivot ROW is a free choice), so the check is its
+    defining identity through the storage contract of include/m4ri_b200.h: unpack L and E (or U),
+    verify their shapes, and P * L * E must be the input bit for bit; the rank and the pivot
+    columns Q (the column rank profile, which IS unique) must equal the oracle's."""
+    L = m4.lib()
+    pluq = entry == "mzd_pluq"
+    for m, n, kind, A in _ple_cases(orc):
+        w = orc.width(n)
+        _, r_want, Pw, Qw = orc.ple(A, n, pluq)
+        a = host(m4, A, n)
+        P, Q = L.mzp_init(m), L.mzp_init(n)
+        r = getattr(L, entry)(a, P, Q, 0)
+        assert r == r_want, (entry, m, n, kind, r, r_want)
+        Pv, Qv = _perm_values(P), _perm_values(Q)
+        assert Qv == [int(q) for q in Qw], (entry, m, n, kind)
+        got = m4.mzd_words(a)
+        assert not got[:, w:].any()
+        back = orc.ple_reconstruct(np.ascontiguousarray(got), n, r, Pv, Qv, pluq)
+        assert (back[:, :w] == A[:, :w]).all(), (entry, m, n, kind)
+        # same input, same answer (pivot rows are chosen deterministically)
+        a2 = host(m4, A, n)
+        P2, Q2 = L.mzp_init(m), L.mzp_init(n)
+        assert getattr(L, entry)(a2, P2, Q2, 0) == r and _perm_values(P2) == Pv
+        assert L.mzd_equal(a, a2) == 1
+        for q in (P, Q, P2, Q2):
+            L.mzp_free(q)
+        L.mzd_free(a)
+        L.mzd_free(a2)
+
+
+def test_ple_through_the_products(gpu, m4, orc):
+    """mzd_apply_p_left(A, P) == L * E with the product done by mzd_mul on the GPU; full rank
+    square input, where PLE is the LU decomposition with row pivoting."""
+    L = m4.lib()
+    n = 1536
+    for seed in range(40):
+        A = orc.random(n, n, 500 + seed)
+        if orc.rref(A, n)[1] == n:
+            break
+    a, lu = host(m4, A, n), host(m4, A, n)
+    P, Q = L.mzp_init(n), L.mzp_init(n)
+    assert L.mzd_ple(lu, P, Q, 0) == n and _perm_values(Q) == list(range(n))
+    packed = orc.to_bits(np.ascontiguousarray(m4.mzd_words(lu)), n)
+    lower = np.tril(packed, -1) + np.eye(n, dtype=np.uint8)
+    upper = np.triu(packed)
+    l, u = host(m4, orc.from_bits(lower), n), host(m4, orc.from_bits(upper), n)
+    prod = L.mzd_mul(None, l, u, 0)
+    L.mzd_apply_p_left(a, P)
+    assert L.mzd_equal(prod, a) == 1
+    L.mzd_apply_p_left_trans(a, P)  # and back
+    assert (m4.mzd_words(a)[:, : orc.width(n)] == A[:, : orc.width(n)]).all()
+    for q in (a, lu, l, u, prod):
+        L.mzd_free(q)
+    L.mzp_free(P)
+    L.mzp_free(Q)
+
+
+def test_apply_permutations(gpu, m4, orc):
+    L = m4.lib()
+    rng = np.random.default_rng(5)
+    for (m, n) in [(1, 1), (7, 5), (64, 130), (300, 257), (1000, 70)]:
+        A = orc.random(m, n, 31 + n)
+        bits = orc.to_bits(A, n)
+        for which, length in (("left", m), ("left_trans", m), ("right", n), ("right_trans", n)):
+            P = L.mzp_init(length)
+            vals = [int(rng.integers(i, length)) for i in range(length)]
+            for i, v in enumerate(vals):
+                P.contents.values[i] = v
+            want = bits.copy()
+            order = range(length) if which in ("left", "right_trans") else reversed(range(length))
+            for i in order:
+                if which.startswith("left"):
+                    want[[i, vals[i]]] = want[[vals[i], i]]
+                else:
+                    want[:, [i, vals[i]]] = want[:, [vals[i], i]]
+            a = host(m4, A, n)
+            getattr(L, "mzd_apply_p_" + which)(a, P)
+            got = orc.to_bits(np.ascontiguousarray(m4.mzd_words(a)), n)
+            assert (got == want).all(), (which, m, n)
+            L.mzd_free(a)
+            L.mzp_free(P)
+    # windows and copies of permutations (host bookkeeping)
+    P = L.mzp_init(10)
+    assert _perm_values(P) == list(range(10))
+    W = L.mzp_init_window(P, 3, 8)
+    assert W.contents.length == 5
+    W.contents.values[0] = 7
+    assert P.contents.values[3] == 7
+    C = L.mzp_copy(None, P)
+    assert _perm_values(C) == _perm_values(P)
+    L.mzp_set_ui(P, 1)
+    assert _perm_values(P) == list(range(10))
+    L.Mzp_free_window(W)
+    L.mzp_free(C)
+    L.mzp_free(P)

@@ -171,3 +171,29 @@ def test_strassen_strategy_matches_definition(orc, m, k, n, cutoff):
     if n % 64:
         assert not (got[:, w - 1] >> np.uint64(n % 64)).any()
     assert not got[:, w:].any()
+
+
+def test_ple_restatement_satisfies_its_definition(orc):
+    """oracle_ple (m4ri-sys/src/ple.rs:35,65): P * L * E reproduces the input through the storage
+    contract, the rank and the pivot columns agree with the Gauss-Jordan restatement."""
+    for (m, n, kind) in [(1, 1, "r"), (5, 7, "r"), (64, 64, "r"), (100, 300, "r"), (300, 100, "r"),
+                         (200, 200, "low"), (130, 257, "zc"), (65, 63, "r")]:
+        if kind == "r":
+            A = orc.random(m, n, 3 + m)
+        elif kind == "low":
+            A = orc.mul_m4rm(orc.random(m, 20, 1), orc.random(20, n, 2), 20, n)
+        else:
+            A = orc.random(m, n, 7)
+            A[:, : orc.width(n) // 2] = 0
+            A[m // 2:] = A[: m - m // 2]
+        _, rank, piv = orc.rref(A, n)
+        for pluq in (False, True):
+            R, r, P, Q = orc.ple(A, n, pluq)
+            assert r == rank and list(Q[:r]) == list(piv)
+            back = orc.ple_reconstruct(R, n, r, P, Q, pluq)
+            assert (back[:, : orc.width(n)] == A[:, : orc.width(n)]).all(), (m, n, kind, pluq)
+    # identity: no swaps, L = I, E = I
+    n = 70
+    I = orc.from_bits(np.eye(n, dtype=np.uint8))
+    R, r, P, Q = orc.ple(I, n)
+    assert r == n and list(P) == list(range(n)) and list(Q) == list(range(n)) and (R == I).all()

@@ -28,7 +28,7 @@ def rust_decls():
 def header_decls():
     src = re.sub(r"/\*.*?\*/", "", open(HEADER).read(), flags=re.S)
     return {m.group(1): _args(m.group(2))
-            for m in re.finditer(r"\b(_?mzd_\w+|m4ri_b200_\w+)\s*\(([^;{]*?)\)\s*;", src, re.S)}
+            for m in re.finditer(r"\b(_?mzd_\w+|[mM]zp_\w+|m4ri_b200_\w+)\s*\(([^;{]*?)\)\s*;", src, re.S)}
 
 
 def test_every_rust_declaration_is_in_the_header_with_the_same_arity():
@@ -41,6 +41,11 @@ def test_every_rust_declaration_is_in_the_header_with_the_same_arity():
     for name in ("mzd_mul", "mzd_addmul", "mzd_mul_m4rm", "mzd_addmul_m4rm", "_mzd_mul_m4rm", "mzd_mul_naive",
                  "mzd_addmul_naive", "_mzd_mul_naive", "_mzd_mul_va", "mzd_mul_v", "mzd_transpose", "mzd_add",
                  "mzd_init", "mzd_free", "mzd_copy", "mzd_equal", "mzd_randomize", "mzd_set_ui"):
+        assert name in rust
+    # and the decomposition surface of m4ri-sys/src/ple.rs and mzp.rs
+    for name in ("mzd_ple", "mzd_pluq", "mzp_init", "mzp_free", "mzp_init_window", "Mzp_free_window", "mzp_copy",
+                 "mzp_set_ui", "mzd_apply_p_left", "mzd_apply_p_left_trans", "mzd_apply_p_right",
+                 "mzd_apply_p_right_trans", "mzp_print"):
         assert name in rust
 
 
