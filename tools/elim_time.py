@@ -20,6 +20,39 @@ for n in [int(x) for x in sys.argv[1:]] or [1024, 4096, 8192, 16384, 32768]:
         rec["rref_device_ms"] = (time.perf_counter() - t0) * 1e3
         rec["rref_launches"] = m4.launch_count() - l0
     rec["rank"] = r
+    # PLE decomposition, device-resident (P, Q come back as host arrays), checked at the end by
+    # the GPU's own product: rows of the input permuted by P must equal L * E
+    Pv, Qv = (ctypes.c_int * n)(), (ctypes.c_int * n)()
+    for rep in range(2):
+        W.fill_random(7)
+        L.m4ri_b200_synchronize()
+        t0 = time.perf_counter()
+        rp = L.m4ri_b200_dple(W.h, Pv, Qv, 0)
+        L.m4ri_b200_synchronize()
+        rec["ple_device_ms"] = (time.perf_counter() - t0) * 1e3
+    rec["ple_rank"] = rp
+    if n <= 16384:
+        packed = oracle.to_bits(np.ascontiguousarray(m4.mzd_words(W.to_host())), n)
+        lower = np.zeros_like(packed)
+        upper = np.zeros_like(packed)
+        q = list(Qv)
+        for i in range(n):
+            k = min(i, rp)
+            lower[i, :k] = packed[i, :k]
+            if i < rp:
+                lower[i, i] = 1
+                upper[i, q[i]:] = packed[i, q[i]:]
+        l, u = m4.mzd_from_words(oracle.from_bits(lower), n), m4.mzd_from_words(oracle.from_bits(upper), n)
+        prod = L.mzd_mul(None, l, u, 0)
+        a0 = W.fill_random(7).to_host()
+        P = L.mzp_init(n)
+        for i in range(n):
+            P.contents.values[i] = Pv[i]
+        L.mzd_apply_p_left(a0, P)
+        rec["ple_identity_holds"] = bool(L.mzd_equal(prod, a0) == 1)
+        for x in (l, u, prod, a0):
+            L.mzd_free(x)
+        L.mzp_free(P)
     # inversion through the host ABI (H2D + [A|I] elimination + D2H)
     a = W.fill_random(7).to_host()
     for rep in range(2):
