@@ -449,6 +449,17 @@ static int strassen_levels(int m, int k, int n, int algo, int cutoff) {
       mm /= 2, kk /= 2, nn /= 2;
       L++;
     }
+    // The LAST level is cheaper than the upper ones when it runs fused (operand sums in two
+    // launches, the seven products as one persistent launch: no wave tail per product), so it
+    // pays on smaller leaves: volume of an 8192-cube with a contraction of at least 8192 bits
+    // (profiles/r2p_rect_sweep.jsonl: 16384^3 1.079 -> 1.038 ms, 8192 x 32768 x 16384
+    // 1.038 -> 0.998, 16384 x 32768 x 16384 2.067 -> 1.960; no gain at 8192 x 32768 x 8192 or
+    // with leaves of k = 4096; a second level on top never paid).
+    if (L == 0 && m % 512 == 0 && k % 512 == 0 && n % 512 == 0 && m / 2 >= 4096 && n / 2 >= 4096 && k / 2 >= 8192 &&
+        (double)(m / 2) * (double)(k / 2) * (double)(n / 2) >= 8192.0 * 8192.0 * 8192.0 &&
+        !getenv("M4RI_B200_NO_FUSED_STRASSEN") &&
+        (mma_variant() == M4RI_B200_MMA_FP4_S256_PAIR || mma_variant() == M4RI_B200_MMA_FP4_S256_SINGLE))
+      L = 1;
     return L;
   }
   if (cutoff <= 0) cutoff = algo == M4RI_B200_ALGO_MMA ? 16384 : 32768;
@@ -572,7 +583,8 @@ static const size_t PIPELINE_MIN_BYTES = (size_t)24 << 20;
 // 2 % (profiles/r1k_e2e_sweep.jsonl: 8x1 12.85, 8x4 11.15, 4x4 10.98, 8x8 13.2, 16x8 14.0 ms).
 static void plan_pipeline(rci_t m, rci_t k, rci_t n, int clear, int *best_na, int *best_nb) {
   static const int cand[] = {1, 2, 3, 4, 6, 8, 12, 16};
-  const double pcie = 55e9 * 1e-3 /* bytes per ms */, wave = k * 1.31e-6, launch = 0.008;
+  // constants fitted to profiles/r2p_e2e_sweep*.jsonl (n = 12288 ... 65536, rms error 4 %)
+  const double pcie = 50e9 * 1e-3 /* bytes per ms */, wave = k * 1.14e-6 /* mma6 */, launch = 0.015;
   double best = 1e300;
   *best_na = *best_nb = 1;
   for (int ca : cand)
@@ -597,7 +609,16 @@ static void plan_pipeline(rci_t m, rci_t k, rci_t n, int clear, int *best_na, in
         for (int i = 0; i < na; i++) {
           const double ready = arr_a[i] > arr_b[j] ? arr_a[i] : arr_b[j];
           const double tiles = ceil(rows_of(i) / 256) * ceil(cols_of(j) / 256);
-          t = (t > ready ? t : ready) + ceil(tiles / 74) * wave + launch;
+          // Strassen levels of the piece: an upper-criterion level saves ~10 % (7.62 vs 8.27 ms at
+          // n = 32768), the relaxed fused level ~4 % (profiles/r2p_rect_sweep.jsonl)
+          const int pm = (int)rows_of(i), pn = (int)cols_of(j);
+          const int lv = (pm % 512 || pn % 512 || k % 512) ? 0 : strassen_levels(pm, k, pn, M4RI_B200_ALGO_MMA, 0);
+          double f = 1.0;
+          if (lv > 0) {
+            const double leaf = (double)(pm >> lv) * (double)(k >> lv) * (double)(pn >> lv);
+            f = leaf >= 16384.0 * 16384.0 * 16384.0 ? pow(0.90, lv) : 0.96;
+          }
+          t = (t > ready ? t : ready) + ceil(tiles / 74) * wave * f + launch;
         }
       t += rows_of(na - 1) * cols_of(nb - 1) / 8 / pcie;  // the last block's way home
       if (t < best) best = t, *best_na = na, *best_nb = nb;

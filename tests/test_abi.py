@@ -131,7 +131,8 @@ def test_product_without_gpu_dies_loudly(m4):
 
 def test_pipeline_plan_is_host_arithmetic():
     """m4ri_b200_pipeline_plan needs no device: the block plan of the host-ABI pipeline for the
-    benchmark shape is the one measured fastest (profiles/r1k_e2e_sweep.jsonl), and every plan
+    benchmark shapes is the one measured fastest (profiles/r2p_e2e_sweep*.jsonl; at n = 65536 within
+    0.5 % of it), and every plan
     has at least one block each way."""
     import ctypes
     import m4ri_rust_b200 as m4
@@ -140,9 +141,10 @@ def test_pipeline_plan_is_host_arithmetic():
         a, b = ctypes.c_int(), ctypes.c_int()
         L.m4ri_b200_pipeline_plan(m, k, n, clear, ctypes.byref(a), ctypes.byref(b))
         return a.value, b.value
-    assert plan(32768, 32768, 32768) == (4, 4)
-    assert plan(16384, 16384, 16384) == (4, 2)
+    assert plan(32768, 32768, 32768) == (16, 2)
+    assert plan(16384, 16384, 16384) == (2, 4)
     assert plan(12288, 12288, 12288) == (2, 4)
+    assert plan(65536, 65536, 65536) == (8, 4)
     for shape in [(1, 1, 1), (300, 70000, 129), (1 << 20, 512, 512), (8192, 65536, 65536), (5000, 20000, 9000)]:
         a, b = plan(*shape)
         assert 1 <= a <= 16 and 1 <= b <= 16

@@ -18,8 +18,8 @@ ref = dC.checksum()
 import ctypes
 pa, pb = ctypes.c_int(), ctypes.c_int()
 L.m4ri_b200_pipeline_plan(n, n, n, 1, ctypes.byref(pa), ctypes.byref(pb))
-plans = [(0, 0)] + ([(8, 1), (8, 2), (8, 4), (8, 8), (4, 4), (16, 4), (4, 8), (16, 8), (12, 6)] if n == 32768 else
-                    [(1, 1), (2, 2), (4, 2), (4, 4), (8, 4), (2, 4), (1, 6), (1, 4)])
+plans = [(0, 0)] + ([(8, 1), (8, 2), (8, 4), (8, 8), (4, 4), (16, 4), (4, 8), (16, 8), (12, 6), (4, 2), (6, 3), (16, 2), (12, 2), (16, 3), (16, 1), (12, 3)] if n == 32768 else
+                    [(1, 1), (2, 2), (4, 2), (4, 4), (8, 4), (2, 4), (1, 6), (1, 4), (1, 8), (2, 8), (6, 6), (8, 8)])
 for rows, cols in plans:
     if rows == 0:
         os.environ.pop("M4RI_B200_PIPE_ROWS", None), os.environ.pop("M4RI_B200_PIPE_COLS", None)
