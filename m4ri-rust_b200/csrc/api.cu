@@ -439,27 +439,30 @@ static int strassen_levels(int m, int k, int n, int algo, int cutoff) {
   // tuned on B200 (profiles/r1g_size_sweep_fp4.jsonl): one level pays from n = 32768 up on the
   // tensor path (leaves of 16384), never on the Four-Russians path below n = 65536
   if (cutoff <= 0 && algo == M4RI_B200_ALGO_MMA) {
-    // the leaf kernel's efficiency depends on the leaf's volume (tiles x k), not on its smallest
-    // side: a level pays while the leaves keep the volume of a 16384-cube and whole tiles —
-    // e.g. the 8192 x 65536 x 65536 row-block of the 8-GPU product (leaves 4096 x 32768 x 32768)
-    long long mm = m, kk = k, nn = n;
+    // Measured rule (profiles/r2p_rect_sweep*.jsonl, r2p_size_sweep.jsonl). What decides whether a
+    // level pays is the LEAF the recursion ends in: the tensor kernel's per-tile cost is fixed, so
+    // its efficiency follows the leaf's contraction length (0.81 / 0.87 / 0.90 of the pipe at
+    // k = 8192 / 16384 / 32768) and it needs whole 256-row tiles over all SMs.
+    //   one level (the fused one: operand sums in two launches, the seven products one persistent
+    //   launch): leaf k >= 8192, sides >= 4096, volume >= 8192^3 — 16384^3 1.079 -> 1.038 ms,
+    //   8192 x 32768 x 16384 1.038 -> 0.998; no gain at 8192 x 32768 x 8192 or leaf k = 4096;
+    //   more levels (unfused Winograd schedule above the fused one): leaf k >= 16384, sides >= 4096,
+    //   volume >= 4096 x 16384 x 16384 — 65536^3 63.6 -> 57.9 ms, the 2-GPU row-block
+    //   32768 x 65536 x 65536 31.5 -> 29.3, the 4-GPU one 15.9 -> 15.1; a second level with leaves
+    //   of k = 8192 loses (32768^3: 7.62 -> 7.81).
+    const bool fused = !getenv("M4RI_B200_NO_FUSED_STRASSEN") &&
+                       (mma_variant() == M4RI_B200_MMA_FP4_S256_PAIR || mma_variant() == M4RI_B200_MMA_FP4_S256_SINGLE);
+    auto leaf_ok = [&](int L) {
+      if ((m % (256 << L)) || (k % (256 << L)) || (n % (256 << L))) return false;
+      const long long lm = m >> L, lk = k >> L, ln = n >> L;
+      if (lm < 4096 || ln < 4096) return false;
+      const double vol = (double)lm * (double)lk * (double)ln;
+      if (!fused) return lk >= 4096 && vol >= 16384.0 * 16384.0 * 16384.0;  // the r1 rule (other variants)
+      if (L == 1) return lk >= 8192 && vol >= 8192.0 * 8192.0 * 8192.0;
+      return lk >= 16384 && vol >= 4096.0 * 16384.0 * 16384.0;
+    };
     int L = 0;
-    while (L < 4 && mm / 2 >= 4096 && kk / 2 >= 4096 && nn / 2 >= 4096 &&
-           (double)(mm / 2) * (double)(kk / 2) * (double)(nn / 2) >= 16384.0 * 16384.0 * 16384.0) {
-      mm /= 2, kk /= 2, nn /= 2;
-      L++;
-    }
-    // The LAST level is cheaper than the upper ones when it runs fused (operand sums in two
-    // launches, the seven products as one persistent launch: no wave tail per product), so it
-    // pays on smaller leaves: volume of an 8192-cube with a contraction of at least 8192 bits
-    // (profiles/r2p_rect_sweep.jsonl: 16384^3 1.079 -> 1.038 ms, 8192 x 32768 x 16384
-    // 1.038 -> 0.998, 16384 x 32768 x 16384 2.067 -> 1.960; no gain at 8192 x 32768 x 8192 or
-    // with leaves of k = 4096; a second level on top never paid).
-    if (L == 0 && m % 512 == 0 && k % 512 == 0 && n % 512 == 0 && m / 2 >= 4096 && n / 2 >= 4096 && k / 2 >= 8192 &&
-        (double)(m / 2) * (double)(k / 2) * (double)(n / 2) >= 8192.0 * 8192.0 * 8192.0 &&
-        !getenv("M4RI_B200_NO_FUSED_STRASSEN") &&
-        (mma_variant() == M4RI_B200_MMA_FP4_S256_PAIR || mma_variant() == M4RI_B200_MMA_FP4_S256_SINGLE))
-      L = 1;
+    while (L < 4 && leaf_ok(L + 1)) L++;
     return L;
   }
   if (cutoff <= 0) cutoff = algo == M4RI_B200_ALGO_MMA ? 16384 : 32768;
@@ -616,7 +619,7 @@ static void plan_pipeline(rci_t m, rci_t k, rci_t n, int clear, int *best_na, in
           double f = 1.0;
           if (lv > 0) {
             const double leaf = (double)(pm >> lv) * (double)(k >> lv) * (double)(pn >> lv);
-            f = leaf >= 16384.0 * 16384.0 * 16384.0 ? pow(0.90, lv) : 0.96;
+            f = lv >= 2 ? 0.85 * pow(0.93, lv - 2) : (leaf >= 16384.0 * 16384.0 * 16384.0 ? 0.905 : 0.96);
           }
           t = (t > ready ? t : ready) + ceil(tiles / 74) * wave * f + launch;
         }
