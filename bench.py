@@ -498,6 +498,10 @@ def main():
             L.m4ri_b200_synchronize()
             L.m4ri_b200_set_algo(algo)
             L.m4ri_b200_set_devices(world)
+            # as a host without torch calls it: the library's own stream (the steps above ran on
+            # torch's current stream — the legacy default stream — for the CUDA-event timing)
+            if os.environ.get("BENCH_E2E_TORCH_STREAM") != "1":
+                L.m4ri_b200_use_own_stream()
             e2e_steps = max(3, min(args.steps, 5))
             for i in range(2):
                 L.mzd_free(L.mzd_mul(None, hA, hB, 0))
@@ -509,6 +513,7 @@ def main():
             e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
             L.m4ri_b200_set_devices(1)
             L.m4ri_b200_set_algo(0)
+            L.m4ri_b200_set_stream(ctypes.c_void_p(stream.cuda_stream))
             # the rows this rank also computed device-resident must be the same words
             mine = m4.mzd_words(hC)[r0:r0 + rows]
             step_ = max(1, rows // 64)

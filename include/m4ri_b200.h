@@ -206,6 +206,8 @@ void m4ri_b200_host_cache_trim(void);
 void m4ri_b200_host_cache_stats(unsigned long long *hits, unsigned long long *misses,
                                 unsigned long long *bytes_held);
 void m4ri_b200_set_stream(void *stream);
+/* Back to the calling thread's own non-blocking stream (the default before any set_stream). */
+void m4ri_b200_use_own_stream(void);
 void m4ri_b200_synchronize(void);
 /* Count of kernels the library launched since process start (bench: gpu_launches). */
 unsigned long long m4ri_b200_launch_count(void);
@@ -258,7 +260,7 @@ void m4ri_b200_dfill_random(m4ri_b200_dmat_t *M, uint64_t seed);
  * of one big matrix generate exactly their own rows). */
 void m4ri_b200_dfill_random_at(m4ri_b200_dmat_t *M, uint64_t seed, uint64_t first_index);
 /* Per-kernel device timing of the dominant product kernel (CUDA events on the
- * launching stream). reset() enables recording and clears it; ms() synchronises and
+ * launching stream). reset() enables recording and clears it; ms() ends the recording, synchronises and
  * returns the summed duration of the recorded launches; count() their number;
  * name() the kernel they belong to. */
 void m4ri_b200_timing_reset(void);

@@ -99,7 +99,7 @@ def lib():
         "m4ri_b200_set_mma_variant": (None, [i]),
         "m4ri_b200_device_count": (i, []),
         "m4ri_b200_device_info": (i, [ctypes.c_char_p, i, ctypes.POINTER(i), ctypes.POINTER(i), ctypes.POINTER(i)]),
-        "m4ri_b200_set_stream": (None, [vp]), "m4ri_b200_synchronize": (None, []),
+        "m4ri_b200_set_stream": (None, [vp]), "m4ri_b200_use_own_stream": (None, []), "m4ri_b200_synchronize": (None, []),
         "m4ri_b200_launch_count": (ctypes.c_ulonglong, []),
         "m4ri_b200_version": (ctypes.c_char_p, []),
         "m4ri_b200_dmat_init": (vp, [i, i]), "m4ri_b200_dmat_wrap": (vp, [vp, i, i, i]),

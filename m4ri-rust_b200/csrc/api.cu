@@ -1255,6 +1255,10 @@ void m4ri_b200_set_stream(void *stream) {
   t_user_stream = (cudaStream_t)stream;
   t_use_user_stream = true;
 }
+void m4ri_b200_use_own_stream(void) {
+  t_user_stream = nullptr;
+  t_use_user_stream = false;
+}
 void m4ri_b200_synchronize(void) { M4B_CUDA(cudaStreamSynchronize(current_stream())); }
 unsigned long long m4ri_b200_launch_count(void) { return g_launches.load(); }
 const char *m4ri_b200_version(void) { return "m4ri_b200 0.1 (sm_100a)"; }
@@ -1347,6 +1351,7 @@ void m4ri_b200_timing_reset(void) {
 }
 double m4ri_b200_timing_ms(void) {
   std::lock_guard<std::mutex> g(g_tmu);
+  g_timing_on = false;  // the window ends here: later launches are not recorded (nor slowed down)
   double tot = 0;
   for (auto &p : g_tev) {
     M4B_CUDA(cudaEventSynchronize(p.second));

@@ -134,6 +134,7 @@ extern "C" {
     pub fn m4ri_b200_device_info(name: *mut c_char, name_len: c_int, sm_count: *mut c_int,
                                  cc_major: *mut c_int, cc_minor: *mut c_int) -> c_int;
     pub fn m4ri_b200_set_stream(stream: *mut c_void);
+    pub fn m4ri_b200_use_own_stream();
     pub fn m4ri_b200_synchronize();
     pub fn m4ri_b200_launch_count() -> c_ulonglong;
     pub fn m4ri_b200_version() -> *const c_char;
