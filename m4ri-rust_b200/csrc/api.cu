@@ -578,6 +578,41 @@ static int pipeline_parts(const char *env, int dflt) {  // experiment hook: chun
 }
 static const size_t PIPELINE_MIN_BYTES = (size_t)24 << 20;
 
+// Time factor of a pipeline piece for the Strassen levels it takes (profiles/r2p_rect_sweep*.jsonl):
+// the small fused level saves ~4 %, a level on big leaves ~9.5 %, two levels ~15 %.
+static double piece_level_factor(int pm, int k, int pn) {
+  const int lv = (pm % 512 || pn % 512 || k % 512) ? 0 : strassen_levels(pm, k, pn, M4RI_B200_ALGO_MMA, 0);
+  if (lv <= 0) return 1.0;
+  const double leaf = (double)(pm >> lv) * (double)(k >> lv) * (double)(pn >> lv);
+  return lv >= 2 ? 0.85 * pow(0.93, lv - 2) : (leaf >= 16384.0 * 16384.0 * 16384.0 ? 0.905 : 0.96);
+}
+
+// Row chunks of a GPU's block when its Bt is already complete on the device (the N-GPU single
+// call): chunks of A go up, (chunk x k x n) products run, chunks of C go home. Few chunks keep the
+// Strassen levels of a big product, many chunks hide more of the first upload and the last download.
+static int plan_row_chunks(rci_t m, rci_t k, rci_t n, int clear) {
+  static const int cand[] = {1, 2, 3, 4, 6, 8, 12, 16};
+  // (contractions longer than the kernel's 32768-bit chunk take accumulating passes: +7 %)
+  const double pcie = 50e9 * 1e-3, wave = k * 1.14e-6 * (k > 32768 ? 1.07 : 1.0), launch = 0.015;
+  double best = 1e300;
+  int best_na = 1;
+  for (int ca : cand) {
+    const rci_t per = ((m + ca - 1) / ca + 255) / 256 * 256;
+    const int na = (m + per - 1) / per;
+    double up = 0, t = 0, last = 0;
+    for (int i = 0; i < na; i++) {
+      const double rows = (double)((i + 1) * (long long)per < m ? per : m - i * (long long)per);
+      up += rows * (k + (clear ? 0 : n)) / 8 / pcie;
+      const double tiles = ceil(rows / 256) * ceil((double)n / 256);
+      t = (t > up ? t : up) + ceil(tiles / 74) * wave * piece_level_factor((int)rows, k, n) + launch;
+      last = rows;
+    }
+    t += last * n / 8 / pcie;
+    if (t < best) best = t, best_na = na;
+  }
+  return best_na;
+}
+
 // Block plan of the pipeline below: (row-chunks of A) x (column blocks of B), chosen by replaying
 // the schedule on a cost model — PCIe at 55 GB/s each way, a product = ceil(tiles / 74 CTA pairs)
 // waves of 256 x 256 x k tiles at the measured 7.4 Pop/s (1.31 ns per wave per bit of k) + 8 us
@@ -587,7 +622,7 @@ static const size_t PIPELINE_MIN_BYTES = (size_t)24 << 20;
 static void plan_pipeline(rci_t m, rci_t k, rci_t n, int clear, int *best_na, int *best_nb) {
   static const int cand[] = {1, 2, 3, 4, 6, 8, 12, 16};
   // constants fitted to profiles/r2p_e2e_sweep*.jsonl (n = 12288 ... 65536, rms error 4 %)
-  const double pcie = 50e9 * 1e-3 /* bytes per ms */, wave = k * 1.14e-6 /* mma6 */, launch = 0.015;
+  const double pcie = 50e9 * 1e-3 /* bytes per ms */, wave = k * 1.14e-6 /* mma6 */ * (k > 32768 ? 1.07 : 1.0), launch = 0.015;
   double best = 1e300;
   *best_na = *best_nb = 1;
   for (int ca : cand)
@@ -612,15 +647,7 @@ static void plan_pipeline(rci_t m, rci_t k, rci_t n, int clear, int *best_na, in
         for (int i = 0; i < na; i++) {
           const double ready = arr_a[i] > arr_b[j] ? arr_a[i] : arr_b[j];
           const double tiles = ceil(rows_of(i) / 256) * ceil(cols_of(j) / 256);
-          // Strassen levels of the piece: an upper-criterion level saves ~10 % (7.62 vs 8.27 ms at
-          // n = 32768), the relaxed fused level ~4 % (profiles/r2p_rect_sweep.jsonl)
-          const int pm = (int)rows_of(i), pn = (int)cols_of(j);
-          const int lv = (pm % 512 || pn % 512 || k % 512) ? 0 : strassen_levels(pm, k, pn, M4RI_B200_ALGO_MMA, 0);
-          double f = 1.0;
-          if (lv > 0) {
-            const double leaf = (double)(pm >> lv) * (double)(k >> lv) * (double)(pn >> lv);
-            f = lv >= 2 ? 0.85 * pow(0.93, lv - 2) : (leaf >= 16384.0 * 16384.0 * 16384.0 ? 0.905 : 0.96);
-          }
+          const double f = piece_level_factor((int)rows_of(i), k, (int)cols_of(j));
           t = (t > ready ? t : ready) + ceil(tiles / 74) * wave * f + launch;
         }
       t += rows_of(na - 1) * cols_of(nb - 1) / 8 / pcie;  // the last block's way home
@@ -899,8 +926,7 @@ static void multi_worker(MultiJob *J, int g) {
     }
   }
   M4B_CUDA(cudaEventRecord(e_slab, t_h2d));
-  int na = 1, nb_unused = 1;
-  if (m > 0) plan_pipeline(m, k, n, clear, &na, &nb_unused);
+  int na = m > 0 ? plan_row_chunks(m, k, n, clear) : 1;
   na = pipeline_parts("M4RI_B200_PIPE_ROWS", na);
   rci_t per = m > 0 ? ((m + na - 1) / na + 255) / 256 * 256 : 256;
   na = m > 0 ? (m + per - 1) / per : 0;
