@@ -262,23 +262,10 @@ pivot_search_kernel(const word *PT, int pstride, int j, int m, const ElimGlobal 
 //                       Tab[g][v][w] = XOR over bits b of v of R'[4g + b][w]
 //   CTAs [nrc, ..)  mult[i] bit k = bit pc[k] of the OLD word j of row i, for every row
 constexpr int RP_XW = 4;
-__global__ void __launch_bounds__(256)
-prepare_step_kernel(word *Tab, unsigned long long *mult, int L, const word *PT, int pstride, int j, int bw, int m,
-                    int nrc, const ElimState *st) {
-  __shared__ word srows[64 * RP_XW], srp[64 * RP_XW];
-  __shared__ int spc[64];
+// The table part of a step, one CTA of 256 threads per RP_XW words (shared by both flavours).
+__device__ __forceinline__ void step_tables(word *Tab, int L, const word *PT, int pstride, int j, int bw,
+                                            const ElimState *st, word *srows, word *srp) {
   const int kp = st->kp, t = threadIdx.x;
-  if ((int)blockIdx.x >= nrc) {
-    if (t < 64) spc[t] = st->pc[t];
-    __syncthreads();
-    const int i = (blockIdx.x - nrc) * 256 + t;
-    if (i >= m) return;
-    const word w = PT[(size_t)i * pstride + j];
-    unsigned long long mm = 0;
-    for (int k = 0; k < kp; k++) mm |= ((w >> spc[k]) & 1ull) << k;
-    mult[i] = mm;
-    return;
-  }
   const int k = t / RP_XW, xx = t % RP_XW, w = j + blockIdx.x * RP_XW + xx;
   const bool live = w < L;
   if (live && k < kp) srows[t] = PT[(size_t)st->pr[k] * pstride + w];
@@ -312,6 +299,26 @@ prepare_step_kernel(word *Tab, unsigned long long *mult, int L, const word *PT, 
     if (v & 8) o ^= r4[3 * RP_XW];
     Tab[(size_t)e * L + w] = o;
   }
+}
+
+__global__ void __launch_bounds__(256)
+prepare_step_kernel(word *Tab, unsigned long long *mult, int L, const word *PT, int pstride, int j, int bw, int m,
+                    int nrc, const ElimState *st) {
+  __shared__ word srows[64 * RP_XW], srp[64 * RP_XW];
+  __shared__ int spc[64];
+  const int kp = st->kp, t = threadIdx.x;
+  if ((int)blockIdx.x >= nrc) {
+    if (t < 64) spc[t] = st->pc[t];
+    __syncthreads();
+    const int i = (blockIdx.x - nrc) * 256 + t;
+    if (i >= m) return;
+    const word w = PT[(size_t)i * pstride + j];
+    unsigned long long mm = 0;
+    for (int k = 0; k < kp; k++) mm |= ((w >> spc[k]) & 1ull) << k;
+    mult[i] = mm;
+    return;
+  }
+  step_tables(Tab, L, PT, pstride, j, bw, st, srows, srp);
 }
 
 // Every (row, word): PT[i][w] ^= sum over k in mult[i] of R'[k][w], w in [j, L), as 16 table
@@ -605,18 +612,25 @@ lu_pivot_search_kernel(const word *PT, int pstride, int j, int m, const ElimGlob
 // pivot columns are the entries of L, mult = the same bits in selection indices), the step's
 // pivot rows get their [L | 1 | E] word, rows above the block's first candidate and the pivots of
 // earlier steps are left alone (mult = 0).
+// (one launch with the step's tables: CTAs [0, nrc) build the tables of the words right of j —
+// they read words > j of the pivot rows, the row part writes word j only)
 __global__ void __launch_bounds__(256)
-lu_rows_kernel(word *PT, int pstride, int j, int m, const ElimGlobal *gl, const unsigned char *ispiv, const int *pidx,
-               unsigned long long *mult, const ElimState *st) {
-  __shared__ word pwcol[64];
-  __shared__ int kcol[64];
+lu_prepare_kernel(word *Tab, int L, int bw, int nrc, word *PT, int pstride, int j, int m, const ElimGlobal *gl,
+                  const unsigned char *ispiv, const int *pidx, unsigned long long *mult, const ElimState *st) {
+  __shared__ word srows[64 * RP_XW], srp[64 * RP_XW];
+  if ((int)blockIdx.x < nrc) {
+    step_tables(Tab, L, PT, pstride, j + 1, bw, st, srows, srp);
+    return;
+  }
+  word *pwcol = srows;                // (the row part reuses the table part's shared memory)
+  int *kcol = (int *)srp;
   const int t = threadIdx.x;
   if (t < 64) {
     pwcol[t] = st->pwcol[t];
     kcol[t] = st->kcol[t];
   }
   __syncthreads();
-  const int i = blockIdx.x * 256 + t;
+  const int i = (blockIdx.x - nrc) * 256 + t;
   if (i >= m) return;
   const int pk = pidx[i];
   if (pk) {
@@ -646,19 +660,44 @@ lu_rows_kernel(word *PT, int pstride, int j, int m, const ElimGlobal *gl, const 
 // ---- PLE, the end: L compressed into the first `rank` columns ---------------------------------
 // Lc[i] bit k = W[i][Q[k]] for k < min(i, rank): row i's multiplier for pivot k sits at pivot
 // column Q[k] during the elimination; the documented storage (ple.rs:44-51, "L and S stored in
-// place over A") has column k of L in column k.
-__global__ void gather_l_kernel(word *Lc, int lcs, int lcw, const word *W, int ws, int m, int rank, const int *Q) {
+// place over A") has column k of L in column k. pm[w] = the pivot columns of word w as a mask,
+// pcnt[w] = pivots left of word w: a destination word walks the set bits of the masks from the
+// word that holds pivot 64*dw on — shifts and masks on a few source words, no load per bit.
+__global__ void pivot_masks_kernel(word *pm, const int *Q, int rank) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < rank) atomicOr((unsigned long long *)&pm[Q[k] >> 6], 1ull << (Q[k] & 63));
+}
+__global__ void pivot_prefix_kernel(int *pcnt, const word *pm, int width) {  // width is a few hundred words
+  const int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= width) return;
+  int acc = 0;
+  for (int u = 0; u < w; u++) acc += __popcll(pm[u]);
+  pcnt[w] = acc;
+}
+__global__ void gather_l_kernel(word *Lc, int lcs, int lcw, const word *W, int ws, int width, int m, int rank,
+                                const int *Q, const word *pm, const int *pcnt) {
   const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (idx >= (long long)m * lcw) return;
   const int i = (int)(idx / lcw), dw = (int)(idx % lcw);
-  const int kmax = min(i, rank);
-  const word *row = W + (size_t)i * ws;
+  const int kmax = min(i, rank), k0 = 64 * dw;
   word o = 0;
-  for (int b = 0; b < 64; b++) {
-    const int k = 64 * dw + b;
-    if (k >= kmax) break;
-    const int c = Q[k];
-    o |= ((row[c >> 6] >> (c & 63)) & 1) << b;
+  if (k0 < kmax) {
+    const word *row = W + (size_t)i * ws;
+    const int want = min(64, kmax - k0);
+    int w = Q[k0] >> 6, filled = 0;
+    int skip = k0 - pcnt[w];  // pivots of word w that belong to earlier destination words
+    while (filled < want && w < width) {
+      word mask = pm[w];
+      const word v = row[w];
+      for (; skip > 0; skip--) mask &= mask - 1;
+      while (mask && filled < want) {
+        const int b = __ffsll((long long)mask) - 1;
+        o |= ((v >> b) & 1) << filled;
+        filled++;
+        mask &= mask - 1;
+      }
+      w++;
+    }
   }
   Lc[(size_t)i * lcs + dw] = o;
 }
@@ -788,13 +827,12 @@ static int eliminate(DMat *W, int pivot_cols, bool lu, std::vector<int> *pivots,
       const int valid = std::min(64, bcols - 64 * j);
       const word colmask = valid == 64 ? ~(word)0 : (((word)1 << valid) - 1);
       if (lu) {
-        // the word column itself is finished by lu_rows_kernel; the rank-64 update starts right of it
+        // the word column itself is finished by lu_prepare_kernel; the rank-64 update starts right of it
         lu_pivot_search_kernel<<<1, 1024, 0, s>>>(PT->d, pstride, j, m, gl, ispiv, pidx, st, c0, colmask);
         M4B_LAUNCHED();
         const int nrc = (int)cdiv(L - j - 1, RP_XW);
-        prepare_step_kernel<<<nrc, 256, 0, s>>>(Rp, mult, L, PT->d, pstride, j + 1, bw, m, nrc, st);
-        M4B_LAUNCHED();
-        lu_rows_kernel<<<cdiv(m, 256), 256, 0, s>>>(PT->d, pstride, j, m, gl, ispiv, pidx, mult, st);
+        lu_prepare_kernel<<<nrc + cdiv(m, 256), 256, 0, s>>>(Rp, L, bw, nrc, PT->d, pstride, j, m, gl, ispiv, pidx, mult,
+                                                            st);
         M4B_LAUNCHED();
         apply_rprime_kernel<<<cdiv((long long)m * (L - j - 1), 256), 256, 0, s>>>(PT->d, pstride, j + 1, L, m, pidx,
                                                                                  mult, Rp, st);
@@ -818,8 +856,22 @@ static int eliminate(DMat *W, int pivot_cols, bool lu, std::vector<int> *pivots,
       gather_pivot_rows_kernel<<<cdiv((long long)B * (tw + 1), 256), 256, 0, s>>>(OP->d, OP->rowstride, W->d, ws, tw0, tw,
                                                                                  PT->d, pstride, bw, st);
       M4B_LAUNCHED();
-      DMat Wt = dwin(W, 0, t0, m, n - t0), Tg = dwin(PT, 0, B, m, B), Ot = dwin(OP, 0, 0, B, n - t0);
-      dmul(&Wt, &Tg, &Ot, 0, M4RI_B200_ALGO_AUTO, s);
+      // PLE: rows above the rank are finished (their tags are zero) — skip them, using the newest
+      // rank that has already come home (a lower bound of the current one)
+      // (the host stays at most three blocks ahead of the device: enough queued work to keep it
+      // busy, and a rank that is at most three blocks old)
+      int row_lb = 0;
+      if (lu && b >= 3) {
+        M4B_CUDA(cudaEventSynchronize(ev[b - 3]));
+        int q = b - 3;
+        while (q + 1 < b && cudaEventQuery(ev[q + 1]) == cudaSuccess) q++;
+        row_lb = h_rank[q] / 256 * 256;
+      }
+      if (row_lb < m) {
+        DMat Wt = dwin(W, row_lb, t0, m - row_lb, n - t0), Tg = dwin(PT, row_lb, B, m - row_lb, B),
+             Ot = dwin(OP, 0, 0, B, n - t0);
+        dmul(&Wt, &Tg, &Ot, 0, M4RI_B200_ALGO_AUTO, s);
+      }
     }
     writeback_panel_kernel<<<cdiv((long long)m * bw, 256), 256, 0, s>>>(W->d, ws, W->width, PT->d, pstride, m, cw0, bw);
     M4B_LAUNCHED();
@@ -894,8 +946,20 @@ int k_ple(DMat *W, int *P, int *Q, bool pluq, cudaStream_t s) {
   if (r > 0) {
     const int lcw = width_of(r);
     DMat *Lc = dmat_new(m, r, s);
-    gather_l_kernel<<<cdiv((long long)m * lcw, 256), 256, 0, s>>>(Lc->d, Lc->rowstride, lcw, W->d, ws, m, r, dq);
+    word *pm;
+    int *pcnt;
+    M4B_CUDA(cudaMallocAsync(&pm, (size_t)width * 8, s));
+    M4B_CUDA(cudaMallocAsync(&pcnt, (size_t)width * sizeof(int), s));
+    M4B_CUDA(cudaMemsetAsync(pm, 0, (size_t)width * 8, s));
+    pivot_masks_kernel<<<cdiv(r, 256), 256, 0, s>>>(pm, dq, r);
     M4B_LAUNCHED();
+    pivot_prefix_kernel<<<cdiv(width, 128), 128, 0, s>>>(pcnt, pm, width);
+    M4B_LAUNCHED();
+    gather_l_kernel<<<cdiv((long long)m * lcw, 256), 256, 0, s>>>(Lc->d, Lc->rowstride, lcw, W->d, ws, width, m, r, dq,
+                                                                 pm, pcnt);
+    M4B_LAUNCHED();
+    M4B_CUDA(cudaFreeAsync(pm, s));
+    M4B_CUDA(cudaFreeAsync(pcnt, s));
     strip_l_kernel<<<cdiv((long long)m * width, 256), 256, 0, s>>>(W->d, ws, width, m, r, dq);
     M4B_LAUNCHED();
     if (pluq) {
