@@ -105,3 +105,44 @@ def test_matvec_on_generated_shapes(gpu, m4, orc, m, n, seed):
     col = m4.BinMatrix(a).mul_slice(x[0][: orc.width(n)])
     assert (m4.mzd_words(col.mzd)[:, 0] == [(int(want[i // 64]) >> (i % 64)) & 1 for i in range(m)]).all()
     L.mzd_free(hx)
+
+
+# ---- the consumers: generated shapes and rank structures for PLE / PLUQ / echelon form ----------
+edim = st.one_of(st.integers(1, 8), st.sampled_from([63, 64, 65, 127, 128, 129, 1023, 1024, 1025]),
+                 st.integers(1, 400), st.integers(400, 1500))
+
+
+@settings(max_examples=40, **COMMON)
+@given(m=edim, n=edim, rank_frac=st.sampled_from([0.0, 0.1, 0.5, 1.0]), seed=st.integers(0, 2 ** 31),
+       pluq=st.booleans())
+def test_ple_and_echelon_form_on_generated_shapes(gpu, m4, orc, m, n, rank_frac, seed, pluq):
+    """mzd_ple / mzd_pluq (ple.rs:65,35) satisfy their defining identity and agree with the oracle
+    on rank and pivot columns; mzd_echelonize gives the oracle's reduced form of the same matrix."""
+    L = m4.lib()
+    r_target = int(round(rank_frac * min(m, n)))
+    if rank_frac >= 1.0:
+        A = orc.random(m, n, seed)
+    elif r_target == 0:
+        A = orc.zeros(m, n)
+    else:
+        A = orc.mul_m4rm(orc.random(m, r_target, seed), orc.random(r_target, n, seed + 1), r_target, n)
+    w = orc.width(n)
+    want, rank, piv = orc.rref(A, n)
+    a = m4.mzd_from_words(A, n)
+    P, Q = L.mzp_init(m), L.mzp_init(n)
+    r = (L.mzd_pluq if pluq else L.mzd_ple)(a, P, Q, 0)
+    assert r == rank, (m, n, r, rank)
+    Pv = [int(P.contents.values[i]) for i in range(m)]
+    Qv = [int(Q.contents.values[i]) for i in range(n)]
+    assert Qv[:r] == [int(c) for c in piv]
+    got = np.ascontiguousarray(m4.mzd_words(a))
+    assert not got[:, w:].any()
+    back = orc.ple_reconstruct(got, n, r, Pv, Qv, pluq)
+    assert (back[:, :w] == A[:, :w]).all(), (m, n, rank_frac, pluq)
+    L.mzp_free(P)
+    L.mzp_free(Q)
+    L.mzd_free(a)
+    e = m4.mzd_from_words(A, n)
+    assert L.mzd_echelonize(e, 1) == rank
+    assert (m4.mzd_words(e)[:, :w] == want[:, :w]).all()
+    L.mzd_free(e)
