@@ -172,8 +172,10 @@ def cpu_arm(n, m_total, steps, warmup, target_s=12.0, budget_s=600.0, strassen_n
             "strategies": {"strassen": strassen, "m4rm": m4rm}}
 
 
-def run_lpn(args):
+def run_lpn(args, quick=False):
     """BASELINE configs[4] (extra bench line, not the headline): the LPN covering-code shapes.
+    quick = True is the summary the default line carries under "also_measured" (product, mat-vec,
+    8-vector batch only).
     (a) tall product 2^20 x 512 times 512 x 512 — compute bound, every algorithm;
     (b) mat-vec y = A*x on the resident 2^20 x 512 A, packed words in and out — HBM bound:
         algorithmic bytes = 8*(m*width + width) + ceil(m/64)*8 per product."""
@@ -208,7 +210,7 @@ def run_lpn(args):
            "config": {"workload": "tall 2^20x512 * 512x512 + mat-vec on the resident A", "m": m, "k": k, "n": n,
                       "l2": "L2 flushed between steps by writing a 256 MiB buffer"}}
     prod = {}
-    for name in ("auto", "mma", "m4rm"):
+    for name in (("auto",) if quick else ("auto", "mma", "m4rm")):
         ms = timed(lambda: m4.dmul(dC, dA, dB, clear=True, algo=m4.ALGO_NAMES[name]), args.steps, args.warmup)
         ok = L.m4ri_b200_dfreivalds(dC.h, dA.h, dB.h, 0xF5E1)
         prod[name] = {"ms": ms, "tbitops": 2.0 * m * k * n / ms / 1e9, "freivalds": bool(ok),
@@ -250,7 +252,7 @@ def run_lpn(args):
                      "timing": "24 launches back to back over 4 resident copies of A (256 MiB > L2), one event pair",
                      "roofline": roof(bytes_alg, ms, "mul_v_coal_kernel<4,2>")}
     # batched: b vectors against the resident A in one pass (m4ri_b200_dmul_v_batched)
-    for bvec in (8, 32):
+    for bvec in ((8,) if quick else (8, 32)):
         dX = m4.DMat.init(bvec, k).fill_random(24)
         dY = m4.DMat.init(bvec, m)
         msb = rotating(lambda A_: L.m4ri_b200_dmul_v_batched(dY.h, A_.h, dX.h, 1))
@@ -259,6 +261,8 @@ def run_lpn(args):
         out[f"matvec_batched_{bvec}"] = {"ms": msb, "tbitops": 2.0 * m * k * bvec / msb / 1e9, "vectors": bvec,
                                         "passes_over_A": passes,
                                         "roofline": roof(bb, msb, "mul_vb_coal_kernel<4,1,8>")}
+    if quick:
+        return out
     # the reference's own call: BinMatrix::mul_slice = mzd_mul_naive(NULL, A, x_column) on HOST
     # operands (binary_matrix.rs:416-431): 64 MiB of A cross PCIe per call, then the same kernel
     hA = L.mzd_init(m, k)
@@ -314,6 +318,54 @@ def run_lpn(args):
     out["matvec_batched_8_32768x32768"] = {"ms": ms3b, "tbitops": 2.0 * m3 * n3 * 8 / ms3b / 1e9,
                                            "roofline": roof(b3 + 7 * (n3 // 8 + m3 // 8), ms3b, "mul_vb_long_kernel<8>")}
     print(json.dumps(out))
+    return out
+
+
+def also_measured(args):
+    """Summary of the other Section-8 rows inside the default N = 1 line, so that the driver's own run
+    carries them: the LPN shapes (configs[4]) and the consumers of the product (RREF and PLE of a
+    random 8192 x 8192 matrix, device-resident, checked against the CPU oracle's rank, pivot
+    columns and reduced form)."""
+    import m4ri_rust_b200 as m4
+    import oracle
+    L = m4.lib()
+    la = argparse.Namespace(steps=5, warmup=3)
+    lpn = run_lpn(la, quick=True)
+    out = {"lpn_2^20x512": {"product_ms": lpn["product"]["auto"]["ms"], "product_tbitops": lpn["product"]["auto"]["tbitops"],
+                            "product_freivalds": lpn["product"]["auto"]["freivalds"],
+                            "matvec_ms": lpn["matvec"]["ms"], "matvec_hbm_frac": lpn["matvec"]["roofline"]["frac"],
+                            "matvec_batched_8_ms": lpn["matvec_batched_8"]["ms"],
+                            "full_line": "python bench.py --workload lpn"}}
+    n = 8192
+    W = m4.DMat.init(n, n)
+    A = W.fill_random(7).to_words()
+    want, rank, piv = oracle.rref(np.ascontiguousarray(A), n)
+    ts = []
+    for _ in range(3):
+        W.fill_random(7)
+        L.m4ri_b200_synchronize()
+        t0 = time.perf_counter()
+        r = L.m4ri_b200_drref(W.h, 0, None, 0)
+        L.m4ri_b200_synchronize()
+        ts.append((time.perf_counter() - t0) * 1e3)
+    got = W.to_words()
+    w = n // 64
+    ok_rref = bool(r == rank and (got[:, :w] == want[:, :w]).all())
+    P, Q = (ctypes.c_int * n)(), (ctypes.c_int * n)()
+    tp = []
+    for _ in range(3):
+        W.fill_random(7)
+        L.m4ri_b200_synchronize()
+        t0 = time.perf_counter()
+        rp = L.m4ri_b200_dple(W.h, P, Q, 0)
+        L.m4ri_b200_synchronize()
+        tp.append((time.perf_counter() - t0) * 1e3)
+    ok_ple = bool(rp == rank and list(Q)[:rp] == [int(c) for c in piv])
+    out["elimination_8192"] = {"rref_ms": min(ts), "ple_ms": min(tp), "rank": int(r),
+                               "rref_equals_cpu_oracle": ok_rref, "ple_rank_and_pivot_columns_equal_cpu_oracle": ok_ple}
+    if not (ok_rref and ok_ple):
+        raise SystemExit("bench.py: elimination result differs from the CPU oracle")
+    return out
 
 
 def main():
@@ -332,6 +384,7 @@ def main():
     ap.add_argument("--workload", default="square", choices=["square", "lpn"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the also_measured summary (LPN shapes, elimination)")
     args = ap.parse_args()
     if args.chunks not in ("ramp", "ramp4", "auto"):
         args.chunks = int(args.chunks)
@@ -634,6 +687,8 @@ def main():
         line["parity"]["equals_cpu_oracle_full_size"] = same
         if not same:
             raise SystemExit("bench.py: GPU product differs from the CPU oracle's at full size")
+    if world == 1 and not args.no_extras:
+        line["also_measured"] = also_measured(args)
     print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()
