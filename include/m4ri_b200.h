@@ -81,6 +81,13 @@ mzd_t *mzd_add(mzd_t *C, const mzd_t *A, const mzd_t *B);/* mzd.rs:223 (C may al
 mzd_t *mzd_sub(mzd_t *C, const mzd_t *A, const mzd_t *B);/* mzd.rs:230 (alias of add)  */
 /* [A B] and [A; B] (BinMatrix::augmented / stacked, binary_matrix.rs:221-244): host copies, so that
  * an unmodified m4ri-rust links against this library alone. */
+/* Row / column utilities m4ri-sys binds next to them: host word work on the caller's matrix. */
+void mzd_row_swap(mzd_t *M, rci_t rowa, rci_t rowb);                 /* mzd.rs:130 */
+void mzd_copy_row(mzd_t *B, rci_t i, const mzd_t *A, rci_t j);       /* mzd.rs:141 */
+void mzd_col_swap(mzd_t *M, rci_t cola, rci_t colb);                 /* mzd.rs:144 */
+mzd_t *mzd_submatrix(mzd_t *S, const mzd_t *M, rci_t lowr, rci_t lowc, rci_t highr, rci_t highc); /* mzd.rs:205 (copy; any lowc) */
+int mzd_is_zero(const mzd_t *A);                                     /* mzd.rs:233 (declared there without its int result) */
+void mzd_row_clear_offset(mzd_t *M, rci_t row, rci_t coloffset);     /* mzd.rs:240 */
 mzd_t *mzd_concat(mzd_t *C, const mzd_t *A, const mzd_t *B); /* mzd.rs:195 */
 mzd_t *mzd_stack(mzd_t *C, const mzd_t *A, const mzd_t *B);  /* mzd.rs:201 */
 
@@ -89,6 +96,9 @@ mzd_t *mzd_stack(mzd_t *C, const mzd_t *A, const mzd_t *B);  /* mzd.rs:201 */
 mzd_t *mzd_mul(mzd_t *C, const mzd_t *A, const mzd_t *B, int cutoff);      /* strassen.rs:18 */
 /* C ^= A*B. */
 mzd_t *mzd_addmul(mzd_t *C, const mzd_t *A, const mzd_t *B, int cutoff);   /* strassen.rs:31 */
+/* M4RI's multi-core forms of the two: the same GPU calls. */
+mzd_t *mzd_mul_mp(mzd_t *C, const mzd_t *A, const mzd_t *B, int cutoff);   /* mp.rs:6 */
+mzd_t *mzd_addmul_mp(mzd_t *C, const mzd_t *A, const mzd_t *B, int cutoff); /* mp.rs:8 */
 mzd_t *mzd_mul_m4rm(mzd_t *C, const mzd_t *A, const mzd_t *B, int k);      /* brilliantrussian.rs:216 */
 mzd_t *mzd_addmul_m4rm(mzd_t *C, const mzd_t *A, const mzd_t *B, int k);   /* brilliantrussian.rs:224 */
 /* upstream-M4RI-shaped, named by the north star; not declared by m4ri-sys */
@@ -110,8 +120,10 @@ mzd_t *mzd_mul_v(mzd_t *y, const mzd_t *A, const mzd_t *x);
 rci_t mzd_echelonize(mzd_t *A, int full);               /* echelonform.rs:16 (BinMatrix::echelonize/rank, binary_matrix.rs:247-261) */
 rci_t mzd_echelonize_pluq(mzd_t *A, int full);          /* echelonform.rs:27 */
 rci_t mzd_echelonize_m4ri(mzd_t *A, int full, int k);   /* echelonform.rs:36 */
+rci_t mzd_top_echelonize_m4ri(mzd_t *A, int k);         /* brilliantrussian.rs:199 (declared there without its rank result) */
 /* dst = src^-1 (dst NULL: allocate); NULL when src is singular. */
 mzd_t *mzd_inv_m4ri(mzd_t *dst, const mzd_t *src, int k); /* brilliantrussian.rs:208 (BinMatrix::inverted, binary_matrix.rs:264-268) */
+mzd_t *mzd_invert_naive(mzd_t *inv, const mzd_t *A, const mzd_t *identity); /* mzd.rs:218 (identity is not needed) */
 /* Solves A X = B, X stored in the first ncols(A) rows of B (free variables zero, other rows of B
  * zeroed); 0 = solved, -1 = inconsistent (B untouched). A is left as it was. */
 int mzd_solve_left(mzd_t *A, mzd_t *B, int cutoff, int inconsistency_check); /* solve.rs:23 (solve_left, binary_matrix.rs:582-586) */
@@ -147,6 +159,11 @@ rci_t mzd_ple(mzd_t *A, mzp_t *P, mzp_t *Q, int cutoff);
 /* A = P L U Q in place, returns the rank (ple.rs:35): as mzd_ple, with U = E after the column
  * swaps i <-> Q[i], i = 0 .. r-1 in turn (mzd_apply_p_right_trans), upper triangular r x ncols. */
 rci_t mzd_pluq(mzd_t *A, mzp_t *P, mzp_t *Q, int cutoff);
+/* Solves (P L U Q) X = B from the packed factors mzd_pluq left in A and its rank (solve.rs:53): X
+ * overwrites the first ncols(A) rows of B (free variables zero, other rows zeroed); 0 = solved,
+ * -1 = inconsistent (B untouched). B needs at least max(nrows(A), ncols(A)) rows. */
+int mzd_pluq_solve_left(const mzd_t *A, rci_t rank, const mzp_t *P, const mzp_t *Q, mzd_t *B, int cutoff,
+                        int inconsistency_check);
 
 /* ---- additive API: algorithm choice, device-resident operands --------------- */
 enum m4ri_b200_algo {

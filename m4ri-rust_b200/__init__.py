@@ -83,8 +83,14 @@ def lib():
         "mzd_apply_p_left": (None, [MzdP, MzpP]), "mzd_apply_p_left_trans": (None, [MzdP, MzpP]),
         "mzd_apply_p_right": (None, [MzdP, MzpP]), "mzd_apply_p_right_trans": (None, [MzdP, MzpP]),
         "mzd_ple": (i, [MzdP, MzpP, MzpP, i]), "mzd_pluq": (i, [MzdP, MzpP, MzpP, i]),
+        "mzd_pluq_solve_left": (i, [MzdP, i, MzpP, MzpP, MzdP, i, i]),
         "m4ri_b200_dple": (i, [vp, ctypes.POINTER(i), ctypes.POINTER(i), i]),
         "mzd_concat": (MzdP, [MzdP, MzdP, MzdP]), "mzd_stack": (MzdP, [MzdP, MzdP, MzdP]),
+        "mzd_row_swap": (None, [MzdP, i, i]), "mzd_col_swap": (None, [MzdP, i, i]),
+        "mzd_copy_row": (None, [MzdP, i, MzdP, i]), "mzd_is_zero": (i, [MzdP]),
+        "mzd_row_clear_offset": (None, [MzdP, i, i]), "mzd_submatrix": (MzdP, [MzdP, MzdP, i, i, i, i]),
+        "mzd_mul_mp": (MzdP, [MzdP, MzdP, MzdP, i]), "mzd_addmul_mp": (MzdP, [MzdP, MzdP, MzdP, i]),
+        "mzd_invert_naive": (MzdP, [MzdP, MzdP, MzdP]), "mzd_top_echelonize_m4ri": (i, [MzdP, i]),
         "mzd_mul": (MzdP, [MzdP, MzdP, MzdP, i]), "mzd_addmul": (MzdP, [MzdP, MzdP, MzdP, i]),
         "mzd_mul_m4rm": (MzdP, [MzdP, MzdP, MzdP, i]),
         "mzd_addmul_m4rm": (MzdP, [MzdP, MzdP, MzdP, i]),

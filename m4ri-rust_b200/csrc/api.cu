@@ -1160,6 +1160,10 @@ mzd_t *mzd_mul(mzd_t *C, const mzd_t *A, const mzd_t *B, int cutoff) {
 mzd_t *mzd_addmul(mzd_t *C, const mzd_t *A, const mzd_t *B, int cutoff) {
   return host_product(C, A, B, 0, M4RI_B200_ALGO_AUTO, 0, "mzd_addmul", cutoff < 0 ? 0 : cutoff);
 }
+// mp.rs:6,8 — M4RI's OpenMP products: here every product already runs on all SMs (and, with
+// m4ri_b200_set_devices, on all GPUs of the process), so they are the same calls
+mzd_t *mzd_mul_mp(mzd_t *C, const mzd_t *A, const mzd_t *B, int cutoff) { return mzd_mul(C, A, B, cutoff); }
+mzd_t *mzd_addmul_mp(mzd_t *C, const mzd_t *A, const mzd_t *B, int cutoff) { return mzd_addmul(C, A, B, cutoff); }
 mzd_t *mzd_mul_m4rm(mzd_t *C, const mzd_t *A, const mzd_t *B, int k) {
   (void)k;  // table width is fixed by the shared-memory budget
   return host_product(C, A, B, 1, M4RI_B200_ALGO_M4RM, 0, "mzd_mul_m4rm", -1);

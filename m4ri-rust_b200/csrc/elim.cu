@@ -741,6 +741,27 @@ __global__ void permute_rows_kernel(word *out, int os, const word *in, int is, i
   const int i = (int)(idx / width), w = (int)(idx % width);
   out[(size_t)i * os + w] = in[(size_t)src[i] * is + w];
 }
+// dst (r x r, zeroed) = the unit lower (lower != 0) or the upper triangle of the packed factors:
+// bits c < i plus the diagonal, or bits c >= i, of the first r columns of row i
+__global__ void tri_extract_kernel(word *dst, int ds, const word *src, int ss, int r, int lower) {
+  const int rw = (r + 63) / 64;
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (idx >= (long long)r * rw) return;
+  const int i = (int)(idx / rw), w = (int)(idx % rw);
+  word v = src[(size_t)i * ss + w];
+  const int lo = 64 * w;                       // first column of this word
+  word below = 0;                              // mask of the columns c < i in this word
+  if (i >= lo + 64) below = ~(word)0;
+  else if (i > lo) below = ((word)1 << (i - lo)) - 1;
+  if (lower) {
+    v &= below;
+    if (i >= lo && i < lo + 64) v |= (word)1 << (i - lo);
+  } else {
+    v &= ~below;
+  }
+  if (w == rw - 1 && (r & 63)) v &= ((word)1 << (r & 63)) - 1;
+  dst[(size_t)i * ds + w] = v;
+}
 __global__ void iota_kernel(int *a, int n) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) a[i] = i;
@@ -1067,6 +1088,86 @@ rci_t mzd_pluq(mzd_t *A, mzp_t *P, mzp_t *Q, int cutoff) {
   return host_ple(A, P, Q, true, "mzd_pluq");
 }
 
+// forward declarations (defined below)
+static std::vector<int> compose_swaps(const mzp_t *P, int n, bool reverse);
+
+// rows [0, n) of D permuted in place by a gather list
+static void permute_rows_inplace(DMat *D, int n, const std::vector<int> &src, cudaStream_t s) {
+  bool moved = false;
+  for (int i = 0; i < n && !moved; i++) moved = src[i] != i;
+  if (!moved) return;
+  int *dsrc;
+  M4B_CUDA(cudaMallocAsync(&dsrc, (size_t)n * sizeof(int), s));
+  M4B_CUDA(cudaMemcpyAsync(dsrc, src.data(), (size_t)n * sizeof(int), cudaMemcpyHostToDevice, s));
+  DMat *T = dmat_new(n, D->ncols, s);
+  permute_rows_kernel<<<cdiv((long long)n * D->width, 256), 256, 0, s>>>(T->d, T->rowstride, D->d, D->rowstride, n,
+                                                                      D->width, dsrc);
+  M4B_LAUNCHED();
+  DMat top = dwin(D, 0, 0, n, D->ncols);
+  k_copy(&top, T, s);
+  M4B_CUDA(cudaStreamSynchronize(s));  // src (host) and dsrc are done with
+  M4B_CUDA(cudaFreeAsync(dsrc, s));
+  dmat_delete(T, s);
+}
+
+// Solves (P L U Q) X = B with the packed factors mzd_pluq left in A (solve.rs:53): rows of B
+// permuted by P, Y = L11^-1 B[:r] and U11^-1 Y as reduced row echelon forms of [L11 | .] and
+// [U11 | .] on the GPU, the consistency check B[r:] == L21 Y as one product, X = Z permuted by Q
+// (free variables zero). X overwrites B (its other rows are zeroed); -1 and B untouched when the
+// system is inconsistent.
+int mzd_pluq_solve_left(const mzd_t *A, rci_t rank, const mzp_t *P, const mzp_t *Q, mzd_t *B, int cutoff,
+                        int inconsistency_check) {
+  (void)cutoff;
+  (void)inconsistency_check;  // always checked
+  const rci_t m = A->nrows, n = A->ncols, k = B->ncols, r = rank;
+  if (P->length != m || Q->length != n) die("m4ri_b200: mzd_pluq_solve_left: permutation lengths must match A\n");
+  if (B->nrows < m || B->nrows < n) die("m4ri_b200: mzd_pluq_solve_left: B needs at least max(nrows(A), ncols(A)) rows\n");
+  if (r < 0 || r > m || r > n) die("m4ri_b200: mzd_pluq_solve_left: rank %d out of range\n", r);
+  if (k == 0 || B->nrows == 0) return 0;
+  cudaStream_t s = current_stream();
+  DMat *dB = dmat_new(B->nrows, k, s);
+  upload(dB, B, s);
+  permute_rows_inplace(dB, m, compose_swaps(P, m, false), s);
+  DMat *dX = dmat_new(B->nrows, k, s);  // zero: free variables and the rows beyond ncols(A)
+  int ok = 1;
+  if (r > 0) {
+    DMat *dA = dmat_new(m, n, s);
+    upload(dA, A, s);
+    const rci_t off = (r + 127) / 128 * 128;
+    DMat *W = dmat_new(r, off + k, s);
+    DMat left = dwin(W, 0, 0, r, r), right = dwin(W, 0, off, r, k), btop = dwin(dB, 0, 0, r, k);
+    tri_extract_kernel<<<cdiv((long long)r * width_of(r), 256), 256, 0, s>>>(W->d, W->rowstride, dA->d, dA->rowstride, r, 1);
+    M4B_LAUNCHED();
+    k_copy(&right, &btop, s);
+    if (k_rref(W, r, nullptr, s) != r) die("m4ri_b200: mzd_pluq_solve_left: L is not unit lower triangular\n");
+    if (m > r) {  // B[r:] ^= L21 * Y must vanish
+      DMat rest = dwin(dB, r, 0, m - r, k), L21 = dwin(dA, r, 0, m - r, r);
+      dmul(&rest, &L21, &right, 0, M4RI_B200_ALGO_AUTO, s);
+      ok = k_is_zero(&rest, s) ? 1 : 0;
+    }
+    if (ok) {
+      // [U11 | Y] -> [I | Z]; Y sits in the right part already
+      k_zero(&left, s);
+      tri_extract_kernel<<<cdiv((long long)r * width_of(r), 256), 256, 0, s>>>(W->d, W->rowstride, dA->d, dA->rowstride, r, 0);
+      M4B_LAUNCHED();
+      if (k_rref(W, r, nullptr, s) != r) die("m4ri_b200: mzd_pluq_solve_left: U has a zero on its diagonal\n");
+      DMat xtop = dwin(dX, 0, 0, r, k);
+      k_copy(&xtop, &right, s);
+      permute_rows_inplace(dX, n, compose_swaps(Q, n, true), s);
+    }
+    dmat_delete(W, s);
+    dmat_delete(dA, s);
+  } else if (m > 0) {
+    DMat rest = dwin(dB, 0, 0, m, k);
+    ok = k_is_zero(&rest, s) ? 1 : 0;
+  }
+  if (ok) download(B, dX, s);
+  dmat_delete(dB, s);
+  dmat_delete(dX, s);
+  M4B_CUDA(cudaStreamSynchronize(s));
+  return ok ? 0 : -1;
+}
+
 // The swaps i <-> P[i] (i ascending, or descending for `reverse`) composed into one gather list:
 // position p of the result holds element src[p] of the input.
 static std::vector<int> compose_swaps(const mzp_t *P, int n, bool reverse) {
@@ -1168,6 +1269,19 @@ mzd_t *mzd_inv_m4ri(mzd_t *dst, const mzd_t *src, int k) {
   dmat_delete(W, s);
   M4B_CUDA(cudaStreamSynchronize(s));
   return out;
+}
+
+// mzd.rs:218 — inverse by elimination; the identity argument only saved M4RI an allocation.
+// NULL when A is singular (M4RI's naive routine does not notice and returns garbage).
+mzd_t *mzd_invert_naive(mzd_t *inv, const mzd_t *A, const mzd_t *identity) {
+  (void)identity;
+  return mzd_inv_m4ri(inv, A, 0);
+}
+// brilliantrussian.rs:199 — completes an upper triangular form to the reduced one: the reduced
+// row echelon form of whatever is passed in (the same unique object); returns the rank.
+rci_t mzd_top_echelonize_m4ri(mzd_t *A, int k) {
+  (void)k;
+  return host_echelonize(A, "mzd_top_echelonize_m4ri");
 }
 
 // Solves A X = B; X overwrites the first ncols(A) rows of B (the rest of B is zeroed). Returns 0,

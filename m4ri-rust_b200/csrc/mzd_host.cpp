@@ -380,4 +380,87 @@ void mzp_print(const mzp_t *P) {
   printf("]");
 }
 
+// ---- row / column utilities m4ri-sys also binds (mzd.rs:130,141,144,205,233,240): host word work ----
+void mzd_row_swap(mzd_t *M, rci_t rowa, rci_t rowb) {
+  if (rowa == rowb || M->width == 0) return;
+  word *a = M->rows[rowa], *b = M->rows[rowb];
+  const word hm = M->high_bitmask;
+  for (wi_t w = 0; w + 1 < M->width; w++) {
+    const word t = a[w];
+    a[w] = b[w];
+    b[w] = t;
+  }
+  // the last word may be shared with a parent's other columns (windows): swap the valid bits only
+  const wi_t l = M->width - 1;
+  const word t = (a[l] ^ b[l]) & hm;
+  a[l] ^= t;
+  b[l] ^= t;
+}
+void mzd_copy_row(mzd_t *B, rci_t i, const mzd_t *A, rci_t j) {
+  if (A->ncols > B->ncols) die("m4ri_b200: mzd_copy_row: source has more columns than the target\n");
+  if (A->width == 0) return;
+  const word *src = A->rows[j];
+  word *dst = B->rows[i];
+  for (wi_t w = 0; w + 1 < A->width; w++) dst[w] = src[w];
+  const wi_t l = A->width - 1;
+  dst[l] = (dst[l] & ~A->high_bitmask) | (src[l] & A->high_bitmask);
+}
+void mzd_col_swap(mzd_t *M, rci_t cola, rci_t colb) {
+  if (cola == colb) return;
+  const wi_t wa = cola / 64, wb = colb / 64;
+  const int ba = cola % 64, bb = colb % 64;
+  for (rci_t i = 0; i < M->nrows; i++) {
+    word *row = M->rows[i];
+    const word x = ((row[wa] >> ba) ^ (row[wb] >> bb)) & 1;
+    row[wa] ^= x << ba;
+    row[wb] ^= x << bb;
+  }
+}
+int mzd_is_zero(const mzd_t *A) {
+  if (A->width == 0) return 1;
+  for (rci_t i = 0; i < A->nrows; i++) {
+    const word *row = A->rows[i];
+    word acc = 0;
+    for (wi_t w = 0; w + 1 < A->width; w++) acc |= row[w];
+    acc |= row[A->width - 1] & A->high_bitmask;
+    if (acc) return 0;
+  }
+  return 1;
+}
+void mzd_row_clear_offset(mzd_t *M, rci_t row, rci_t coloffset) {
+  if (coloffset >= M->ncols || M->width == 0) return;
+  word *r = M->rows[row];
+  const wi_t w0 = coloffset / 64;
+  const word keep_low = (coloffset % 64) ? ((m4ri_one << (coloffset % 64)) - 1) : 0;
+  for (wi_t w = w0; w < M->width; w++) {
+    word clear = m4ri_ffff;
+    if (w == w0) clear &= ~keep_low;
+    if (w == M->width - 1) clear &= M->high_bitmask;
+    r[w] &= ~clear;
+  }
+}
+// S = M[lowr .. highr) x [lowc .. highc) as a copy (S NULL: allocate); any lowc.
+mzd_t *mzd_submatrix(mzd_t *S, const mzd_t *M, rci_t lowr, rci_t lowc, rci_t highr, rci_t highc) {
+  if (lowr < 0 || lowc < 0 || highr < lowr || highc < lowc || highr > M->nrows || highc > M->ncols)
+    die("m4ri_b200: mzd_submatrix: window out of range\n");
+  const rci_t nr = highr - lowr, nc = highc - lowc;
+  if (!S) S = mzd_init(nr, nc);
+  else if (S->nrows < nr || S->ncols < nc) die("m4ri_b200: mzd_submatrix: got S with dimension %d x %d but expected %d x %d\n", S->nrows, S->ncols, nr, nc);
+  if (nc == 0) return S;
+  const wi_t w0 = lowc / 64, nw = width_of(nc);
+  const int sh = lowc % 64;
+  const word hm = high_mask(nc);
+  for (rci_t i = 0; i < nr; i++) {
+    const word *src = M->rows[lowr + i];
+    word *dst = S->rows[i];
+    for (wi_t w = 0; w < nw; w++) {
+      word v = src[w0 + w] >> sh;
+      if (sh && w0 + w + 1 < M->width) v |= src[w0 + w + 1] << (64 - sh);
+      if (w == nw - 1) dst[w] = (dst[w] & ~hm) | (v & hm);
+      else dst[w] = v;
+    }
+  }
+  return S;
+}
+
 }  // extern "C"

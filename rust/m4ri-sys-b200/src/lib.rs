@@ -102,12 +102,30 @@ extern "C" {
     pub fn mzd_inv_m4ri(dst: *mut Mzd, src: *const Mzd, k: c_int) -> *mut Mzd;
     /// Solves A X = B, X in the first ncols(A) rows of B; 0 on success, -1 when inconsistent.
     pub fn mzd_solve_left(a: *mut Mzd, b: *mut Mzd, cutoff: c_int, inconsistency_check: c_int) -> c_int;
+    /// `mzd.rs:218`; NULL when `a` is singular. `identity` is accepted and not needed.
+    pub fn mzd_invert_naive(inv: *mut Mzd, a: *const Mzd, identity: *const Mzd) -> *mut Mzd;
+    /// `brilliantrussian.rs:199`; returns the rank.
+    pub fn mzd_top_echelonize_m4ri(m: *mut Mzd, k: c_int) -> Rci;
+    /// `mp.rs:6,8`: M4RI's OpenMP products — the same GPU calls as `mzd_mul` / `mzd_addmul`.
+    pub fn mzd_mul_mp(c: *mut Mzd, a: *const Mzd, b: *const Mzd, cutoff: c_int) -> *mut Mzd;
+    pub fn mzd_addmul_mp(c: *mut Mzd, a: *const Mzd, b: *const Mzd, cutoff: c_int) -> *mut Mzd;
+
+    // ---- row / column utilities (`mzd.rs:130-240`): host word work ----
+    pub fn mzd_row_swap(matrix: *mut Mzd, rowa: Rci, rowb: Rci);
+    pub fn mzd_copy_row(b: *mut Mzd, i: Rci, a: *const Mzd, j: Rci);
+    pub fn mzd_col_swap(matrix: *mut Mzd, cola: Rci, colb: Rci);
+    pub fn mzd_submatrix(s: *mut Mzd, m: *const Mzd, lowr: Rci, lowc: Rci, highr: Rci, highc: Rci) -> *mut Mzd;
+    pub fn mzd_is_zero(a: *const Mzd) -> c_int;
+    pub fn mzd_row_clear_offset(m: *mut Mzd, row: Rci, coloffset: Rci);
 
     // ---- PLE / PLUQ decomposition and permutations (m4ri-sys ple.rs, mzp.rs; csrc/elim.cu) ----
     /// A = P L E in place, returns the rank; P has length nrows, Q length ncols (`ple.rs:65`).
     pub fn mzd_ple(a: *mut Mzd, p: *mut Mzp, q: *mut Mzp, cutoff: c_int) -> Rci;
     /// A = P L U Q in place, returns the rank (`ple.rs:35`).
     pub fn mzd_pluq(a: *mut Mzd, p: *mut Mzp, q: *mut Mzp, cutoff: c_int) -> Rci;
+    /// Solves (P L U Q) X = B from the packed factors and the rank `mzd_pluq` returned (`solve.rs:53`).
+    pub fn mzd_pluq_solve_left(a: *const Mzd, rank: Rci, p: *const Mzp, q: *const Mzp, b: *mut Mzd,
+                               cutoff: c_int, inconsistency_check: c_int) -> c_int;
     pub fn mzp_init(length: Rci) -> *mut Mzp;
     pub fn mzp_free(p: *mut Mzp);
     /// (`mzp.rs:26` declares no return value; the window is the returned pointer, as in M4RI.)

@@ -273,3 +273,38 @@ def test_free_rejects_foreign_descriptors(m4):
             "q.padding[9] = 0; L.mzd_free(ctypes.pointer(q))") % ROOT
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True)
     assert r.returncode != 0 and "not created by libm4ri_b200" in r.stderr
+
+
+def test_row_and_column_utilities(m4, orc):
+    """mzd_row_swap / col_swap / copy_row / is_zero / row_clear_offset / submatrix (m4ri-sys
+    mzd.rs:130-240) against numpy on unpacked bits; pure host work, no device needed."""
+    L = m4.lib()
+    for (m, n) in [(5, 7), (64, 130), (33, 257), (70, 64)]:
+        A = orc.random(m, n, 3 + n)
+        bits = orc.to_bits(A, n)
+        a = m4.mzd_from_words(A, n)
+        L.mzd_row_swap(a, 1, m - 1)
+        bits[[1, m - 1]] = bits[[m - 1, 1]]
+        L.mzd_col_swap(a, 0, n - 1)
+        bits[:, [0, n - 1]] = bits[:, [n - 1, 0]]
+        L.mzd_col_swap(a, 2, min(n - 1, 66))
+        bits[:, [2, min(n - 1, 66)]] = bits[:, [min(n - 1, 66), 2]]
+        assert (orc.to_bits(np.ascontiguousarray(m4.mzd_words(a)), n) == bits).all(), (m, n)
+        L.mzd_row_clear_offset(a, 2, n // 2)
+        bits[2, n // 2:] = 0
+        L.mzd_copy_row(a, 0, a, 3)
+        bits[0] = bits[3]
+        got = m4.mzd_words(a)
+        assert (orc.to_bits(np.ascontiguousarray(got), n) == bits).all(), (m, n)
+        assert not got[:, orc.width(n):].any()
+        assert L.mzd_is_zero(a) == 0
+        for (r0, c0, r1, c1) in [(0, 0, m, n), (1, 3, m - 1, n - 1), (2, min(n - 2, 65), m, n), (0, 1, 1, 2)]:
+            sub = L.mzd_submatrix(None, a, r0, c0, r1, c1)
+            sb = orc.to_bits(np.ascontiguousarray(m4.mzd_words(sub)), c1 - c0)
+            assert (sb == bits[r0:r1, c0:c1]).all(), (m, n, r0, c0, r1, c1)
+            assert not m4.mzd_words(sub)[:, orc.width(c1 - c0):].any()
+            L.mzd_free(sub)
+        z = L.mzd_init(m, n)
+        assert L.mzd_is_zero(z) == 1
+        L.mzd_free(z)
+        L.mzd_free(a)

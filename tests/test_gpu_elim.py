@@ -298,3 +298,77 @@ def test_apply_permutations(gpu, m4, orc):
     L.Mzp_free_window(W)
     L.mzp_free(C)
     L.mzp_free(P)
+
+
+def test_m4ri_sys_aliases(gpu, m4, orc):
+    """mzd_mul_mp / mzd_addmul_mp (mp.rs:6,8), mzd_invert_naive (mzd.rs:218) and
+    mzd_top_echelonize_m4ri (brilliantrussian.rs:199) are the GPU calls behind other names."""
+    L = m4.lib()
+    m, k, n = 700, 1300, 900
+    A, B, C0 = orc.random(m, k, 1), orc.random(k, n, 2), orc.random(m, n, 3)
+    want = orc.mul_m4rm(A, B, k, n)
+    a, b = host(m4, A, k), host(m4, B, n)
+    c = L.mzd_mul_mp(None, a, b, 0)
+    assert (m4.mzd_words(c)[:, : orc.width(n)] == want[:, : orc.width(n)]).all()
+    c0 = host(m4, C0, n)
+    L.mzd_addmul_mp(c0, a, b, 0)
+    assert (m4.mzd_words(c0)[:, : orc.width(n)] == (C0 ^ want)[:, : orc.width(n)]).all()
+    for q in (a, b, c, c0):
+        L.mzd_free(q)
+    nn = 300
+    for seed in range(40):
+        S = orc.random(nn, nn, 900 + seed)
+        inv = orc.inverse(S, nn)
+        if inv is not None:
+            break
+    s_ = host(m4, S, nn)
+    p = L.mzd_invert_naive(None, s_, None)
+    assert p and (m4.mzd_words(p)[:, : orc.width(nn)] == inv[:, : orc.width(nn)]).all()
+    E = low_rank(orc, 500, 800, 200, 11)
+    want_e, rank, _ = orc.rref(E, 800)
+    e = host(m4, E, 800)
+    assert L.mzd_top_echelonize_m4ri(e, 0) == rank
+    assert (m4.mzd_words(e)[:, : orc.width(800)] == want_e[:, : orc.width(800)]).all()
+    for q in (s_, p, e):
+        L.mzd_free(q)
+
+
+def test_pluq_solve_left(gpu, m4, orc):
+    """mzd_pluq_solve_left (solve.rs:53): solve from the packed factors mzd_pluq leaves; every
+    solution is verified by substituting it back with the oracle's product."""
+    L = m4.lib()
+    cases = [(10, 10, 3, None), (64, 64, 64, None), (300, 300, 70, None), (700, 500, 33, None), (500, 700, 129, None),
+             (900, 900, 10, 400), (1300, 1100, 65, 500), (1100, 1300, 200, 300), (2100, 2100, 1, None)]
+    for (m, n, k, rk) in cases:
+        A = orc.random(m, n, 7 + m) if rk is None else low_rank(orc, m, n, rk, 3 + n)
+        X0 = orc.random(n, k, 5 + k)
+        Bc = orc.mul_m4rm(A, X0, n, k)  # consistent by construction
+        rows = max(m, n)
+        Bfull = orc.zeros(rows, k)
+        Bfull[:m] = Bc
+        lu = host(m4, A, n)
+        P, Q = L.mzp_init(m), L.mzp_init(n)
+        r = L.mzd_pluq(lu, P, Q, 0)
+        assert r == orc.rref(A, n)[1]
+        b = host(m4, Bfull, k)
+        assert L.mzd_pluq_solve_left(lu, r, P, Q, b, 0, 1) == 0, (m, n, k, rk)
+        X = np.ascontiguousarray(m4.mzd_words(b))
+        assert not X[n:].any(), "rows beyond ncols(A) are zeroed"
+        back = orc.mul_m4rm(A, np.ascontiguousarray(X[:n]), n, k)
+        assert (back[:, : orc.width(k)] == Bc[:, : orc.width(k)]).all(), (m, n, k, rk)
+        # the same answer as mzd_solve_left gives when the solution is unique
+        if r == n:
+            assert (X[:n, : orc.width(k)] == X0[:, : orc.width(k)]).all()
+        L.mzd_free(b)
+        # an inconsistent right-hand side (rank-deficient rows): -1 and B untouched
+        if r < m:
+            Bbad = orc.random(rows, k, 99)
+            Bbad[m:] = 0
+            if orc.solve_left(A, n, np.ascontiguousarray(Bbad[:m]), k) is None:
+                bb = host(m4, Bbad, k)
+                assert L.mzd_pluq_solve_left(lu, r, P, Q, bb, 0, 1) == -1
+                assert (m4.mzd_words(bb)[:, : orc.width(k)] == Bbad[:, : orc.width(k)]).all()
+                L.mzd_free(bb)
+        L.mzd_free(lu)
+        L.mzp_free(P)
+        L.mzp_free(Q)
