@@ -72,6 +72,30 @@ struct ElimGlobal {
 
 static inline unsigned cdiv(long long a, long long b) { return (unsigned)((a + b - 1) / b); }
 
+// The 64-column steps are chains of small dependent kernels (search -> prepare -> apply, ~1 500
+// launches per elimination): they are launched with programmatic stream serialization, so that a
+// kernel's launch overlaps its predecessor's tail. Every kernel of the chain starts with
+// PDL_WAIT() — it touches nothing before the kernels ahead of it have completed and flushed — and
+// lets its successor be scheduled early with PDL_GO().
+#define PDL_WAIT() asm volatile("griddepcontrol.wait;" ::: "memory")
+#define PDL_GO() asm volatile("griddepcontrol.launch_dependents;" ::: "memory")
+template <typename... KArgs, typename... Args>
+static void launch_chained(void (*kernel)(KArgs...), unsigned grid, unsigned block, cudaStream_t s, Args... args) {
+  static const bool off = getenv("M4RI_B200_ELIM_NO_PDL") != nullptr;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(block);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = off ? 0 : 1;
+  M4B_CUDA(cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...));
+  M4B_LAUNCHED();
+}
+
 // PT[i] = [ W[i][cw0 .. cw0+bw) | 0 ... 0 ]  (words past the matrix width read as zero)
 __global__ void extract_panel_kernel(word *PT, int pstride, const word *W, int ws, int wwidth, int m, int cw0,
                                      int bw) {
@@ -106,6 +130,8 @@ __global__ void writeback_panel_kernel(word *W, int ws, int wwidth, const word *
 __global__ void __launch_bounds__(1024)
 pivot_search_kernel(const word *PT, int pstride, int j, int m, const ElimGlobal *gl, unsigned char *ispiv, int *pidx,
                     ElimState *st, int c0, word colmask /* valid columns of this word (pivot limit) */) {
+  PDL_WAIT();
+  PDL_GO();
   const int r0 = gl->rank;
   __shared__ word pw[64], sw[1024];
   __shared__ unsigned long long ctag[64], slt[1024];
@@ -304,6 +330,8 @@ __device__ __forceinline__ void step_tables(word *Tab, int L, const word *PT, in
 __global__ void __launch_bounds__(256)
 prepare_step_kernel(word *Tab, unsigned long long *mult, int L, const word *PT, int pstride, int j, int bw, int m,
                     int nrc, const ElimState *st) {
+  PDL_WAIT();
+  PDL_GO();
   __shared__ word srows[64 * RP_XW], srp[64 * RP_XW];
   __shared__ int spc[64];
   const int kp = st->kp, t = threadIdx.x;
@@ -328,6 +356,8 @@ prepare_step_kernel(word *Tab, unsigned long long *mult, int L, const word *PT, 
 __global__ void __launch_bounds__(256)
 apply_rprime_kernel(word *PT, int pstride, int j, int L, int m, const int *pidx, const unsigned long long *mult,
                     const word *__restrict__ Tab, const ElimState *st) {
+  PDL_WAIT();
+  PDL_GO();
   if (st->kp == 0) return;
   const int LW = L - j;
   const long long idx = blockIdx.x * 256LL + threadIdx.x;
@@ -489,6 +519,8 @@ __device__ __forceinline__ int lu_scan(word &w, unsigned long long &lt, int from
 __global__ void __launch_bounds__(1024)
 lu_pivot_search_kernel(const word *PT, int pstride, int j, int m, const ElimGlobal *gl, unsigned char *ispiv, int *pidx,
                        ElimState *st, int c0, word colmask) {
+  PDL_WAIT();
+  PDL_GO();
   const int r0 = gl->rank;
   __shared__ word pwcol[64], pwk[64], sw[1024];
   __shared__ unsigned long long ctcol[64], ctk[64], slt[1024];
@@ -617,6 +649,8 @@ lu_pivot_search_kernel(const word *PT, int pstride, int j, int m, const ElimGlob
 __global__ void __launch_bounds__(256)
 lu_prepare_kernel(word *Tab, int L, int bw, int nrc, word *PT, int pstride, int j, int m, const ElimGlobal *gl,
                   const unsigned char *ispiv, const int *pidx, unsigned long long *mult, const ElimState *st) {
+  PDL_WAIT();
+  PDL_GO();
   __shared__ word srows[64 * RP_XW], srp[64 * RP_XW];
   if ((int)blockIdx.x < nrc) {
     step_tables(Tab, L, PT, pstride, j + 1, bw, st, srows, srp);
@@ -849,24 +883,19 @@ static int eliminate(DMat *W, int pivot_cols, bool lu, std::vector<int> *pivots,
       const word colmask = valid == 64 ? ~(word)0 : (((word)1 << valid) - 1);
       if (lu) {
         // the word column itself is finished by lu_prepare_kernel; the rank-64 update starts right of it
-        lu_pivot_search_kernel<<<1, 1024, 0, s>>>(PT->d, pstride, j, m, gl, ispiv, pidx, st, c0, colmask);
-        M4B_LAUNCHED();
+        launch_chained(lu_pivot_search_kernel, 1, 1024, s, PT->d, pstride, j, m, gl, ispiv, pidx, st, c0, colmask);
         const int nrc = (int)cdiv(L - j - 1, RP_XW);
-        lu_prepare_kernel<<<nrc + cdiv(m, 256), 256, 0, s>>>(Rp, L, bw, nrc, PT->d, pstride, j, m, gl, ispiv, pidx, mult,
-                                                            st);
-        M4B_LAUNCHED();
-        apply_rprime_kernel<<<cdiv((long long)m * (L - j - 1), 256), 256, 0, s>>>(PT->d, pstride, j + 1, L, m, pidx,
-                                                                                 mult, Rp, st);
-        M4B_LAUNCHED();
+        launch_chained(lu_prepare_kernel, nrc + cdiv(m, 256), 256, s, Rp, L, bw, nrc, PT->d, pstride, j, m, gl, ispiv, pidx,
+                       mult, st);
+        launch_chained(apply_rprime_kernel, cdiv((long long)m * (L - j - 1), 256), 256, s, PT->d, pstride, j + 1, L, m, pidx,
+                       mult, Rp, st);
         continue;
       }
-      pivot_search_kernel<<<1, 1024, 0, s>>>(PT->d, pstride, j, m, gl, ispiv, pidx, st, c0, colmask);
-      M4B_LAUNCHED();
+      launch_chained(pivot_search_kernel, 1, 1024, s, PT->d, pstride, j, m, gl, ispiv, pidx, st, c0, colmask);
       const int nrc = (int)cdiv(L - j, RP_XW);
-      prepare_step_kernel<<<nrc + cdiv(m, 256), 256, 0, s>>>(Rp, mult, L, PT->d, pstride, j, bw, m, nrc, st);
-      M4B_LAUNCHED();
-      apply_rprime_kernel<<<cdiv((long long)m * (L - j), 256), 256, 0, s>>>(PT->d, pstride, j, L, m, pidx, mult, Rp, st);
-      M4B_LAUNCHED();
+      launch_chained(prepare_step_kernel, nrc + cdiv(m, 256), 256, s, Rp, mult, L, PT->d, pstride, j, bw, m, nrc, st);
+      launch_chained(apply_rprime_kernel, cdiv((long long)m * (L - j), 256), 256, s, PT->d, pstride, j, L, m, pidx, mult, Rp,
+                     st);
     }
     // trailing update: everything right of the block, as ONE product of fixed shape (the pivot
     // count stays on the device: rows of OP and columns of T beyond it are zero)
