@@ -576,7 +576,10 @@ static int pipeline_parts(const char *env, int dflt) {  // experiment hook: chun
   int v = e ? atoi(e) : 0;
   return v >= 1 && v <= 64 ? v : dflt;
 }
-static const size_t PIPELINE_MIN_BYTES = (size_t)24 << 20;
+static const size_t PIPELINE_MIN_BYTES = [] {
+  const char *e = getenv("M4RI_B200_PIPE_MIN_MB");  // operands (A + B) from this size on take the copy/compute pipeline
+  return (size_t)(e ? atoi(e) : 24) << 20;
+}();
 
 // Time factor of a pipeline piece for the Strassen levels it takes (profiles/r2p_rect_sweep*.jsonl):
 // the small fused level saves ~4 %, a level on big leaves ~9.5 %, two levels ~15 %.
