@@ -10,6 +10,27 @@
 
 namespace m4b {
 
+// Programmatic dependent launch for the short HBM-bound kernels (a mat-vec over 64 MiB lasts ~14 us,
+// of which ~1.5 us is launch latency and ramp): the kernel is launched with programmatic stream
+// serialization and begins with griddepcontrol.wait — it reads and writes nothing before
+// everything ahead of it in the stream has completed and flushed — so only its launch overlaps
+// the tail of its predecessor. launch_dependents lets its own successor do the same.
+#define M4B_PDL_ENTER() asm volatile("griddepcontrol.wait;\n\tgriddepcontrol.launch_dependents;" ::: "memory")
+template <typename... KArgs, typename... Args>
+static void launch_pdl(void (*kernel)(KArgs...), unsigned grid, unsigned block, cudaStream_t s, Args... args) {
+  static const bool off = getenv("M4RI_B200_NO_PDL") != nullptr;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(block);
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = off ? 0 : 1;
+  M4B_CUDA(cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...));
+}
+
 static inline unsigned cdiv(long long a, long long b) { return (unsigned)((a + b - 1) / b); }
 
 // CTAs of `kernel` (256 threads, no dynamic shared memory) that are resident on the device at
@@ -590,6 +611,7 @@ __global__ void __launch_bounds__(256)
 mul_v_coal_kernel(uint32_t *__restrict__ y, const ulonglong2 *__restrict__ A,
                   const ulonglong2 *__restrict__ x, long long m, int clear) {
   constexpr int RPI = 32 / WV;  // rows per request
+  M4B_PDL_ENTER();
   const int lane = threadIdx.x & 31;
   const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
   const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
@@ -655,6 +677,7 @@ mul_vb_rows_kernel(uint32_t *__restrict__ y, long long ys32, const ulonglong2 *_
   constexpr int RPT = 2;  // rows per thread: a warp owns 64 rows (rows base + lane and base + 32 + lane);
                           // every broadcast read of a vector word feeds two rows
   __shared__ ulonglong2 xsm[BB][WV];
+  M4B_PDL_ENTER();
   for (int i = threadIdx.x; i < BB * WV; i += 256) {
     const int q = i / WV, w = i % WV;
     xsm[q][w] = q < nb ? X[(size_t)q * xs + w] : make_ulonglong2(0, 0);
@@ -784,10 +807,10 @@ static void launch_mul_vb(uint32_t *yy, long long ys32, const DMat *A, const ulo
   if (wv <= 8 && as == wv && (wv & (wv - 1)) == 0 && (wv == 1 || !((uintptr_t)A->d & 31))) {
     const unsigned grid = cdiv(((long long)mm + 63) / 64 * 64, 512);  // 8 warps x 64 rows
     switch (wv) {
-      case 1: mul_vb_rows_kernel<1, BB><<<grid, 256, 0, s>>>(yy, ys32, AA, xx, xs, mm, nb, clear); break;
-      case 2: mul_vb_rows_kernel<2, BB><<<grid, 256, 0, s>>>(yy, ys32, AA, xx, xs, mm, nb, clear); break;
-      case 4: mul_vb_rows_kernel<4, BB><<<grid, 256, 0, s>>>(yy, ys32, AA, xx, xs, mm, nb, clear); break;
-      default: mul_vb_rows_kernel<8, BB><<<grid, 256, 0, s>>>(yy, ys32, AA, xx, xs, mm, nb, clear); break;
+      case 1: launch_pdl(mul_vb_rows_kernel<1, BB>, grid, 256, s, yy, ys32, AA, xx, xs, mm, nb, clear); break;
+      case 2: launch_pdl(mul_vb_rows_kernel<2, BB>, grid, 256, s, yy, ys32, AA, xx, xs, mm, nb, clear); break;
+      case 4: launch_pdl(mul_vb_rows_kernel<4, BB>, grid, 256, s, yy, ys32, AA, xx, xs, mm, nb, clear); break;
+      default: launch_pdl(mul_vb_rows_kernel<8, BB>, grid, 256, s, yy, ys32, AA, xx, xs, mm, nb, clear); break;
     }
   } else {
     const unsigned grid = cdiv(((long long)mm + 63) / 64 * 64, 32);  // whole 64-bit words of y
@@ -851,10 +874,10 @@ void k_mul_v(DMat *y, const DMat *A, const DMat *x, int clear, cudaStream_t s) {
       };
       timing_begin("mul_v_coal_kernel", s, ops);
       switch (wv) {
-        case 1: mul_v_coal_kernel<1, 8><<<grid_of(8, resident_ctas(mul_v_coal_kernel<1, 8>)), 256, 0, s>>>(yy, AA, xx, mm, clear); break;
-        case 2: mul_v_coal_kernel<2, 4><<<grid_of(4, resident_ctas(mul_v_coal_kernel<2, 4>)), 256, 0, s>>>(yy, AA, xx, mm, clear); break;
-        case 4: mul_v_coal_kernel<4, 2><<<grid_of(2, resident_ctas(mul_v_coal_kernel<4, 2>)), 256, 0, s>>>(yy, AA, xx, mm, clear); break;
-        default: mul_v_coal_kernel<8, 1><<<grid_of(1, resident_ctas(mul_v_coal_kernel<8, 1>)), 256, 0, s>>>(yy, AA, xx, mm, clear); break;
+        case 1: launch_pdl(mul_v_coal_kernel<1, 8>, grid_of(8, resident_ctas(mul_v_coal_kernel<1, 8>)), 256, s, yy, AA, xx, mm, clear); break;
+        case 2: launch_pdl(mul_v_coal_kernel<2, 4>, grid_of(4, resident_ctas(mul_v_coal_kernel<2, 4>)), 256, s, yy, AA, xx, mm, clear); break;
+        case 4: launch_pdl(mul_v_coal_kernel<4, 2>, grid_of(2, resident_ctas(mul_v_coal_kernel<4, 2>)), 256, s, yy, AA, xx, mm, clear); break;
+        default: launch_pdl(mul_v_coal_kernel<8, 1>, grid_of(1, resident_ctas(mul_v_coal_kernel<8, 1>)), 256, s, yy, AA, xx, mm, clear); break;
       }
       M4B_LAUNCHED();
       timing_end(s);
