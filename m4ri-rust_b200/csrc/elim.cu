@@ -583,6 +583,14 @@ lu_pivot_search_kernel(const word *PT, int pstride, int j, int m, const ElimGlob
         __syncwarp();
         if (vstop < 64) vstop = lu_scan(v, vt, vstop, pmask, colmask, pwcol, ctcol);  // pivots of earlier groups
         __syncwarp();
+        // The group's pivots stay in registers (lane l holds the l-th pivot of the group) and are
+        // published once, at the end: inside the group the smallest stop column comes first, so a
+        // lane that absorbs a pivot only scans columns ABOVE every pivot of its own group — the
+        // look-ups of lu_scan only ever hit pivots of earlier groups, which are in shared memory.
+        const int kp_g = kp;
+        word myp = 0;
+        unsigned long long myt = 0;
+        int myr = -1, myc = 0;
         for (;;) {
           const int cmin = __reduce_min_sync(0xffffffffu, vstop);
           if (cmin >= 64) break;
@@ -590,12 +598,8 @@ lu_pivot_search_kernel(const word *PT, int pstride, int j, int m, const ElimGlob
           const word pv = __shfl_sync(0xffffffffu, v, src);
           const unsigned long long pt = __shfl_sync(0xffffffffu, vt, src) ^ (1ull << kp);
           const int prow = __shfl_sync(0xffffffffu, vrow, src);
-          if (lane == 0) {
-            pwcol[cmin] = pv; ctcol[cmin] = pt; kcol[cmin] = kp;
-            pwk[kp] = pv; ctk[kp] = pt; pr[kp] = prow; pc[kp] = cmin;
-          }
+          if (lane == kp - kp_g) { myp = pv; myt = pt; myr = prow; myc = cmin; }
           pmask |= (word)1 << cmin;
-          __syncwarp();
           if (lane == src) {
             mine = kp;
             vstop = 64;
@@ -604,9 +608,14 @@ lu_pivot_search_kernel(const word *PT, int pstride, int j, int m, const ElimGlob
             vt ^= pt;
             vstop = lu_scan(v, vt, cmin + 1, pmask, colmask, pwcol, ctcol);
           }
-          __syncwarp();
           kp++;
         }
+        if (lane < kp - kp_g) {
+          const int k = kp_g + lane;
+          pwcol[myc] = myp; ctcol[myc] = myt; kcol[myc] = k;
+          pwk[k] = myp; ctk[k] = myt; pr[k] = myr; pc[k] = myc;
+        }
+        __syncwarp();
         if (mine >= 0) { ispiv[vrow] = 1; pidx[vrow] = mine + 1; }
       }
       if (lane == 0) {
