@@ -66,8 +66,9 @@ __device__ long long g_it[64];
 // every block): nothing of it is needed on the host before the very end, so the whole
 // elimination is enqueued without a host round trip.
 struct ElimGlobal {
-  int rank;   // pivots found in the blocks done so far = first candidate row of the next block
-  int moves;  // rows the current block's permutation moves
+  int rank;    // pivots found in the blocks done so far = first candidate row of the next block
+  int moves;   // rows the current block's permutation moves
+  int max_id;  // inversion: largest ORIGINAL index of a row that has served as a pivot row
 };
 
 static inline unsigned cdiv(long long a, long long b) { return (unsigned)((a + b - 1) / b); }
@@ -805,6 +806,13 @@ __global__ void tri_extract_kernel(word *dst, int ds, const word *src, int ss, i
   if (w == rw - 1 && (r & 63)) v &= ((word)1 << (r & 63)) - 1;
   dst[(size_t)i * ds + w] = v;
 }
+// Inversion ([A | I]): the right half of a row is its own identity bit plus the identity bits of
+// the pivot rows it has absorbed, so the only columns of the right half that a trailing update
+// can touch are those of rows that have been pivot rows — this records how far they reach.
+__global__ void max_pivot_id_kernel(const ElimState *st, const int *rowid, ElimGlobal *gl) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < st->kbn) atomicMax(&gl->max_id, rowid[st->blk_rows[t]]);
+}
 __global__ void iota_kernel(int *a, int n) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) a[i] = i;
@@ -835,8 +843,10 @@ static int block_width() {
 // column, rows eliminated only below and right of a pivot, multipliers left at the pivot columns;
 // d_rowid (m ints on the device, identity on entry) follows the rows through the permutations
 // and d_pivots_out (may be NULL, >= min(m, pivot_cols) + block ints) receives the pivot columns.
+// ident_col0 >= 0: columns [ident_col0, ident_col0 + m) hold the identity on entry (inversion) —
+// the trailing products then stop at the last column a pivot row can have touched.
 static int eliminate(DMat *W, int pivot_cols, bool lu, std::vector<int> *pivots, int *d_rowid, int *d_pivots_out,
-                     cudaStream_t s) {
+                     cudaStream_t s, int ident_col0 = -1) {
   const int m = W->nrows, n = W->ncols;
   if (pivots) pivots->clear();
   if (m == 0 || n == 0 || pivot_cols <= 0) return 0;
@@ -864,6 +874,13 @@ static int eliminate(DMat *W, int pivot_cols, bool lu, std::vector<int> *pivots,
   M4B_CUDA(cudaMallocAsync(&perm, (size_t)4 * B * sizeof(int), s));
   if (d_pivots_out) piv_all = d_pivots_out;
   else M4B_CUDA(cudaMallocAsync(&piv_all, (size_t)(maxrank + B) * sizeof(int), s));
+  int *own_rowid = nullptr;
+  if (ident_col0 >= 0 && !d_rowid) {
+    M4B_CUDA(cudaMallocAsync(&own_rowid, (size_t)m * sizeof(int), s));
+    iota_kernel<<<cdiv(m, 256), 256, 0, s>>>(own_rowid, m);
+    M4B_LAUNCHED();
+    d_rowid = own_rowid;
+  }
   if (d_rowid) M4B_CUDA(cudaMallocAsync(&tmpid, (size_t)2 * B * sizeof(int), s));
   // rank after every block, copied home asynchronously: the host never waits for it, it only
   // looks (two blocks late) whether the rank has reached the row count and stops enqueueing
@@ -872,8 +889,9 @@ static int eliminate(DMat *W, int pivot_cols, bool lu, std::vector<int> *pivots,
   if (h_rank_cap < nblocks + 1) {
     if (h_rank) M4B_CUDA(cudaFreeHost(h_rank));
     h_rank_cap = std::max(nblocks + 1, 1024);
-    M4B_CUDA(cudaMallocHost(&h_rank, (size_t)h_rank_cap * sizeof(int)));
+    M4B_CUDA(cudaMallocHost(&h_rank, (size_t)2 * h_rank_cap * sizeof(int)));  // second half: max_id per block
   }
+  int *h_maxid = h_rank + h_rank_cap;
   std::vector<cudaEvent_t> ev(nblocks);
   for (auto &e : ev) M4B_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   int blocks_done = 0;
@@ -909,8 +927,18 @@ static int eliminate(DMat *W, int pivot_cols, bool lu, std::vector<int> *pivots,
     // trailing update: everything right of the block, as ONE product of fixed shape (the pivot
     // count stays on the device: rows of OP and columns of T beyond it are zero)
     const int t0 = c0 + B;  // first trailing column (multiple of 128)
-    if (t0 < n) {
-      const int tw0 = t0 / 64, tw = W->width - tw0;
+    int n_end = n;          // one past the last trailing column that can change
+    if (ident_col0 >= 0 && t0 < n) {
+      // (one host round trip per block: the steps of the block must have finished anyway before
+      // its product can start, and the product it shortens is worth far more)
+      max_pivot_id_kernel<<<cdiv(B, 256), 256, 0, s>>>(st, d_rowid, gl);
+      M4B_LAUNCHED();
+      M4B_CUDA(cudaMemcpyAsync(&h_maxid[b], &gl->max_id, sizeof(int), cudaMemcpyDeviceToHost, s));
+      M4B_CUDA(cudaStreamSynchronize(s));
+      n_end = std::min(n, std::max(t0, ident_col0 + (h_maxid[b] + 1 + 127) / 128 * 128));
+    }
+    if (t0 < n_end) {
+      const int tw0 = t0 / 64, tw = width_of(n_end) - tw0;
       M4B_CUDA(cudaMemset2DAsync(OP->d, (size_t)OP->rowstride * 8, 0, (size_t)tw * 8, B, s));
       gather_pivot_rows_kernel<<<cdiv((long long)B * (tw + 1), 256), 256, 0, s>>>(OP->d, OP->rowstride, W->d, ws, tw0, tw,
                                                                                  PT->d, pstride, bw, st);
@@ -927,8 +955,8 @@ static int eliminate(DMat *W, int pivot_cols, bool lu, std::vector<int> *pivots,
         row_lb = h_rank[q] / 256 * 256;
       }
       if (row_lb < m) {
-        DMat Wt = dwin(W, row_lb, t0, m - row_lb, n - t0), Tg = dwin(PT, row_lb, B, m - row_lb, B),
-             Ot = dwin(OP, 0, 0, B, n - t0);
+        DMat Wt = dwin(W, row_lb, t0, m - row_lb, n_end - t0), Tg = dwin(PT, row_lb, B, m - row_lb, B),
+             Ot = dwin(OP, 0, 0, B, n_end - t0);
         dmul(&Wt, &Tg, &Ot, 0, M4RI_B200_ALGO_AUTO, s);
       }
     }
@@ -965,6 +993,7 @@ static int eliminate(DMat *W, int pivot_cols, bool lu, std::vector<int> *pivots,
   M4B_CUDA(cudaFreeAsync(perm, s));
   if (!d_pivots_out) M4B_CUDA(cudaFreeAsync(piv_all, s));
   if (tmpid) M4B_CUDA(cudaFreeAsync(tmpid, s));
+  if (own_rowid) M4B_CUDA(cudaFreeAsync(own_rowid, s));
   dmat_delete(PT, s);
   dmat_delete(OP, s);
   return rank;
@@ -972,6 +1001,11 @@ static int eliminate(DMat *W, int pivot_cols, bool lu, std::vector<int> *pivots,
 
 int k_rref(DMat *W, int pivot_cols, std::vector<int> *pivots, cudaStream_t s) {
   return eliminate(W, pivot_cols, false, pivots, nullptr, nullptr, s);
+}
+// The same for [A | I] with the identity starting at column ident_col0 (inversion).
+static int k_rref_identity(DMat *W, int pivot_cols, int ident_col0, cudaStream_t s) {
+  static const bool off = getenv("M4RI_B200_INV_FULL_WIDTH") != nullptr;
+  return eliminate(W, pivot_cols, false, nullptr, nullptr, nullptr, s, off ? -1 : ident_col0);
 }
 
 // PLE / PLUQ decomposition of W in place (m4ri-sys/src/ple.rs:35,65). On return, with r the rank:
@@ -1297,7 +1331,7 @@ mzd_t *mzd_inv_m4ri(mzd_t *dst, const mzd_t *src, int k) {
   DMat left = dwin(W, 0, 0, n, n);
   upload(&left, src, s);
   k_set_identity(W, n, off, s);
-  const int r = k_rref(W, n, nullptr, s);
+  const int r = k_rref_identity(W, n, off, s);
   mzd_t *out = nullptr;
   if (r == n) {
     out = dst ? dst : mzd_init_impl(n, n, 0);
