@@ -1099,6 +1099,95 @@ static mzd_t *host_matvec(mzd_t *y, const mzd_t *A, const mzd_t *x, int x_is_row
   return y;
 }
 
+// ---- small products: one copy each way ----------------------------------------------------
+// Below ~100 KiB per operand a product through the ABI is nothing but fixed costs: three pool
+// allocations with their memsets, two or three copies out of pageable memory (small matrices are
+// malloc'ed: the driver stages each of them), the excess-bit kernels, the frees. The small path
+// packs A and B (and C when accumulating) into ONE pinned staging block in the device layout
+// (excess bits masked on the way), moves it with one H2D copy into a per-thread device arena,
+// runs the usual kernels on views of the arena, brings C back with one D2H copy and unpacks it
+// into the caller's rows. Same kernels, same bits: 59-72 us -> see tools/entry_point_time.py.
+struct TinyArena {
+  int dev = -1;
+  word *d = nullptr, *h = nullptr;  // device arena / pinned staging, TINY_WORDS each
+};
+constexpr size_t TINY_OPERAND_BYTES = (size_t)96 << 10;  // per operand, in the device layout
+constexpr size_t TINY_WORDS = 3 * TINY_OPERAND_BYTES / 8;
+static thread_local TinyArena t_tiny;
+
+static size_t tiny_words(rci_t nrows, rci_t ncols) { return (size_t)nrows * dev_rowstride(ncols); }
+// rows of H -> dst in the device layout (stride words per row), bits beyond ncols cleared
+static void tiny_pack(word *dst, const mzd_t *H) {
+  const int stride = dev_rowstride(H->ncols);
+  const word hm = H->high_bitmask;
+  for (rci_t i = 0; i < H->nrows; i++) {
+    word *d = dst + (size_t)i * stride;
+    const word *src = H->rows[i];
+    for (wi_t w = 0; w + 1 < H->width; w++) d[w] = src[w];
+    if (H->width) d[H->width - 1] = src[H->width - 1] & hm;
+    for (int w = H->width; w < stride; w++) d[w] = 0;
+  }
+}
+static void tiny_unpack(mzd_t *H, const word *src) {
+  const int stride = dev_rowstride(H->ncols);
+  const word hm = H->high_bitmask;
+  const bool keep = shares_last_word(H);
+  for (rci_t i = 0; i < H->nrows; i++) {
+    const word *s_ = src + (size_t)i * stride;
+    word *d = H->rows[i];
+    for (wi_t w = 0; w + 1 < H->width; w++) d[w] = s_[w];
+    if (H->width)  // a window keeps its parent's bits; a whole matrix has zero excess bits
+      d[H->width - 1] = keep ? ((d[H->width - 1] & ~hm) | (s_[H->width - 1] & hm)) : (s_[H->width - 1] & hm);
+  }
+}
+static DMat tiny_view(word *d, rci_t nrows, rci_t ncols) {
+  DMat M;
+  M.d = d;
+  M.nrows = nrows;
+  M.ncols = ncols;
+  M.width = width_of(ncols);
+  M.rowstride = dev_rowstride(ncols);
+  M.base = nullptr;
+  return M;
+}
+static void dmul_abt(DMat *C, const DMat *A, const DMat *Bt, int clear, int algo, cudaStream_t s);
+// true when the product was done here
+static bool tiny_host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int clear, int algo, int form, int cutoff,
+                              cudaStream_t s) {
+  static const bool off = getenv("M4RI_B200_NO_TINY_PATH") != nullptr;
+  if (off || form > 1) return false;
+  const size_t wa = tiny_words(A->nrows, A->ncols), wb = tiny_words(B->nrows, B->ncols),
+               wc = tiny_words(C->nrows, C->ncols);
+  if (wa == 0 || wb == 0 || wc == 0) return false;
+  if (wa * 8 > TINY_OPERAND_BYTES || wb * 8 > TINY_OPERAND_BYTES || wc * 8 > TINY_OPERAND_BYTES) return false;
+  int dev = 0;
+  M4B_CUDA(cudaGetDevice(&dev));
+  TinyArena &T = t_tiny;
+  if (T.dev != dev) {  // first use on this thread (or the thread moved to another GPU)
+    if (T.d) {
+      (void)cudaFree(T.d);
+      (void)cudaFreeHost(T.h);
+    }
+    M4B_CUDA(cudaMalloc(&T.d, TINY_WORDS * 8));
+    M4B_CUDA(cudaMallocHost(&T.h, TINY_WORDS * 8));
+    T.dev = dev;
+  }
+  // layout: [A | B | C], every region 16-byte aligned (strides are even)
+  const size_t oa = 0, ob = wa, oc = wa + wb;
+  tiny_pack(T.h + oa, A);
+  tiny_pack(T.h + ob, B);
+  if (!clear) tiny_pack(T.h + oc, C);
+  M4B_CUDA(cudaMemcpyAsync(T.d, T.h, (clear ? oc : oc + wc) * 8, cudaMemcpyHostToDevice, s));
+  DMat dA = tiny_view(T.d + oa, A->nrows, A->ncols), dB = tiny_view(T.d + ob, B->nrows, B->ncols),
+       dC = tiny_view(T.d + oc, C->nrows, C->ncols);
+  if (form == 0) dmul(&dC, &dA, &dB, clear, algo, s, cutoff);
+  else dmul_abt(&dC, &dA, &dB, clear, algo, s);
+  M4B_CUDA(cudaMemcpyAsync(T.h + oc, T.d + oc, wc * 8, cudaMemcpyDeviceToHost, s));
+  M4B_CUDA(cudaStreamSynchronize(s));
+  tiny_unpack(C, T.h + oc);
+  return true;
+}
+
 // Shared body of the host-ABI products. form: 0 = A*B, 1 = A*Bt^T, 2 = v*A.
 static mzd_t *host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int clear, int algo, int form,
                            const char *who, int cutoff = 0) {
@@ -1140,6 +1229,7 @@ static mzd_t *host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int clear, 
     pipelined_host_product(C, A, B, clear, form, s);
     return C;
   }
+  if (tiny_host_product(C, A, B, clear, algo, form, cutoff, s)) return C;
   DMat *dA = dmat_new(A->nrows, A->ncols, s), *dB = dmat_new(B->nrows, B->ncols, s),
        *dC = dmat_new(m, n, s);
   upload(dA, A, s);
