@@ -1218,6 +1218,7 @@ static mzd_t *host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int clear, 
   //   v * A with a few rows of v (Mul<&BinMatrix> for &BinVector, binary_matrix.rs:552-563) -> mul_va
   if (m > 0 && n == 1 && k > 0 && (form == 0 || form == 1)) return host_matvec(C, A, B, form == 1, clear);
   if (form == 0 && m > 0 && m <= 4 && n > 0 && k > 0) form = 2;
+  if (m > 0 && n > 1 && k > 0 && tiny_host_product(C, A, B, clear, algo, form, cutoff, s)) return C;
   if (form != 2 && m > 0 && n > 0 && k > 0 && resolve_algo(algo, m, k, n) == M4RI_B200_ALGO_MMA &&
       ((size_t)m * A->width + (size_t)B->nrows * B->width) * 8 >= PIPELINE_MIN_BYTES) {
     const int G = multi_devices();
@@ -1229,7 +1230,6 @@ static mzd_t *host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int clear, 
     pipelined_host_product(C, A, B, clear, form, s);
     return C;
   }
-  if (tiny_host_product(C, A, B, clear, algo, form, cutoff, s)) return C;
   DMat *dA = dmat_new(A->nrows, A->ncols, s), *dB = dmat_new(B->nrows, B->ncols, s),
        *dC = dmat_new(m, n, s);
   upload(dA, A, s);
