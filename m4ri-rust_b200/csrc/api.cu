@@ -1100,7 +1100,7 @@ static mzd_t *host_matvec(mzd_t *y, const mzd_t *A, const mzd_t *x, int x_is_row
 }
 
 // ---- small products: one copy each way ----------------------------------------------------
-// Below ~100 KiB per operand a product through the ABI is nothing but fixed costs: three pool
+// Below 256 KiB per operand a product through the ABI is mostly fixed costs: three pool
 // allocations with their memsets, two or three copies out of pageable memory (small matrices are
 // malloc'ed: the driver stages each of them), the excess-bit kernels, the frees. The small path
 // packs A and B (and C when accumulating) into ONE pinned staging block in the device layout
@@ -1111,8 +1111,13 @@ struct TinyArena {
   int dev = -1;
   word *d = nullptr, *h = nullptr;  // device arena / pinned staging, TINY_WORDS each
 };
-constexpr size_t TINY_OPERAND_BYTES = (size_t)96 << 10;  // per operand, in the device layout
-constexpr size_t TINY_WORDS = 3 * TINY_OPERAND_BYTES / 8;
+constexpr size_t TINY_OPERAND_MAX = (size_t)256 << 10;   // arena: three operands of this size
+static const size_t TINY_OPERAND_BYTES = [] {             // per operand, in the device layout
+  const char *e = getenv("M4RI_B200_TINY_KB");
+  size_t kb = e ? (size_t)atoi(e) : 256;  // = the size from which mzd_init hands out pinned memory
+  return (kb > 256 ? 256 : kb) << 10;
+}();
+constexpr size_t TINY_WORDS = 3 * TINY_OPERAND_MAX / 8;
 static thread_local TinyArena t_tiny;
 
 static size_t tiny_words(rci_t nrows, rci_t ncols) { return (size_t)nrows * dev_rowstride(ncols); }
