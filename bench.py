@@ -203,7 +203,7 @@ def run_lpn(args, quick=False):
             b.record(stream)
             torch.cuda.synchronize()
             ts.append(a.elapsed_time(b))
-        return sum(ts) / len(ts)
+        return statistics.median(ts)  # (single flushed launches of 10-40 us kernels: the mean is outlier-driven)
 
     out = {"metric": "GF(2) LPN covering-code workload", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
            "data": "synthetic", "dtype": "u64", "higher_is_better": True,
