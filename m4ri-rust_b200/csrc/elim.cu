@@ -380,6 +380,48 @@ apply_rprime_kernel(word *PT, int pstride, int j, int L, int m, const int *pidx,
   *dst ^= acc;
 }
 
+// The same with two words per thread (16-byte table look-ups and a 16-byte read-modify-write of
+// the row): pairs start at the even word at or below j; a pair's first word is skipped when it
+// lies left of j.
+__global__ void __launch_bounds__(256)
+apply_rprime2_kernel(word *PT, int pstride, int j, int L, int m, const int *pidx, const unsigned long long *mult,
+                     const word *__restrict__ Tab, const ElimState *st) {
+  PDL_WAIT();
+  PDL_GO();
+  if (st->kp == 0) return;
+  const int j0 = j & ~1, LP = (L - j0) / 2;
+  const long long idx = blockIdx.x * 256LL + threadIdx.x;
+  if (idx >= (long long)m * LP) return;
+  const int i = (int)(idx / LP), w = j0 + 2 * (int)(idx % LP);
+  const int pk = pidx[i];
+  const unsigned long long mm = mult[i];
+  ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(PT + (size_t)i * pstride + w);
+  const bool first = w >= j;  // (w + 1 >= j always)
+  if (pk) {
+    const ulonglong2 t = *reinterpret_cast<const ulonglong2 *>(Tab + (size_t)(((pk - 1) >> 2) * 16 + (1 << ((pk - 1) & 3))) * L + w);
+    if (first) *dst = t;
+    else reinterpret_cast<word *>(dst)[1] = t.y;
+    return;
+  }
+  if (!mm) return;
+  const word *tp = Tab + w;
+  ulonglong2 acc = make_ulonglong2(0, 0);
+#pragma unroll
+  for (int g = 0; g < 16; g++) {
+    const ulonglong2 t = __ldg(reinterpret_cast<const ulonglong2 *>(tp + (size_t)(g * 16 + (int)((mm >> (4 * g)) & 15)) * L));
+    acc.x ^= t.x;
+    acc.y ^= t.y;
+  }
+  if (first) {
+    ulonglong2 o = *dst;
+    o.x ^= acc.x;
+    o.y ^= acc.y;
+    *dst = o;
+  } else {
+    reinterpret_cast<word *>(dst)[1] ^= acc.y;
+  }
+}
+
 // OP[t][:] = W[blk_rows[t]][tw0 .. tw0+tw) for t < kb (other rows of OP stay zero);
 // and T[blk_rows[t]] ^= e_t: a pivot row is REPLACED by its combination, i.e. it also loses itself
 __global__ void gather_pivot_rows_kernel(word *OP, int ostride, const word *W, int ws, int tw0, int tw,
@@ -853,6 +895,7 @@ static int eliminate(DMat *W, int pivot_cols, bool lu, std::vector<int> *pivots,
   if (pivot_cols > n) pivot_cols = n;
   if (((uintptr_t)W->d & 15) || (W->rowstride & 1)) die("m4ri_b200: rref needs 16-byte aligned rows\n");
   const int B = block_width(), bw = B / 64, L = 2 * bw;
+  static const bool apply2 = getenv("M4RI_B200_ELIM_APPLY1") == nullptr;  // two words per thread in the apply kernel
   DMat *PT = dmat_new(m, 2 * B, s);       // [panel | tags], stride L
   DMat *OP = dmat_new(B, n, s);           // original pivot rows of the block (trailing columns)
   const int pstride = PT->rowstride, ws = W->rowstride;
@@ -914,15 +957,23 @@ static int eliminate(DMat *W, int pivot_cols, bool lu, std::vector<int> *pivots,
         const int nrc = (int)cdiv(L - j - 1, RP_XW);
         launch_chained(lu_prepare_kernel, nrc + cdiv(m, 256), 256, s, Rp, L, bw, nrc, PT->d, pstride, j, m, gl, ispiv, pidx,
                        mult, st);
-        launch_chained(apply_rprime_kernel, cdiv((long long)m * (L - j - 1), 256), 256, s, PT->d, pstride, j + 1, L, m, pidx,
-                       mult, Rp, st);
+        if (apply2)
+          launch_chained(apply_rprime2_kernel, cdiv((long long)m * ((L - ((j + 1) & ~1)) / 2), 256), 256, s, PT->d, pstride,
+                         j + 1, L, m, pidx, mult, Rp, st);
+        else
+          launch_chained(apply_rprime_kernel, cdiv((long long)m * (L - j - 1), 256), 256, s, PT->d, pstride, j + 1, L, m,
+                         pidx, mult, Rp, st);
         continue;
       }
       launch_chained(pivot_search_kernel, 1, 1024, s, PT->d, pstride, j, m, gl, ispiv, pidx, st, c0, colmask);
       const int nrc = (int)cdiv(L - j, RP_XW);
       launch_chained(prepare_step_kernel, nrc + cdiv(m, 256), 256, s, Rp, mult, L, PT->d, pstride, j, bw, m, nrc, st);
-      launch_chained(apply_rprime_kernel, cdiv((long long)m * (L - j), 256), 256, s, PT->d, pstride, j, L, m, pidx, mult, Rp,
-                     st);
+      if (apply2)
+        launch_chained(apply_rprime2_kernel, cdiv((long long)m * ((L - (j & ~1)) / 2), 256), 256, s, PT->d, pstride, j, L, m,
+                       pidx, mult, Rp, st);
+      else
+        launch_chained(apply_rprime_kernel, cdiv((long long)m * (L - j), 256), 256, s, PT->d, pstride, j, L, m, pidx, mult, Rp,
+                       st);
     }
     // trailing update: everything right of the block, as ONE product of fixed shape (the pivot
     // count stays on the device: rows of OP and columns of T beyond it are zero)
