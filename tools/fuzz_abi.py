@@ -1,7 +1,7 @@
 """Randomised stress of the host ABI against the CPU oracle (a tool, not a test: run it on a GPU box
 for as long as you like). Every iteration draws a shape with mass on the word / tile / small-path
 boundaries and checks one product entry point (fresh and accumulating) and one consumer
-(echelon form, PLE or PLUQ identity, inverse, solve). usage: python tools/fuzz_abi.py [seconds] [seed]"""
+(echelon form, PLE or PLUQ identity, inverse, solve). usage: python tools/fuzz_abi.py [seconds] [seed] [largest dimension]"""
 import os, random, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
@@ -10,9 +10,11 @@ import oracle as orc
 L = m4.lib()
 budget = float(sys.argv[1]) if len(sys.argv) > 1 else 60.0
 rng = random.Random(int(sys.argv[2]) if len(sys.argv) > 2 else 1)
+HI = int(sys.argv[3]) if len(sys.argv) > 3 else 2600
 EDGES = [1, 2, 3, 63, 64, 65, 127, 128, 129, 255, 256, 257, 511, 512, 513, 1023, 1024, 1025, 1447, 1448, 1449, 2047, 2048, 2049]
 
-def dim(hi=2600):
+def dim(hi=None):
+    hi = hi or HI
     r = rng.random()
     if r < 0.35:
         return rng.choice(EDGES)
