@@ -930,13 +930,36 @@ static void multi_worker(MultiJob *J, int g) {
   }
   M4B_CUDA(cudaEventRecord(e_slab, t_h2d));
   int na = m > 0 ? plan_row_chunks(m, k, n, clear) : 1;
+  const bool forced = getenv("M4RI_B200_PIPE_ROWS") != nullptr;
   na = pipeline_parts("M4RI_B200_PIPE_ROWS", na);
   rci_t per = m > 0 ? ((m + na - 1) / na + 255) / 256 * 256 : 256;
   na = m > 0 ? (m + per - 1) / per : 0;
+  // chunk i = rows [cut[i], cut[i + 1])
+  std::vector<rci_t> cut;
+  if (!forced && na <= 6 && m >= 12288 && m % 1024 == 0 && k >= 32768 && !getenv("M4RI_B200_UNIFORM_CHUNKS")) {
+    // Few big chunks keep their Strassen levels but expose the first upload and the last download:
+    // a small chunk at either end (2048 rows: nothing to wait for after the exchange, a short way
+    // home at the end) around chunks as big as the levels like them (12288 rows take one level,
+    // 16384 two); a chunk's upload hides behind its predecessor's product while it has at most
+    // six times its rows (PCIe 0.16 us per 64 Ki-bit row, tensor cores ~1 us).
+    cut.push_back(0);
+    cut.push_back(2048);
+    rci_t left = m - 4096, piece = left < 12288 ? left : 12288;
+    while (left > 0) {
+      cut.push_back(cut.back() + piece);
+      left -= piece;
+      piece = left < 16384 ? left : 16384;
+    }
+    cut.push_back(m);
+  } else {
+    for (int i = 0; i < na; i++) cut.push_back(i * per);
+    cut.push_back(m);
+  }
+  na = (int)cut.size() - 1;
   std::vector<cudaEvent_t> ev(2 * na + 1);
   for (auto &e : ev) M4B_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   for (int i = 0; i < na; i++) {
-    const rci_t a0 = i * per, a1 = a0 + per < m ? a0 + per : m;
+    const rci_t a0 = cut[i], a1 = cut[i + 1];
     upload_rows(dA, &Av, a0, a1, t_h2d);
     if (!clear) upload_rows(dC, &Cv, a0, a1, t_h2d);
     M4B_CUDA(cudaEventRecord(ev[i], t_h2d));
@@ -969,7 +992,7 @@ static void multi_worker(MultiJob *J, int g) {
     if (d != g) M4B_CUDA(cudaStreamWaitEvent(s, J->e_xchg[d], 0));
   // ---- products, chunk by chunk, rows of C going home behind them ----
   for (int i = 0; i < na; i++) {
-    const rci_t a0 = i * per, a1 = a0 + per < m ? a0 + per : m;
+    const rci_t a0 = cut[i], a1 = cut[i + 1];
     DMat Ai = dwin(dA, a0, 0, a1 - a0, k), Ci = dwin(dC, a0, 0, a1 - a0, n);
     M4B_CUDA(cudaStreamWaitEvent(s, ev[i], 0));
     product_with_strassen(&Ci, &Ai, dBt, clear, M4RI_B200_ALGO_MMA, 1, 0, s);
