@@ -190,6 +190,66 @@ __device__ __forceinline__ uint32_t transpose32(uint32_t x, int lane) {
   return x;
 }
 
+// 32 x 32 bit block held by ONE thread (a[r] bit c -> a[c] bit r, LSB first): five stages of 16
+// masked block swaps, ~480 integer operations and no shuffle — the warp-wide form above costs
+// 160 shuffles and ~640 operations per block and was bound by the shuffle / shared-memory pipe
+// (46-50 % of the HBM copy rate).
+template <int J>
+__device__ __forceinline__ void transpose_stage(uint32_t (&a)[32]) {
+  constexpr uint32_t M = J == 16 ? 0x0000FFFFu : J == 8 ? 0x00FF00FFu : J == 4 ? 0x0F0F0F0Fu : J == 2 ? 0x33333333u : 0x55555555u;
+#pragma unroll
+  for (int k = 0; k < 32; k++) {
+    if ((k & J) == 0) {  // (compile-time after unrolling: the array stays in registers)
+      const uint32_t t = ((a[k] >> J) ^ a[k + J]) & M;
+      a[k + J] ^= t;
+      a[k] ^= t << J;
+    }
+  }
+}
+__device__ __forceinline__ void transpose32x32(uint32_t (&a)[32]) {
+  transpose_stage<16>(a);
+  transpose_stage<8>(a);
+  transpose_stage<4>(a);
+  transpose_stage<2>(a);
+  transpose_stage<1>(a);
+}
+
+// Thread-local form of the same tile transpose (the default; M4RI_B200_TRANSPOSE_SHFL=1 keeps the
+// shuffle form for A/B timing): thread t turns block (row-block t / 32, column word t % 32).
+__global__ void __launch_bounds__(256)
+transpose_local_kernel(uint32_t *__restrict__ D, const uint32_t *__restrict__ S, int nrows, int ncols,
+                       int sw32, int ss32, int ds32, int dw32) {
+  __shared__ uint32_t buf[256 * 33];
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  const int r0 = blockIdx.y * 256, cw0 = blockIdx.x * 32;
+#pragma unroll 8
+  for (int i = 0; i < 32; i++) {
+    const int row = i * 8 + w;
+    uint32_t v = 0;
+    if (r0 + row < nrows && cw0 + l < sw32) v = S[(size_t)(r0 + row) * ss32 + cw0 + l];
+    buf[row * 33 + l] = v;
+  }
+  __syncthreads();
+  // rows [32w, 32w + 32) of column word l: bank (i + l) % 32 — conflict-free
+  uint32_t a[32];
+#pragma unroll
+  for (int i = 0; i < 32; i++) a[i] = buf[(32 * w + i) * 33 + l];
+  transpose32x32(a);
+  __syncthreads();
+  // a[j] = word w of output row 32 l + j; out tile: 1024 rows x 8 words, every group of 32 rows
+  // skewed by one word: for a fixed j the 32 lanes write rows 32 l + j — bank (8 j + w + l) % 32
+#pragma unroll
+  for (int j = 0; j < 32; j++) buf[(32 * l + j) * 8 + l + w] = a[j];
+  __syncthreads();
+#pragma unroll 8
+  for (int i = 0; i < 32; i++) {
+    const int idx = i * 256 + threadIdx.x;
+    const int orl = idx >> 3, g = idx & 7;
+    const int orow = cw0 * 32 + orl, ow = (r0 >> 5) + g;
+    if (orow < ncols && ow < dw32) D[(size_t)orow * ds32 + ow] = buf[orl * 8 + (orl >> 5) + g];
+  }
+}
+
 __global__ void __launch_bounds__(256)
 transpose_kernel(uint32_t *__restrict__ D, const uint32_t *__restrict__ S, int nrows, int ncols,
                  int sw32, int ss32, int ds32, int dw32) {
@@ -388,8 +448,13 @@ void k_transpose(DMat *D, const DMat *A, cudaStream_t s) {
   // row blocks cover every 32-bit half of D's words, so stale bits of a reused
   // destination are overwritten with zeros (rows >= nrows read as zero)
   dim3 grid(cdiv(sw32, 32), cdiv(dw32, 8));
-  transpose_kernel<<<grid, 256, 0, s>>>((uint32_t *)D->d, (const uint32_t *)A->d, A->nrows,
-                                        A->ncols, sw32, A->rowstride * 2, D->rowstride * 2, dw32);
+  static const bool shfl = getenv("M4RI_B200_TRANSPOSE_SHFL") != nullptr;
+  if (shfl)
+    transpose_kernel<<<grid, 256, 0, s>>>((uint32_t *)D->d, (const uint32_t *)A->d, A->nrows,
+                                          A->ncols, sw32, A->rowstride * 2, D->rowstride * 2, dw32);
+  else
+    transpose_local_kernel<<<grid, 256, 0, s>>>((uint32_t *)D->d, (const uint32_t *)A->d, A->nrows,
+                                                A->ncols, sw32, A->rowstride * 2, D->rowstride * 2, dw32);
   M4B_LAUNCHED();
 }
 
