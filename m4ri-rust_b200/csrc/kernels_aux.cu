@@ -354,13 +354,16 @@ transpose_wide_kernel(TransposeDsts dsts, const uint32_t *__restrict__ S, int nr
       in[row * 33 + l] = v;
     }
     asm volatile("bar.sync %0, 256;" ::"r"(1 + half) : "memory");
-    uint32_t res[32];
+    // thread (w, l) turns the block of rows [32 w, 32 w + 32) x column word l in registers
+    // (transpose32x32: no shuffles); a[j] = word (sub*8 + w) of output row 32 l + j
+    uint32_t a[32];
 #pragma unroll
-    for (int c = 0; c < 32; c++) res[c] = transpose32(in[(32 * w + l) * 33 + c], l);
+    for (int i = 0; i < 32; i++) a[i] = in[(32 * w + i) * 33 + l];
+    transpose32x32(a);
     asm volatile("bar.sync %0, 256;" ::"r"(1 + half) : "memory");  // the input buffer may be refilled
-    // lane l of res[c] = word (sub*8 + w) of output row c*32 + l
+    // row r is stored rotated by r + r / 32 words: for a fixed j the 32 lanes (rows 32 l + j) hit 32 banks
 #pragma unroll
-    for (int c = 0; c < 32; c++) out[(c * 32 + l) * 32 + ((sub * 8 + w + l) & 31)] = res[c];
+    for (int j = 0; j < 32; j++) out[(32 * l + j) * 32 + ((sub * 8 + w + j + l) & 31)] = a[j];
   }
   __syncthreads();
 #pragma unroll 4
@@ -370,10 +373,11 @@ transpose_wide_kernel(TransposeDsts dsts, const uint32_t *__restrict__ S, int nr
     const int orow = cw0 * 32 + r, ow = (r0 >> 5) + 4 * g;
     if (orow < ncols && ow < dw32) {
       uint4 v;
-      v.x = out[r * 32 + ((4 * g + 0 + r) & 31)];
-      v.y = out[r * 32 + ((4 * g + 1 + r) & 31)];
-      v.z = out[r * 32 + ((4 * g + 2 + r) & 31)];
-      v.w = out[r * 32 + ((4 * g + 3 + r) & 31)];
+      const int rot = r + (r >> 5);
+      v.x = out[r * 32 + ((4 * g + 0 + rot) & 31)];
+      v.y = out[r * 32 + ((4 * g + 1 + rot) & 31)];
+      v.z = out[r * 32 + ((4 * g + 2 + rot) & 31)];
+      v.w = out[r * 32 + ((4 * g + 3 + rot) & 31)];
       const size_t off = (size_t)orow * ds32 + ow;
       if (ow + 4 <= dw32) {
         for (int d = 0; d < dsts.n; d++) *reinterpret_cast<uint4 *>(dsts.p[d] + off) = v;
