@@ -308,3 +308,27 @@ def test_row_and_column_utilities(m4, orc):
         assert L.mzd_is_zero(z) == 1
         L.mzd_free(z)
         L.mzd_free(a)
+
+
+def test_permutation_bookkeeping(m4):
+    """mzp_init / mzp_init_window / mzp_copy / mzp_set_ui / mzp_free (m4ri-sys/src/mzp.rs:18-36):
+    pure host bookkeeping on M4RI's published {values, length} layout — no device needed."""
+    L = m4.lib()
+    P = L.mzp_init(10)
+    assert P.contents.length == 10 and [P.contents.values[i] for i in range(10)] == list(range(10))
+    W = L.mzp_init_window(P, 3, 8)
+    assert W.contents.length == 5 and W.contents.values[0] == 3
+    W.contents.values[0] = 7  # a window shares its parent's values
+    assert P.contents.values[3] == 7
+    C = L.mzp_copy(None, P)
+    assert [C.contents.values[i] for i in range(10)] == [0, 1, 2, 7, 4, 5, 6, 7, 8, 9]
+    C.contents.values[0] = 9  # a copy does not
+    assert P.contents.values[0] == 0
+    L.mzp_set_ui(P, 1)
+    assert [P.contents.values[i] for i in range(10)] == list(range(10))
+    Z = L.mzp_init(0)
+    assert Z.contents.length == 0
+    for q in (C, Z):
+        L.mzp_free(q)
+    L.mzp_free_window(W)
+    L.mzp_free(P)
