@@ -247,6 +247,35 @@ void m4ri_b200_download(mzd_t *H, const m4ri_b200_dmat_t *D);
 /* C (^)= A*B on device, async on the current stream. algo as enum above. */
 void m4ri_b200_dmul(m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *A, const m4ri_b200_dmat_t *B,
                     int clear, int algo);
+/* C (^)= A*B on device like m4ri_b200_dmul, for callers that must not allocate. It has no
+ * counterpart in the reference (M4RI allocates its temporaries freely; m4ri-sys declares nothing
+ * like it). m4ri_b200_dmul takes B^T from the CUDA memory pool; this entry point keeps B^T in a
+ * fixed array inside the library's device image instead and calls no cudaMalloc / cudaFree /
+ * pool routine at all. It is meant for hosts whose device memory is owned by someone else (a
+ * torch program passing its tensors, a service that filled the GPU with its own matrices), where
+ * an allocation inside the library fails or takes memory the owner budgeted, and for tight
+ * loops of small products that cannot afford cudaMalloc's device-wide synchronisation.
+ *   C, A, B   device pointers to m x n, m x k, k x n bit matrices in the mzd_t packing (64-bit
+ *             words, row-major, LSB first, bits beyond ncols zero), 16-byte aligned; C must not
+ *             overlap A or B
+ *   *_rowstride  words between rows: even, >= ceil(ncols/64)
+ *   clear     non-zero: C = A*B; zero: C ^= A*B
+ *   stream    a cudaStream_t, or NULL for the calling thread's library stream (the one every
+ *             m4ri_b200_d* call uses; a thread's first such call creates it)
+ * Limit: n * roundup(ceil(k/64), 4) <= M4RI_B200_NOALLOC_SCRATCH_WORDS, i.e. B up to 8192 x 8192
+ * bits; any m. The array (8 MiB) exists on every GPU the process uses and stays until exit. No
+ * Strassen level is applied (those need temporaries), so large products run a few percent
+ * slower than m4ri_b200_dmul.
+ * The first call on each device looks up that device's copy of the array; make that call
+ * before any stream capture. All calls on one device share the array: two calls whose kernels
+ * can overlap on the GPU (different streams, no dependency between them) race on it. Calls on
+ * one stream are ordered and safe; the array is re-initialised at the start of every call.
+ * Asynchronous on `stream`. Returns 0, or without launching anything: -1 B beyond the limit,
+ * -2 misaligned operand or odd row stride, -3 negative size / NULL operand / stride below the row
+ * width (each with a message on stderr). CUDA errors abort like everywhere else in the library. */
+#define M4RI_B200_NOALLOC_SCRATCH_WORDS (1u << 20)
+int m4ri_b200_mul_noalloc(word *C, wi_t c_rowstride, const word *A, wi_t a_rowstride, const word *B,
+                          wi_t b_rowstride, rci_t m, rci_t k, rci_t n, int clear, void *stream);
 /* C (^)= A*Bt^T on device (both operands k-contiguous). */
 void m4ri_b200_dmul_abt(m4ri_b200_dmat_t *C, const m4ri_b200_dmat_t *A,
                         const m4ri_b200_dmat_t *Bt, int clear, int algo);

@@ -115,6 +115,7 @@ def lib():
         "m4ri_b200_upload": (None, [vp, MzdP]), "m4ri_b200_download": (None, [MzdP, vp]),
         "m4ri_b200_dmul": (None, [vp, vp, vp, i, i]),
         "m4ri_b200_dmul_abt": (None, [vp, vp, vp, i, i]),
+        "m4ri_b200_mul_noalloc": (i, [vp, i, vp, i, vp, i, i, i, i, i, vp]),
         "m4ri_b200_dmul_abt_fp4_debug": (None, [vp, vp, vp, vp, i]),
         "m4ri_b200_dmul_v": (None, [vp, vp, vp, i]),
         "m4ri_b200_dmul_va": (None, [vp, vp, vp, i]),

@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libm4ri_b200.so")
-SOURCES = ["api.cu", "elim.cu", "kernels_aux.cu", "kernels_m4rm.cu", "kernels_mma.cu", "kernels_mma2.cu", "kernels_mma4.cu", "kernels_mma5.cu", "kernels_mma6.cu", "mzd_host.cpp"]
+SOURCES = ["api.cu", "elim.cu", "kernels_aux.cu", "kernels_m4rm.cu", "kernels_mma.cu", "kernels_mma2.cu", "kernels_mma4.cu", "kernels_mma5.cu", "kernels_mma6.cu", "noalloc.cu", "mzd_host.cpp"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",
