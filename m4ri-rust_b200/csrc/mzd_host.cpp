@@ -253,12 +253,16 @@ mzd_t *mzd_concat(mzd_t *C, const mzd_t *A, const mzd_t *B) {
     die("m4ri_b200: mzd_concat: C has wrong dimension\n");
   for (rci_t i = 0; i < A->nrows; i++) {
     word *dst = C->rows[i];
+    if (!C->width) continue;
+    // C may be a window whose last word also holds columns of its parent: those bits stay
+    const word foreign = dst[C->width - 1] & ~C->high_bitmask;
     memset(dst, 0, sizeof(word) * (size_t)C->width);
     if (A->width) {
       memcpy(dst, A->rows[i], sizeof(word) * (size_t)A->width);
       dst[A->width - 1] &= A->high_bitmask;
     }
     if (B->width) append_bits(dst, A->ncols, B->rows[i], B->ncols, B->high_bitmask);
+    dst[C->width - 1] |= foreign;
   }
   return C;
 }
@@ -273,8 +277,11 @@ mzd_t *mzd_stack(mzd_t *C, const mzd_t *A, const mzd_t *B) {
     const mzd_t *S = i < A->nrows ? A : B;
     const word *src = S->rows[i < A->nrows ? i : i - A->nrows];
     if (!C->width) continue;
-    memcpy(C->rows[i], src, sizeof(word) * (size_t)C->width);
-    C->rows[i][C->width - 1] &= C->high_bitmask;
+    word *dst = C->rows[i];
+    const wi_t l = C->width - 1;
+    const word last = (dst[l] & ~C->high_bitmask) | (src[l] & C->high_bitmask);  // a window's parent keeps its bits
+    memcpy(dst, src, sizeof(word) * (size_t)l);
+    dst[l] = last;
   }
   return C;
 }

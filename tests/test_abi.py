@@ -265,6 +265,32 @@ def test_concat_and_stack(m4):
             L.mzd_free(p)
 
 
+def test_concat_and_stack_into_a_window_keep_the_parents_bits(m4):
+    """C may be a window (mzd.rs:121-127) that ends inside a word of its parent: the parent's
+    columns in that word, and everything outside the window, survive."""
+    L = m4.lib()
+    for (r, ca, cb) in [(6, 30, 40), (5, 64, 1), (4, 100, 27)]:
+        n = ca + cb
+        for op in ("concat", "stack"):
+            parent = L.mzd_init(r + 4, 64 + n + 50)
+            L.mzd_randomize(parent)
+            before = _bits(m4, parent)
+            win = L.mzd_init_window(parent, 2, 64, 2 + r, 64 + n)
+            if op == "concat":
+                a, b = L.mzd_init(r, ca), L.mzd_init(r, cb)
+            else:
+                a, b = L.mzd_init(2, n), L.mzd_init(r - 2, n)
+            L.mzd_randomize(a)
+            L.mzd_randomize(b)
+            (L.mzd_concat if op == "concat" else L.mzd_stack)(win, a, b)
+            want = before.copy()
+            want[2:2 + r, 64:64 + n] = np.concatenate([_bits(m4, a), _bits(m4, b)], axis=1 if op == "concat" else 0)
+            assert (_bits(m4, parent) == want).all(), (op, r, ca, cb)
+            L.mzd_free(win)
+            for p in (a, b, parent):
+                L.mzd_free(p)
+
+
 def test_free_rejects_foreign_descriptors(m4):
     """A descriptor this library did not create (e.g. from another M4RI in the process) must not
     reach free()/cudaFreeHost: mzd_free dies loudly instead."""
