@@ -877,6 +877,20 @@ static int block_width() {
 
 }  // namespace
 
+// Non-blocking "has this event happened yet". The host runs ahead of the device here, so
+// cudaErrorNotReady is the usual answer; it is not a failure, and it must not stay behind as the
+// thread's last error for the next M4B_LAUNCHED() to find.
+static bool event_done(cudaEvent_t e) {
+  const cudaError_t r = cudaEventQuery(e);
+  if (r == cudaSuccess) return true;
+  if (r == cudaErrorNotReady) {
+    (void)cudaGetLastError();
+    return false;
+  }
+  M4B_CUDA(r);
+  return false;
+}
+
 // Reduced row echelon form of W in place, pivots searched in columns [0, pivot_cols) only (the
 // rest is carried along: the right-hand side of a solve, the identity of an inversion).
 // Returns the rank; pivots (if given) receives the pivot columns in increasing order.
@@ -939,7 +953,7 @@ static int eliminate(DMat *W, int pivot_cols, bool lu, std::vector<int> *pivots,
   for (auto &e : ev) M4B_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   int blocks_done = 0;
   for (int b = 0, c0 = 0; c0 < pivot_cols; b++, c0 += B) {
-    if (b >= 2 && cudaEventQuery(ev[b - 2]) == cudaSuccess && h_rank[b - 2] >= m) break;  // every row is a pivot row
+    if (b >= 2 && event_done(ev[b - 2]) && h_rank[b - 2] >= m) break;  // every row is a pivot row
     const int cw0 = c0 / 64;
     const int bcols = std::min(B, pivot_cols - c0);            // columns of this block that may hold pivots
     const int steps = (bcols + 63) / 64;
@@ -1002,7 +1016,7 @@ static int eliminate(DMat *W, int pivot_cols, bool lu, std::vector<int> *pivots,
       if (lu && b >= 3) {
         M4B_CUDA(cudaEventSynchronize(ev[b - 3]));
         int q = b - 3;
-        while (q + 1 < b && cudaEventQuery(ev[q + 1]) == cudaSuccess) q++;
+        while (q + 1 < b && event_done(ev[q + 1])) q++;
         row_lb = h_rank[q] / 256 * 256;
       }
       if (row_lb < m) {
