@@ -187,7 +187,7 @@ void m4ri_b200_set_sm_limit(int sms);
  * mzd_mul/mzd_addmul/_mzd_mul_naive on host operands is cut into n row-blocks of A and C, one per
  * GPU of this process (devices 0..n-1), each running the copy/compute pipeline on its block over
  * its own PCIe link; the blocks are independent (no collective). get returns the effective count
- * (clamped to the devices present). */
+ * (clamped to the devices present, and to 8). */
 void m4ri_b200_set_devices(int n);
 int m4ri_b200_get_devices(void);
 /* Block plan the host-ABI products use to overlap PCIe copies with the kernels on an

@@ -777,8 +777,11 @@ static void pipelined_host_product(mzd_t *C, const mzd_t *A, const mzd_t *B, int
 // behind a C ABI should do; no launcher") ---------------------------------------------------
 // m4ri_b200_set_devices(G) / M4RI_B200_DEVICES=G: a large host product is cut into G row-blocks
 // of A and C; a resident worker thread per GPU runs the copy/compute pipeline above on its
-// block — its rows of A, all of B, over its own PCIe link — and writes its rows of C. No
-// collective and no peer access: the blocks are independent. One multi-GPU call at a time.
+// block — its rows of A over its own PCIe link — and writes its rows of C. B travels once when
+// every pair of the GPUs is peer-capable (slab g over GPU g's link, then a transposing scatter
+// over NVLink into every GPU's copy of B^T, multi_worker below); otherwise every GPU uploads all
+// of B itself and the blocks are fully independent. One multi-GPU call at a time.
+constexpr int MULTI_MAX = 8;            // GPUs one call may span (MultiJob's per-GPU arrays, scatter fan-out)
 static std::atomic<int> g_devices{-1};  // -1: not decided yet (environment)
 
 static int multi_devices() {
@@ -790,6 +793,7 @@ static int multi_devices() {
     g_devices.store(g);
   }
   std::call_once(g_once, probe);
+  if (g > MULTI_MAX) g = MULTI_MAX;  // a box with more visible GPUs still uses the first eight
   return g < g_ndev ? g : (g_ndev > 0 ? g_ndev : 1);
 }
 
@@ -848,8 +852,8 @@ struct MultiJob {
   mzd_t *C = nullptr;
   const mzd_t *A = nullptr, *B = nullptr;
   rci_t per = 0, slab = 0;  // rows of A/C per GPU; rows of B (form 0) or of Bt (form 1) per GPU
-  DMat *dBt[8] = {};
-  cudaEvent_t e_alloc[8] = {}, e_xchg[8] = {};
+  DMat *dBt[MULTI_MAX] = {};
+  cudaEvent_t e_alloc[MULTI_MAX] = {}, e_xchg[MULTI_MAX] = {};
   HostBarrier bar;
 };
 
@@ -971,8 +975,8 @@ static void multi_worker(MultiJob *J, int g) {
     if (d != g) M4B_CUDA(cudaStreamWaitEvent(s, J->e_alloc[d], 0));
   if (s1 > s0) {
     if (form == 0) {
-      DMat wins[8];
-      DMat *dst[8];
+      DMat wins[MULTI_MAX];
+      DMat *dst[MULTI_MAX];
       for (int d = 0; d < J->used; d++) {
         wins[d] = dwin(J->dBt[d], 0, s0, n, s1 - s0);  // columns [s0, s1) of Bt: 128-byte aligned (slabs of 1024 rows)
         dst[d] = &wins[d];
