@@ -102,10 +102,23 @@ class ShardedMul:
                 self.chunk_product(i, k0, k1, i == 0)
 
 
+def release_stream(m4):
+    """Hand the calling thread's library work back to the library's own stream.
+
+    exchange() / step() and the product of gpu_chunk_product() bind the thread's library stream to
+    torch's current stream (m4ri_b200_set_stream) and leave it bound: the next step needs the same
+    binding, and the caller's own device-API calls between steps (checksums, Freivalds) must stay
+    ordered behind the product. The binding outlives the step, so a caller that is about to destroy
+    that torch stream, or that goes on to use the host ABI (mzd_mul ...) expecting the library's own
+    stream, calls this first."""
+    m4.lib().m4ri_b200_use_own_stream()
+
+
 def gpu_chunk_product(m4, tA, tB, tC, rows, k, n, algo=0):
     """chunk_product for resident torch tensors on the current CUDA device: windows of
     A_block (columns k0:k1) and of B (rows k0:k1) wrapped as device matrices, product by
-    libm4ri_b200 on torch's current stream."""
+    libm4ri_b200 on torch's current stream. Side effect: the thread's library stream stays bound to
+    that torch stream afterwards (release_stream undoes it)."""
     sa, sb, sc = tA.stride(0), tB.stride(0), tC.stride(0)
     dC = m4.DMat.wrap(tC.data_ptr(), rows, n, sc, keepalive=tC)
     cache = {}
@@ -239,7 +252,9 @@ class FusedBroadcastMul:
                 self.pieces.append((dSrc, (ctypes.c_void_p * len(dDst))(*[d.h for d in dDst]), len(dDst), copy))
 
     def exchange(self):
-        """Distribute the root's B: afterwards every rank's Bt holds all of B transposed."""
+        """Distribute the root's B: afterwards every rank's Bt holds all of B transposed.
+        Side effect: the thread's library stream stays bound to torch's current stream
+        (release_stream undoes it)."""
         # the symmetric-memory barriers run on torch's current stream: the library must issue the
         # scatter and the product on that same stream or the barriers order nothing
         import ctypes
