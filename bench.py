@@ -361,9 +361,16 @@ def also_measured(args):
         L.m4ri_b200_synchronize()
         tp.append((time.perf_counter() - t0) * 1e3)
     ok_ple = bool(rp == rank and list(Q)[:rp] == [int(c) for c in piv])
+    try:  # the packed factors must stand for the input: P * L * E == A (what smoke() checks at 700 x 900)
+        back = oracle.ple_reconstruct(np.ascontiguousarray(W.to_words()), n, rp, list(P), list(Q))
+        ok_ple_identity = bool((back[:, :w] == A[:, :w]).all())
+    except AssertionError:
+        ok_ple_identity = False
     out["elimination_8192"] = {"rref_ms": min(ts), "ple_ms": min(tp), "rank": int(r),
-                               "rref_equals_cpu_oracle": ok_rref, "ple_rank_and_pivot_columns_equal_cpu_oracle": ok_ple}
-    return out  # (a mismatch is reported in the flags above: the summary never costs the run its headline line)
+                               "rref_equals_cpu_oracle": ok_rref, "ple_rank_and_pivot_columns_equal_cpu_oracle": ok_ple,
+                               "ple_p_l_e_equals_a": ok_ple_identity}
+    out["ok"] = bool(ok_rref and ok_ple and ok_ple_identity and lpn["product"]["auto"]["freivalds"])
+    return out  # (main() prints the line first and then fails the run when ok is false)
 
 
 def main():
@@ -393,7 +400,7 @@ def main():
     n = args.n or (32768 if world == 1 else 65536)
     workload = f"square mzd_mul n={n} random" + (
         "" if world == 1 else f", C/A row-blocks sharded over {world} ranks, B of rank 0 distributed every step: "
-        + ("exchange fused into the transpose (plan in config.exchange_plan)"
+        + ("exchange fused into the transpose (plan in the line's exchange_plan)"
            if args.exchange == "fused" else
            f"NCCL broadcast in k-chunks ({args.chunks}) overlapped with the product; the product leaves {args.reserve} SMs to NCCL while a chunk is in flight"))
     config = {"workload": workload, "m": n, "k": n, "n": n, "algo": args.algo,
@@ -409,7 +416,7 @@ def main():
             return
         steps, warmup = args.steps, args.warmup
         r = cpu_arm(n, n, steps, warmup, target_s=30.0)
-        config = dict(config, cpu_threads=r["cores"], cpu_sample=r["sample"])
+        # (threads and sample live under cpu_baseline: `config` stays word for word the product arm's)
         line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": "Tbit-op/s",
                 "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": r["ms_per_step"],
                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u64",
@@ -442,12 +449,13 @@ def main():
     r0, rows = sharded.row_block(n, world, rank)
     ws = n // 64  # words per row (n % 128 == 0 so device stride == width)
     fused = world > 1 and args.exchange == "fused"
+    exchange_plan = None
     if fused:
         # exchange fused into the transpose: each rank transposes one k-slab of the root's B over
         # NVLink and stores it into every rank's Bt (peer stores); one product launch per step
         fm = sharded.FusedBroadcastMul(m4, n, n, n, dist, src=0)
         tA, tB, tC, dA, dB, dC = fm.tA, fm.tB, fm.tC, fm.dA, fm.dB, fm.dC
-        config["exchange_plan"] = {
+        exchange_plan = {
             "mc_root": "mc_root: the root transposes its B in one kernel whose stores go to the NVSwitch multicast mapping of the symmetric Bt buffer: one store per 16 bytes reaches every GPU (root egress |B|, no remote reads)",
             "mc_slabs": "mc_slabs: every rank transposes one k-slab of the root's B (read over NVLink) and stores it to the multicast mapping of Bt",
             "peer": "peer: every rank transposes one k-slab of the root's B (read over NVLink; root_serves=%s, pulled in %d pieces by the copy engine) and stores it into every rank's Bt with peer stores" % (fm.root_serves, fm.chunks),
@@ -665,6 +673,8 @@ def main():
             "clocks": clocks, "gpu_launches": int(launches), "roofline": roof,
             "parity": {"freivalds_2^-64": True, "checksum_rank0": f"{chk:016x}"},
             "step_ms_rank0": [round(x, 3) for x in step_ms]}
+    if exchange_plan:
+        line["exchange_plan"] = exchange_plan  # beside config, not in it: both arms print one config
     if e2e_ms is not None:
         line["e2e"] = {"value": total_ops / (e2e_max * 1e-3) / 1e12, "unit": "Tbit-op/s",
                        "ms_per_step": e2e_max, "h2d_bytes_per_step": e2e_bytes[0],
@@ -690,9 +700,15 @@ def main():
             line["also_measured"] = also_measured(args)
         except Exception as ex:  # the summary is an extra: it must never take the headline line with it
             line["also_measured"] = {"error": f"{type(ex).__name__}: {ex}"}
-    print(json.dumps(line))
+    # a wrong result of an extra must not be published as a timing with a nested false flag: the
+    # headline line is still printed (its own parity block stands), then the run fails
+    extras_ok = line.get("also_measured", {}).get("ok", True)
+    line["ok"] = bool(extras_ok)
+    print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
+    if not extras_ok:
+        raise SystemExit("bench.py: an also_measured result differs from the CPU oracle (see the flags in the line)")
 
 
 if __name__ == "__main__":

@@ -44,7 +44,8 @@ def test_reference_arm_ignores_torchrun_thread_cap():
     capped = json.loads(run({"OMP_NUM_THREADS": "1", "RANK": "0", "LOCAL_RANK": "0", "WORLD_SIZE": "2"}).splitlines()[-1])
     cores = len(os.sched_getaffinity(0))
     assert free["cpu_baseline"]["cores"] == capped["cpu_baseline"]["cores"] == cores
-    assert capped["config"]["cpu_threads"] == cores
+    # `config` carries what the product arm's carries and nothing else (same_config)
+    assert set(capped["config"]) == set(free["config"]) == {"workload", "m", "k", "n", "algo", "l2"}
     for k in ("strassen", "m4rm"):
         assert free["cpu_baseline"]["strategies"][k]["sample"] == capped["cpu_baseline"]["strategies"][k]["sample"]
     if cores > 1:  # a one-thread run would be several times slower
