@@ -663,6 +663,55 @@ def test_fp4_accumulators_exact_on_dense_operands(gpu, m4, orc):
         L.mzd_free(b)
 
 
+@pytest.mark.parametrize("k", [32768, 65536])
+def test_fp4_accumulators_lone_quarter_worst_case(gpu, m4, k):
+    """VERDICT r2 (weak 3): the deterministic worst case for alignment loss in the fp32 accumulator
+    — a sum that is already as large as the contraction allows and then receives ONE 0.25, and the
+    mirror image (the lone 0.25 first, everything else on top). Row r < 64 of A is all ones up to
+    the last 64-bit word, which holds the single bit r; row 64 + r holds the single bit r in its
+    FIRST word and all ones after it; rows 128.. repeat both with the full words cut at k/2 (a
+    lone quarter on either side of the kernel's k-chunk boundary). B is all ones, and all ones
+    with one hole per row. Raw accumulators (debug entry) and the default kernels' parities are
+    compared with exact integer arithmetic."""
+    import torch
+    L = m4.lib()
+    kw = k // 64
+    ones = np.uint64(0xFFFFFFFFFFFFFFFF)
+    A = np.zeros((256, kw), dtype=np.uint64)
+    for r in range(64):
+        bit = np.uint64(1) << np.uint64(r)
+        A[r, : kw - 1], A[r, kw - 1] = ones, bit              # 8176.0 (k = 32768) ... then 0.25
+        A[64 + r, 1:], A[64 + r, 0] = ones, bit               # 0.25 ... then the rest
+        A[128 + r, : kw // 2], A[128 + r, kw - 1] = ones, bit
+        A[192 + r, kw // 2:], A[192 + r, 0] = ones, bit
+    B = np.full((256, kw), ones)
+    holes = np.random.default_rng(k).integers(0, k, size=128)
+    for j, h in enumerate(holes):
+        B[128 + j, h // 64] ^= np.uint64(1) << np.uint64(h % 64)
+    a8 = np.unpackbits(A.view(np.uint8), axis=1, bitorder="little").astype(np.float64)
+    b8 = np.unpackbits(B.view(np.uint8), axis=1, bitorder="little").astype(np.float64)
+    pc = a8 @ b8.T  # exact in float64
+    assert pc.max() == k - 63 and (pc[:128, :128] == k - 63).all()
+    a, b = host(m4, A, k), host(m4, B, k)
+    dA, dB, dC = m4.DMat.from_host(a), m4.DMat.from_host(b), m4.DMat.init(256, 256)
+    for cg in (1, 2):
+        acc = torch.full((256, 256), -1.0, dtype=torch.float32, device="cuda")
+        torch.cuda.synchronize()
+        L.m4ri_b200_dmul_abt_fp4_debug(dC.h, dA.h, dB.h, acc.data_ptr(), cg)
+        L.m4ri_b200_synchronize()
+        assert (acc.cpu().numpy().astype(np.float64) * 4 == pc).all(), cg
+    want = np.packbits((pc.astype(np.int64) & 1).astype(np.uint8), axis=1, bitorder="little").view(np.uint64)
+    for variant in ("fp4s256", "fp4s256cg1", "fp4ldg", "fp4"):
+        L.m4ri_b200_set_mma_variant(m4.MMA_VARIANTS[variant])
+        try:
+            m4.dmul_abt(dC, dA, dB, clear=True, algo=m4.ALGO_MMA)
+            assert (dC.to_words()[:, :4] == want).all(), variant
+        finally:
+            L.m4ri_b200_set_mma_variant(0)
+    L.mzd_free(a)
+    L.mzd_free(b)
+
+
 def test_n65536_single_gpu(gpu, m4):
     """configs[3] on ONE GPU: n = 65536 through m4ri_b200_dmul AUTO — the plan with TWO Strassen
     levels (api.cu strassen_levels: leaves of 16384) — checked with Freivalds (2^-64), against the
