@@ -100,6 +100,12 @@ def host_threads():
         return max(1, os.cpu_count() or 1)
 
 
+def block_digest(words):
+    """Digest of a block of result rows (valid words only), for comparing results across ranks."""
+    import hashlib
+    return hashlib.blake2b(np.ascontiguousarray(words).tobytes(), digest_size=16).hexdigest()
+
+
 def cpu_arm(n, m_total, steps, warmup, target_s=12.0, budget_s=600.0, strassen_n=None):
     """CPU arm on the box's host cores, both strategies of the reference's `mul_impl!`
     (m4ri-rust/src/friendly/binary_matrix.rs:53-95), all host threads:
@@ -541,8 +547,13 @@ def main():
     # host (a store key, not an NCCL kernel that would sit on their SMs).
     e2e_ms = None
     e2e_bytes = (0, 0)
+    parity_extra = {}
+    n1_same_size_ms = None
     if not args.no_e2e:
         store = dist.distributed_c10d._get_default_store() if dist is not None else None
+        my_digest = block_digest(dC.to_words()[:, :ws])
+        if store is not None:
+            store.set(f"m4ri_b200_block_{rank}", f"{r0}:{rows}:{my_digest}")
         barrier()
         if rank == 0:
             if world > 1:
@@ -573,11 +584,59 @@ def main():
             L.m4ri_b200_set_devices(1)
             L.m4ri_b200_set_algo(0)
             L.m4ri_b200_set_stream(ctypes.c_void_p(stream.cuda_stream))
-            # the rows this rank also computed device-resident must be the same words
-            mine = m4.mzd_words(hC)[r0:r0 + rows]
-            step_ = max(1, rows // 64)
-            if not bool((mine[::step_] == dC.to_words()[::step_]).all()):
-                raise SystemExit("bench.py: host-ABI result differs from the device-resident result")
+            # The WHOLE result of the one host call against (1) the block every rank computed
+            # device-resident in the timed steps (each Freivalds-checked above) and (2) the CPU
+            # oracle's checksum of this seeded product (tests/golden/full_size_checksums.json)
+            import oracle
+            words = m4.mzd_words(hC)
+            blocks = [(r0, rows, my_digest)] if store is None else [
+                (int(a), int(b), c) for a, b, c in (store.get(f"m4ri_b200_block_{i}").decode().split(":") for i in range(world))]
+            if sum(b for _, b, _ in blocks) != n:
+                raise SystemExit("bench.py: the ranks' row-blocks do not cover the result")
+            for i, (b0, brows, dig) in enumerate(blocks):
+                if block_digest(words[b0:b0 + brows, :ws]) != dig:
+                    raise SystemExit(f"bench.py: host-ABI result differs from rank {i}'s device-resident block (rows {b0}..{b0 + brows})")
+            parity_extra["e2e_equals_every_ranks_block"] = True
+            full = f"{oracle.checksum(np.ascontiguousarray(words[:, :ws]), n):016x}"
+            parity_extra["checksum_all_ranks"] = full
+            golden = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "tests", "golden", "full_size_checksums.json")))
+            if str(n) in golden:
+                parity_extra["equals_cpu_oracle_full_size"] = full == golden[str(n)]["checksum"]
+                if full != golden[str(n)]["checksum"]:
+                    raise SystemExit("bench.py: the full result's checksum differs from the committed CPU-oracle checksum")
+            if world > 1:
+                # GPUTEST only ever sees one GPU: one ragged multi-device product, fresh and accumulating,
+                # against the CPU oracle, inside every N > 1 line
+                L.m4ri_b200_set_devices(world)
+                L.m4ri_b200_use_own_stream()
+                rm, rk, rn = 5000, 20000, 9000
+                rA, rB, rC0 = oracle.random(rm, rk, 21), oracle.random(rk, rn, 22), oracle.random(rm, rn, 23)
+                want = oracle.mul_m4rm(rA, rB, rk, rn, threads=0)[:, : oracle.width(rn)]
+                ra, rb, rc = m4.mzd_from_words(rA, rk), m4.mzd_from_words(rB, rn), m4.mzd_from_words(rC0, rn)
+                fresh = L.mzd_mul(None, ra, rb, 0)
+                L.mzd_addmul(rc, ra, rb, 0)
+                ok_r = bool((m4.mzd_words(fresh)[:, : oracle.width(rn)] == want).all() and
+                            (m4.mzd_words(rc)[:, : oracle.width(rn)] == (rC0[:, : oracle.width(rn)] ^ want)).all())
+                parity_extra["ragged_multi_device_5000x20000x9000"] = ok_r
+                for p_ in (ra, rb, rc, fresh):
+                    L.mzd_free(p_)
+                L.m4ri_b200_set_devices(1)
+                L.m4ri_b200_set_stream(ctypes.c_void_p(stream.cuda_stream))
+                if not ok_r:
+                    raise SystemExit("bench.py: ragged multi-device product differs from the CPU oracle")
+                # the same-size one-GPU step (strong-scaling denominator): the N = 1 step (m4ri_b200_dmul
+                # on resident operands) at THIS n on rank 0's GPU alone, 1 warm-up + 3 timed
+                dA1, dB1, dC1 = m4.DMat.init(n, n).fill_random(SEED_A), m4.DMat.init(n, n).fill_random(SEED_B), m4.DMat.init(n, n)
+                m4.dmul(dC1, dA1, dB1, clear=True, algo=algo)
+                ev1 = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+                ev1[0].record(stream)
+                for i in range(3):
+                    m4.dmul(dC1, dA1, dB1, clear=True, algo=algo)
+                    ev1[i + 1].record(stream)
+                torch.cuda.synchronize()
+                parity_extra["n1_same_size_checksum_equal"] = f"{dC1.checksum():016x}" == full
+                n1_same_size_ms = ev1[0].elapsed_time(ev1[3]) / 3
+                del dA1, dB1, dC1
             e2e_bytes = (2 * n * ws * 8 if world > 1 else (rows * ws + n * ws) * 8, (n if world > 1 else rows) * ws * 8)
             for p in (hA, hB, hC):
                 L.mzd_free(p)
@@ -673,6 +732,9 @@ def main():
             "clocks": clocks, "gpu_launches": int(launches), "roofline": roof,
             "parity": {"freivalds_2^-64": True, "checksum_rank0": f"{chk:016x}"},
             "step_ms_rank0": [round(x, 3) for x in step_ms]}
+    line["parity"].update(parity_extra)
+    if n1_same_size_ms is not None:
+        line["n1_same_size_ms"] = n1_same_size_ms  # one GPU, same n: ms_per_step * n_gpus / this = strong-scaling efficiency
     if exchange_plan:
         line["exchange_plan"] = exchange_plan  # beside config, not in it: both arms print one config
     if e2e_ms is not None:
