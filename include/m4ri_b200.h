@@ -116,7 +116,11 @@ mzd_t *mzd_mul_v(mzd_t *y, const mzd_t *A, const mzd_t *x);
 /* ---- consumers of the product: blocked Gauss-Jordan on the GPU whose trailing
  * update is one accumulating product per column block (csrc/elim.cu) ---------------------------- */
 /* (Reduced) row echelon form in place, returns the rank. The REDUCED form is returned for either
- * value of `full` (it is an upper triangular form, and unlike that one it is unique). */
+ * value of `full` (it is an upper triangular form, and unlike that one it is unique).
+ * DIFFERS FROM M4RI: with full = 0 M4RI stops at an upper triangular form and leaves the entries
+ * above the pivots as they fall; a caller that relied on exactly those entries sees different (still
+ * valid echelon) rows here. m4ri-rust only ever reads the rank or passes full = 1
+ * (binary_matrix.rs:247-261), so it cannot tell. */
 rci_t mzd_echelonize(mzd_t *A, int full);               /* echelonform.rs:16 (BinMatrix::echelonize/rank, binary_matrix.rs:247-261) */
 rci_t mzd_echelonize_pluq(mzd_t *A, int full);          /* echelonform.rs:27 */
 rci_t mzd_echelonize_m4ri(mzd_t *A, int full, int k);   /* echelonform.rs:36 */
@@ -125,7 +129,10 @@ rci_t mzd_top_echelonize_m4ri(mzd_t *A, int k);         /* brilliantrussian.rs:1
 mzd_t *mzd_inv_m4ri(mzd_t *dst, const mzd_t *src, int k); /* brilliantrussian.rs:208 (BinMatrix::inverted, binary_matrix.rs:264-268) */
 mzd_t *mzd_invert_naive(mzd_t *inv, const mzd_t *A, const mzd_t *identity); /* mzd.rs:218 (identity is not needed) */
 /* Solves A X = B, X stored in the first ncols(A) rows of B (free variables zero, other rows of B
- * zeroed); 0 = solved, -1 = inconsistent (B untouched). A is left as it was. */
+ * zeroed); 0 = solved, -1 = inconsistent (B untouched). A is left as it was.
+ * DIFFERS FROM M4RI: M4RI factors in place and returns with A overwritten by its PLUQ factors;
+ * here A is only read. m4ri-rust clones A before the call and drops the clone
+ * (binary_matrix.rs:582-586), so both behaviours look the same to it. */
 int mzd_solve_left(mzd_t *A, mzd_t *B, int cutoff, int inconsistency_check); /* solve.rs:23 (solve_left, binary_matrix.rs:582-586) */
 
 /* ---- PLE / PLUQ decomposition and permutations (m4ri-sys/src/ple.rs, mzp.rs) ----

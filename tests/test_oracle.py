@@ -197,3 +197,24 @@ def test_ple_restatement_satisfies_its_definition(orc):
     I = orc.from_bits(np.eye(n, dtype=np.uint8))
     R, r, P, Q = orc.ple(I, n)
     assert r == n and list(P) == list(range(n)) and list(Q) == list(range(n)) and (R == I).all()
+
+
+def test_committed_full_size_checksum_is_reproducible(orc):
+    """tests/golden/full_size_checksums.json (made by make_full_size_checksums.py) holds the checksum
+    of the oracle's product of bench.py's seeded operands at the benchmark sizes; bench.py holds the
+    GPU result of every N to it. Recompute the n = 32768 entry here (a few seconds on all cores) with
+    the OTHER oracle strategy, Four Russians without the Strassen recursion, on a row sample, and
+    the full Strassen product's checksum itself."""
+    import json
+    import os
+    import bench
+    golden = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "full_size_checksums.json")))
+    assert set(golden) >= {"32768", "65536"}
+    for e in golden.values():
+        assert (e["seed_a"], e["seed_b"]) == (bench.SEED_A, bench.SEED_B)
+    n = 32768
+    A, B = orc.random(n, n, bench.SEED_A), orc.random(n, n, bench.SEED_B)
+    C = orc.mul_strassen(A, B, n, n, threads=0)
+    assert f"{orc.checksum(C, n):016x}" == golden[str(n)]["checksum"]
+    rows = np.arange(0, n, 997)  # the Strassen result against plain Four Russians on a sample of rows
+    assert (orc.mul_m4rm(np.ascontiguousarray(A[rows]), B, n, n, threads=0) == C[rows]).all()
