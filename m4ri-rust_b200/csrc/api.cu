@@ -10,6 +10,7 @@
 
 #include <condition_variable>
 #include <functional>
+#include <chrono>
 #include <mutex>
 #include <thread>
 #include <utility>
@@ -430,6 +431,38 @@ static void strassen_mul(DMat *C, const DMat *A, const DMat *B, int algo, int fo
   dmat_delete(Z, s);
 }
 
+// ---- burst or sustained? ----------------------------------------------------------------------
+// The level rule below was tuned on short bursts. Under a long run of large products the board's
+// power management lowers the SM clock (sw_power_cap: n = 32768 drifts 7.6 -> 8.0 ms within twenty
+// products), and a schedule with one more Strassen level — 12.5 % fewer tensor operations on
+// shorter, less efficient leaves — then wins and holds its time (profiles/r3e_levels_*.json: 7.685 ms
+// flat against 7.74 and climbing). The library therefore counts large tensor-path products that
+// arrive back to back (issued within 250 ms of the previous one); from the fifth on it takes the
+// extra level where the leaves stay >= 8192. A lone call, or calls with pauses between them, keep
+// the burst schedule. M4RI_B200_SUSTAINED=0 never switches, =1 always does. The result is the same
+// bits either way.
+static std::atomic<long long> g_last_large_ns{0};
+static std::atomic<int> g_large_streak{0};
+static int sustained_setting() {
+  static const int v = [] {
+    const char *e = getenv("M4RI_B200_SUSTAINED");
+    return e && *e ? atoi(e) : -1;
+  }();
+  return v;
+}
+static void note_large_product(int m, int k, int n) {  // called once per executed device product
+  if ((double)m * (double)k * (double)n < 16384.0 * 16384.0 * 16384.0) return;
+  const long long now = std::chrono::duration_cast<std::chrono::nanoseconds>(
+                            std::chrono::steady_clock::now().time_since_epoch()).count();
+  const long long last = g_last_large_ns.exchange(now);
+  if (last && now - last < 250000000LL) g_large_streak.fetch_add(1);
+  else g_large_streak.store(0);
+}
+static bool sustained_load() {
+  const int set = sustained_setting();
+  return set >= 0 ? set != 0 : g_large_streak.load() >= 4;
+}
+
 // Levels of recursion for an m x k x n product: the explicit setting, else as many
 // as keep every leaf dimension >= the cutoff (tuned on B200).
 static int strassen_levels(int m, int k, int n, int algo, int cutoff) {
@@ -463,6 +496,15 @@ static int strassen_levels(int m, int k, int n, int algo, int cutoff) {
     };
     int L = 0;
     while (L < 4 && leaf_ok(L + 1)) L++;
+    if (fused && L >= 1 && L < 4 && sustained_load()) {
+      // one more level than the burst rule, while the leaves keep k >= 8192, 4096-row sides and
+      // the volume the fused level needs
+      const int X = L + 1;
+      const long long lm = m >> X, lk = k >> X, ln = n >> X;
+      if (!(m % (256 << X)) && !(k % (256 << X)) && !(n % (256 << X)) && lm >= 4096 && ln >= 4096 && lk >= 8192 &&
+          (double)lm * (double)lk * (double)ln >= 8192.0 * 8192.0 * 8192.0)
+        L = X;
+    }
     return L;
   }
   if (cutoff <= 0) cutoff = algo == M4RI_B200_ALGO_MMA ? 16384 : 32768;
@@ -478,6 +520,7 @@ static int strassen_levels(int m, int k, int n, int algo, int cutoff) {
 
 static void product_with_strassen(DMat *C, const DMat *A, const DMat *B, int clear, int algo,
                                   int form, int cutoff, cudaStream_t s) {
+  if (algo == M4RI_B200_ALGO_MMA) note_large_product(C->nrows, A->ncols, C->ncols);
   const int L = strassen_levels(C->nrows, A->ncols, C->ncols, algo, cutoff);
   if (L <= 0 || (C->nrows % 512) || (C->ncols % 512) || (A->ncols % 512)) {
     leaf_mul(C, A, B, clear, algo, form, s);
